@@ -1,0 +1,93 @@
+// modarith.cuh -- 32-bit signed Montgomery arithmetic over two 27-bit NTT primes.
+//
+// Replaces the reference's 64-bit Barrett field (include/ntt_gpu/ntt_gpuntt.cuh:51-224,
+// FFP / barrett_mult over p ~ 2^60).  SURVEY.md F2: the external product is an exact
+// integer negacyclic convolution with |S| < 2^51, so any modulus P > 2^52 gives the
+// same ciphertext bits.  We use P = p0 * p1 (~2^54) with two primes < 2^27, each
+// = 1 (mod 2048), and recombine with a centred CRT.  Every modular multiply is then
+// 3 integer-pipe instructions (IMAD.WIDE, IMAD, IMAD.HI) on sm_100a instead of a
+// 64x64->128 Barrett product, and lazy signed residues need no conditional corrections.
+//
+// All functions are host+device so the same code is checked on the CPU
+// (tests/emul) before it runs on a GPU.
+#pragma once
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#define B2_HD __host__ __device__ __forceinline__
+#else
+#define B2_HD inline
+#endif
+
+namespace b2 {
+
+constexpr int kN = 1024;        // lvl1 ring degree (TFHEpp params/128bit.hpp:42-72)
+constexpr int kNbit = 10;
+constexpr int kLwe = 636;       // lvl0 dimension (128bit.hpp:7-23)
+constexpr int kL = 2;           // gadget levels
+constexpr int kRows = 4;        // (k+1)*l TRGSW rows
+constexpr int kIksT = 7;        // key-switch digits
+constexpr int kLvl0Words = kLwe + 1;
+constexpr int kLvl1Words = kN + 1;
+constexpr uint32_t kMu0 = 1u << 13;
+constexpr uint32_t kMu1 = 1u << 29;
+
+constexpr uint32_t inv32(uint32_t p)
+{   // p^-1 mod 2^32 by Newton iteration (p odd)
+    uint32_t x = p;
+    for (int i = 0; i < 5; i++) x *= 2u - p * x;
+    return x;
+}
+
+template <int Q> struct Prime;
+template <> struct Prime<0> {
+    static constexpr uint32_t p = 134215681u;           // 65535 * 2048 + 1
+    static constexpr uint32_t pinv = inv32(134215681u);
+};
+template <> struct Prime<1> {
+    static constexpr uint32_t p = 134203393u;           // 65529 * 2048 + 1
+    static constexpr uint32_t pinv = inv32(134203393u);
+};
+constexpr uint32_t kP[2] = {Prime<0>::p, Prime<1>::p};
+
+// a * b / 2^32 (mod p), result in (-p, p).  |a| < 2^31, 0 <= bt < p.
+// With bt = b * 2^32 mod p (Montgomery form) this is a * b mod p.
+template <int Q>
+B2_HD int32_t montmul(int32_t a, uint32_t bt)
+{
+    const int64_t prod = (int64_t)a * (int64_t)(int32_t)bt;
+    const int32_t m = (int32_t)((uint32_t)prod * Prime<Q>::pinv);
+#ifdef __CUDA_ARCH__
+    const int32_t t = __mulhi(m, (int32_t)Prime<Q>::p);
+#else
+    const int32_t t = (int32_t)(((int64_t)m * (int64_t)Prime<Q>::p) >> 32);
+#endif
+    return (int32_t)(prod >> 32) - t;
+}
+
+// canonical representative in [0, p) of a value in (-p, p)
+template <int Q>
+B2_HD uint32_t canon(int32_t a)
+{
+    return (uint32_t)(a + ((a >> 31) & (int32_t)Prime<Q>::p));
+}
+
+// ---- host-only helpers for table generation --------------------------------
+inline uint32_t h_mulmod(uint32_t a, uint32_t b, uint32_t p) { return (uint32_t)((uint64_t)a * b % p); }
+inline uint32_t h_powmod(uint32_t b, uint64_t e, uint32_t p)
+{
+    uint32_t r = 1;
+    while (e) { if (e & 1) r = h_mulmod(r, b, p); b = h_mulmod(b, b, p); e >>= 1; }
+    return r;
+}
+inline uint32_t h_to_mont(uint32_t a, uint32_t p) { return (uint32_t)((((uint64_t)a) << 32) % p); }
+// primitive 2N-th root of unity (smallest generator candidate g with (g^((p-1)/2N))^N == -1)
+inline uint32_t h_psi(uint32_t p)
+{
+    for (uint32_t g = 2;; g++) {
+        uint32_t psi = h_powmod(g, (p - 1) / (2 * kN), p);
+        if (h_powmod(psi, kN, p) == p - 1) return psi;
+    }
+}
+
+}  // namespace b2
