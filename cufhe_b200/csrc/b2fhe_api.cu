@@ -1,0 +1,241 @@
+// b2fhe_api.cu -- C ABI (include/b2fhe.h) over the sm_100a kernels.
+// Host-side counterpart of the reference's launch wrappers and key upload
+// (src/bootstrap_gpu.cu:97-155,782-1292, src/keyswitch_gpu.cu, src/cufhe_gates_gpu.cu).
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/b2fhe.h"
+#include "k_blindrotate.cuh"
+#include "k_keyswitch.cuh"
+#include "k_ntt.cuh"
+
+using namespace b2;
+
+namespace {
+
+constexpr int kMaxDev = 16;
+struct DevCtx {
+    bool ready = false;
+    bool owns_keys = false;
+    uint32_t* bk_ntt = nullptr;     // [636][4][2 primes][2][1024] Montgomery residues
+    uint32_t* ksk = nullptr;        // T[1024][7][3][320]
+    LaneTables* tab = nullptr;
+    int sm_count = 0;
+};
+DevCtx g_ctx[kMaxDev];
+std::mutex g_mu;
+int g_gates_per_cta = 0;
+std::atomic<uint64_t> g_launches{0};
+thread_local std::string t_err;
+
+int fail(int code, const char* what, const char* file, int line)
+{
+    char buf[512];
+    snprintf(buf, sizeof buf, "b2fhe: %s failed at %s:%d : %s", what, file, line,
+             code >= 10000 ? "invalid use" : cudaGetErrorString((cudaError_t)code));
+    t_err = buf;
+    return code;
+}
+#define CK(expr)                                                         \
+    do {                                                                 \
+        cudaError_t e_ = (expr);                                         \
+        if (e_ != cudaSuccess) return fail((int)e_, #expr, __FILE__, __LINE__); \
+    } while (0)
+#define REQUIRE(cond, code)                                              \
+    do {                                                                 \
+        if (!(cond)) return fail(code, #cond, __FILE__, __LINE__);       \
+    } while (0)
+#define LAUNCHED() do { g_launches.fetch_add(1, std::memory_order_relaxed); CK(cudaGetLastError()); } while (0)
+
+template <int G> int set_br_attr()
+{
+    CK(cudaFuncSetAttribute(k_blind_rotate<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, br_smem_bytes(G)));
+    return 0;
+}
+
+// twiddle tables + kernel attributes on `device` (InitializeNTThandlers, src/bootstrap_gpu.cu:97-109)
+int setup_device(int device)
+{
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    REQUIRE(device >= 0 && device < ndev && device < kMaxDev, B2FHE_E_NO_DEVICE);
+    CK(cudaSetDevice(device));
+    DevCtx& c = g_ctx[device];
+    if (c.tab) return 0;
+    static NttTables T;
+    static bool made = false;
+    if (!made) { make_tables(T); made = true; }
+    CK(cudaMemcpyToSymbol(c_fw1, T.fw1, sizeof T.fw1));
+    CK(cudaMemcpyToSymbol(c_iv1, T.iv1, sizeof T.iv1));
+    CK(cudaMemcpyToSymbol(c_r2, T.r2, sizeof T.r2));
+    CK(cudaMemcpyToSymbol(c_crt_p0inv, &T.crt_p0inv_mont, sizeof(uint32_t)));
+    static LaneTables L;
+    memcpy(L.fw2, T.fw2, sizeof L.fw2);
+    memcpy(L.iv2, T.iv2, sizeof L.iv2);
+    memcpy(L.scale, T.scale, sizeof L.scale);
+    CK(cudaMalloc(&c.tab, sizeof(LaneTables)));
+    CK(cudaMemcpy(c.tab, &L, sizeof L, cudaMemcpyHostToDevice));
+    CK(cudaDeviceGetAttribute(&c.sm_count, cudaDevAttrMultiProcessorCount, device));
+    // keep stream-ordered scratch cached between calls
+    cudaMemPool_t pool;
+    CK(cudaDeviceGetDefaultMemPool(&pool, device));
+    uint64_t keep = ~0ull;
+    CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    if (int r = set_br_attr<1>()) return r;
+    if (int r = set_br_attr<2>()) return r;
+    if (int r = set_br_attr<4>()) return r;
+    if (int r = set_br_attr<6>()) return r;
+    if (int r = set_br_attr<8>()) return r;
+    CK(cudaFuncSetAttribute(k_ntt_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
+    CK(cudaFuncSetAttribute(k_ntt_inv, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
+    CK(cudaFuncSetAttribute(k_polymul, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
+    return 0;
+}
+
+int ntt_grid(const DevCtx& c, size_t npoly)
+{
+    size_t blocks = (npoly + kNttPolysPerCta - 1) / kNttPolysPerCta;
+    size_t cap = (size_t)c.sm_count * 16;
+    return (int)(blocks < cap ? (blocks ? blocks : 1) : cap);
+}
+
+// BootstrappingKeyToNTT + KeySwitchingKeyToDevice on one device (src/bootstrap_gpu.cu:111-138,
+// src/keyswitch_gpu.cu:6-16)
+int convert_keys(int device, const uint32_t* bk_raw, const uint16_t* ksk_raw)
+{
+    DevCtx& c = g_ctx[device];
+    CK(cudaSetDevice(device));
+    uint32_t* d_raw = nullptr;
+    uint16_t* d_kraw = nullptr;
+    CK(cudaMalloc(&c.bk_ntt, B2FHE_BK_NTT_BYTES));
+    CK(cudaMalloc(&c.ksk, B2FHE_KSK_DEV_BYTES));
+    c.owns_keys = true;
+    CK(cudaMalloc(&d_raw, B2FHE_BK_RAW_WORDS * 4));
+    CK(cudaMalloc(&d_kraw, B2FHE_KSK_RAW_WORDS * 2));
+    CK(cudaMemcpy(d_raw, bk_raw, B2FHE_BK_RAW_WORDS * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_kraw, ksk_raw, B2FHE_KSK_RAW_WORDS * 2, cudaMemcpyHostToDevice));
+    const int npoly = kLwe * kRows * 2;
+    k_ntt_fwd<<<ntt_grid(c, npoly), kNttThreads, kNttSmemBytes>>>(d_raw, c.bk_ntt, npoly, 1, 0, c.tab);
+    LAUNCHED();
+    k_ksk_layout<<<c.sm_count * 8, 256>>>(d_kraw, c.ksk);
+    LAUNCHED();
+    CK(cudaDeviceSynchronize());
+    CK(cudaFree(d_raw));
+    CK(cudaFree(d_kraw));
+    c.ready = true;
+    return 0;
+}
+
+int get_ctx(int device, DevCtx*& c)
+{
+    REQUIRE(device >= 0 && device < kMaxDev, B2FHE_E_NO_DEVICE);
+    c = &g_ctx[device];
+    REQUIRE(c->ready, B2FHE_E_NOT_INITIALIZED);
+    CK(cudaSetDevice(device));
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* b2fhe_last_error_string(void) { return t_err.c_str(); }
+uint64_t b2fhe_kernel_launches(void) { return g_launches.load(); }
+int b2fhe_set_gates_per_cta(int gates)
+{
+    REQUIRE(gates == 0 || gates == 1 || gates == 2 || gates == 4 || gates == 6 || gates == 8, B2FHE_E_BAD_ARGUMENT);
+    g_gates_per_cta = gates;
+    return 0;
+}
+int b2fhe_num_devices(void)
+{
+    int n = 0;
+    for (int i = 0; i < kMaxDev; i++) n += g_ctx[i].ready;
+    return n;
+}
+
+int b2fhe_init_device(int device, const uint32_t* bk_raw, const uint16_t* ksk_raw)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    REQUIRE(bk_raw && ksk_raw, B2FHE_E_BAD_ARGUMENT);
+    if (int r = setup_device(device)) return r;
+    REQUIRE(!g_ctx[device].ready, B2FHE_E_BAD_ARGUMENT);
+    return convert_keys(device, bk_raw, ksk_raw);
+}
+
+int b2fhe_init(int ngpu, const uint32_t* bk_raw, const uint16_t* ksk_raw)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    REQUIRE(ngpu >= 1 && ngpu <= kMaxDev && bk_raw && ksk_raw, B2FHE_E_BAD_ARGUMENT);
+    for (int d = 0; d < ngpu; d++) {
+        if (int r = setup_device(d)) return r;
+        REQUIRE(!g_ctx[d].ready, B2FHE_E_BAD_ARGUMENT);
+    }
+    if (int r = convert_keys(0, bk_raw, ksk_raw)) return r;
+    // replicate the converted keys device-to-device (NVLink peer copies) instead of
+    // re-uploading and re-converting per GPU as the reference does
+    for (int d = 1; d < ngpu; d++) {
+        DevCtx& c = g_ctx[d];
+        CK(cudaSetDevice(d));
+        CK(cudaMalloc(&c.bk_ntt, B2FHE_BK_NTT_BYTES));
+        CK(cudaMalloc(&c.ksk, B2FHE_KSK_DEV_BYTES));
+        c.owns_keys = true;
+        CK(cudaMemcpyPeer(c.bk_ntt, d, g_ctx[0].bk_ntt, 0, B2FHE_BK_NTT_BYTES));
+        CK(cudaMemcpyPeer(c.ksk, d, g_ctx[0].ksk, 0, B2FHE_KSK_DEV_BYTES));
+        c.ready = true;
+    }
+    return 0;
+}
+
+int b2fhe_adopt_keys(int device, const void* bk_ntt_dev, const void* ksk_dev)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    REQUIRE(bk_ntt_dev && ksk_dev, B2FHE_E_BAD_ARGUMENT);
+    if (int r = setup_device(device)) return r;
+    DevCtx& c = g_ctx[device];
+    REQUIRE(!c.ready, B2FHE_E_BAD_ARGUMENT);
+    c.bk_ntt = (uint32_t*)bk_ntt_dev;
+    c.ksk = (uint32_t*)ksk_dev;
+    c.owns_keys = false;
+    c.ready = true;
+    return 0;
+}
+
+int b2fhe_key_pointers(int device, void** bk_ntt_dev, void** ksk_dev)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    if (bk_ntt_dev) *bk_ntt_dev = c->bk_ntt;
+    if (ksk_dev) *ksk_dev = c->ksk;
+    return 0;
+}
+
+int b2fhe_cleanup(void)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (int d = 0; d < kMaxDev; d++) {
+        DevCtx& c = g_ctx[d];
+        if (!c.tab && !c.ready) continue;
+        CK(cudaSetDevice(d));
+        CK(cudaDeviceSynchronize());
+        if (c.owns_keys) { CK(cudaFree(c.bk_ntt)); CK(cudaFree(c.ksk)); }
+        if (c.tab) CK(cudaFree(c.tab));
+        c = DevCtx();
+    }
+    return 0;
+}
+
+int b2fhe_synchronize(void)
+{
+    for (int d = 0; d < kMaxDev; d++)
+        if (g_ctx[d].ready) { CK(cudaSetDevice(d)); CK(cudaDeviceSynchronize()); }
+    return 0;
+}
+
+}  // extern "C"
+
+#include "b2fhe_gates.inl"

@@ -1,0 +1,354 @@
+// b2fhe_gates.inl -- gate / stage entry points of the C ABI (included by b2fhe_api.cu).
+// Host-side composition that the reference does inside one kernel per gate
+// (__HomGate__ both orders, Mux/NMux, Not/Copy: src/bootstrap_gpu.cu:383-780).
+
+namespace {
+
+template <int G> int launch_br_g(const BrParams& P, cudaStream_t st)
+{
+    const int grid = (P.count + G - 1) / G;
+    k_blind_rotate<G><<<grid, 64 * G, br_smem_bytes(G), st>>>(P);
+    LAUNCHED();
+    return 0;
+}
+int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
+{
+    if (P.count <= 0) return 0;
+    P.bk = c.bk_ntt;
+    P.tab = c.tab;
+    int g = g_gates_per_cta;
+    if (g == 0) {
+        // spread small batches over all SMs; large batches use the widest CTA
+        const int per_sm = (P.count + c.sm_count - 1) / c.sm_count;
+        g = per_sm >= 6 ? 6 : per_sm >= 4 ? 4 : per_sm >= 2 ? 2 : 1;
+    }
+    switch (g) {
+        case 1: return launch_br_g<1>(P, st);
+        case 2: return launch_br_g<2>(P, st);
+        case 4: return launch_br_g<4>(P, st);
+        case 8: return launch_br_g<8>(P, st);
+        default: return launch_br_g<6>(P, st);
+    }
+}
+int launch_ks(const DevCtx& c, KsParams P, cudaStream_t st)
+{
+    if (P.count <= 0) return 0;
+    P.T = c.ksk;
+    k_keyswitch<<<(P.count + kKsGates - 1) / kKsGates, 32 * kKsGates, 0, st>>>(P);
+    LAUNCHED();
+    return 0;
+}
+template <typename T>
+int launch_affine(T* out, const T* A, const T* B, const AffItem* items, int count, int words, int ca, int cb,
+                  uint32_t off, cudaStream_t st)
+{
+    if (count <= 0) return 0;
+    k_affine<T><<<count < 65535 ? count : 65535, 128, 0, st>>>(out, A, B, items, count, words, ca, cb, off);
+    LAUNCHED();
+    return 0;
+}
+
+// stream-ordered scratch
+struct Scratch {
+    cudaStream_t st;
+    std::vector<void*> ptrs;
+    explicit Scratch(cudaStream_t s) : st(s) {}
+    int get(void** p, size_t bytes)
+    {
+        CK(cudaMallocAsync(p, bytes ? bytes : 16, st));
+        ptrs.push_back(*p);
+        return 0;
+    }
+    ~Scratch() { for (void* p : ptrs) cudaFreeAsync(p, st); }
+};
+
+int uniform_gate(const DevCtx& c, cudaStream_t st, int op, int level, void* out, const void* in0, const void* in1,
+                 const void* in2, int count)
+{
+    Scratch S(st);
+    if (op == B2FHE_NOT || op == B2FHE_COPY) {
+        const int ca = op == B2FHE_NOT ? -1 : 1;
+        if (level == 0) return launch_affine<uint16_t>((uint16_t*)out, (const uint16_t*)in0, nullptr, nullptr, count, kLvl0Words, ca, 0, 0u, st);
+        return launch_affine<uint32_t>((uint32_t*)out, (const uint32_t*)in0, nullptr, nullptr, count, kLvl1Words, ca, 0, 0u, st);
+    }
+    BrParams B{};
+    KsParams K{};
+    B.count = K.count = count;
+    B.mu = kMu1;
+    if (op < B2FHE_MUX) {
+        int ca, cb, so;
+        gate_coeffs(op, ca, cb, so);
+        REQUIRE(in1 != nullptr, B2FHE_E_BAD_ARGUMENT);
+        if (level == 0) {       // BR(pre-add) -> SE -> IKS   (src/bootstrap_gpu.cu:402-421)
+            uint32_t* t1;
+            if (int r = S.get((void**)&t1, (size_t)count * kLvl1Words * 4)) return r;
+            B.in0 = (const uint16_t*)in0; B.in1 = (const uint16_t*)in1; B.out = t1;
+            B.ca = ca; B.cb = cb; B.off = so * (int)kMu0;
+            if (int r = launch_br(c, B, st)) return r;
+            K.A = t1; K.out = (uint16_t*)out; K.ca = 1; K.cb = 0; K.off = 0u;
+            return launch_ks(c, K, st);
+        }
+        // IKS(pre-add) -> BR -> SE   (src/bootstrap_gpu.cu:383-400)
+        uint16_t* t0;
+        if (int r = S.get((void**)&t0, (size_t)count * kLvl0Words * 2)) return r;
+        K.A = (const uint32_t*)in0; K.B = (const uint32_t*)in1; K.out = t0;
+        K.ca = ca; K.cb = cb; K.off = (uint32_t)so * kMu1;
+        if (int r = launch_ks(c, K, st)) return r;
+        B.in0 = t0; B.out = (uint32_t*)out; B.ca = 1; B.cb = 0; B.off = 0;
+        return launch_br(c, B, st);
+    }
+    // MUX / NMUX: in0 = inc, in1 = in1, in2 = in0 of the reference signature
+    REQUIRE(in1 != nullptr && in2 != nullptr, B2FHE_E_BAD_ARGUMENT);
+    const int sg = op == B2FHE_NMUX ? -1 : 1;
+    if (level == 0) {           // src/bootstrap_gpu.cu:515-588
+        uint32_t *ta, *tb;
+        if (int r = S.get((void**)&ta, (size_t)count * kLvl1Words * 4)) return r;
+        if (int r = S.get((void**)&tb, (size_t)count * kLvl1Words * 4)) return r;
+        B.in0 = (const uint16_t*)in0; B.in1 = (const uint16_t*)in1; B.out = ta;
+        B.ca = 1; B.cb = 1; B.off = -(int)kMu0;
+        if (int r = launch_br(c, B, st)) return r;
+        B.in1 = (const uint16_t*)in2; B.out = tb; B.ca = -1;
+        if (int r = launch_br(c, B, st)) return r;
+        K.A = ta; K.B = tb; K.out = (uint16_t*)out; K.ca = sg; K.cb = sg; K.off = (uint32_t)sg * kMu1;
+        return launch_ks(c, K, st);
+    }
+    // src/bootstrap_gpu.cu:706-780
+    uint16_t *t0a, *t0b;
+    uint32_t *ea, *eb;
+    if (int r = S.get((void**)&t0a, (size_t)count * kLvl0Words * 2)) return r;
+    if (int r = S.get((void**)&t0b, (size_t)count * kLvl0Words * 2)) return r;
+    if (int r = S.get((void**)&ea, (size_t)count * kLvl1Words * 4)) return r;
+    if (int r = S.get((void**)&eb, (size_t)count * kLvl1Words * 4)) return r;
+    K.A = (const uint32_t*)in0; K.B = (const uint32_t*)in1; K.out = t0a; K.ca = 1; K.cb = 1; K.off = 0u - kMu1;
+    if (int r = launch_ks(c, K, st)) return r;
+    K.B = (const uint32_t*)in2; K.out = t0b; K.ca = -1;
+    if (int r = launch_ks(c, K, st)) return r;
+    B.in0 = t0a; B.out = ea; B.ca = 1; B.cb = 0; B.off = 0;
+    if (int r = launch_br(c, B, st)) return r;
+    B.in0 = t0b; B.out = eb;
+    if (int r = launch_br(c, B, st)) return r;
+    return launch_affine<uint32_t>((uint32_t*)out, ea, eb, nullptr, count, kLvl1Words, sg, sg, (uint32_t)sg * kMu1, st);
+}
+
+template <typename T> int upload(Scratch& S, T** dev, const std::vector<T>& host)
+{
+    if (int r = S.get((void**)dev, host.size() * sizeof(T))) return r;
+    if (!host.empty()) CK(cudaMemcpyAsync(*dev, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice, S.st));
+    return 0;
+}
+
+// per-gate op codes: build work-item lists on the host, then the same three kernels
+int mixed_gate(const DevCtx& c, cudaStream_t st, const uint8_t* ops, int level, void* out, const void* in0,
+               const void* in1, const void* in2, int count)
+{
+    Scratch S(st);
+    std::vector<BrItem> br;
+    std::vector<KsItem> ks;
+    std::vector<AffItem> af;    // level 0: Not/Copy only; level 1: every gate's final write
+    br.reserve(count + count / 4);
+    ks.reserve(count + count / 4);
+    for (int g = 0; g < count; g++) {
+        const int op = ops[g];
+        REQUIRE(op < B2FHE_NUM_OPS, B2FHE_E_BAD_ARGUMENT);
+        if (op == B2FHE_NOT || op == B2FHE_COPY) {
+            AffItem a{}; a.s0 = a.s1 = a.slot = (uint32_t)g; a.ca = op == B2FHE_NOT ? -1 : 1; a.cb = 0; a.off = 0;
+            a.pad[0] = 1;   // marks "source is the input array" for level 1
+            af.push_back(a);
+            continue;
+        }
+        int ca, cb, so;
+        const bool mux = op >= B2FHE_MUX;
+        const int sg = op == B2FHE_NMUX ? -1 : 1;
+        if (!mux) gate_coeffs(op, ca, cb, so);
+        if (level == 0) {
+            KsItem k{}; k.slot = (uint32_t)g;
+            if (!mux) {
+                BrItem b{}; b.g0 = b.g1 = (uint32_t)g; b.ca = (int8_t)ca; b.cb = (int8_t)cb; b.src1 = 0;
+                b.off = so * (int)kMu0; b.slot = (uint32_t)br.size();
+                k.s0 = k.s1 = b.slot; k.ca = 1; k.cb = 0; k.off = 0;
+                br.push_back(b);
+            } else {
+                BrItem b{}; b.g0 = b.g1 = (uint32_t)g; b.ca = 1; b.cb = 1; b.src1 = 0; b.off = -(int)kMu0;
+                b.slot = (uint32_t)br.size(); k.s0 = b.slot; br.push_back(b);
+                b.ca = -1; b.src1 = 1; b.slot = (uint32_t)br.size(); k.s1 = b.slot; br.push_back(b);
+                k.ca = (int8_t)sg; k.cb = (int8_t)sg; k.off = (uint32_t)sg * kMu1;
+            }
+            ks.push_back(k);
+        } else {
+            AffItem a{}; a.slot = (uint32_t)g;
+            if (!mux) {
+                KsItem k{}; k.s0 = k.s1 = (uint32_t)g; k.ca = (int8_t)ca; k.cb = (int8_t)cb; k.off = (uint32_t)so * kMu1;
+                k.slot = (uint32_t)ks.size(); k.pad[0] = 0;
+                a.s0 = a.s1 = k.slot; a.ca = 1; a.cb = 0; a.off = 0;
+                ks.push_back(k);
+            } else {
+                KsItem k{}; k.s0 = k.s1 = (uint32_t)g; k.ca = 1; k.cb = 1; k.off = 0u - kMu1; k.pad[0] = 0;
+                k.slot = (uint32_t)ks.size(); a.s0 = k.slot; ks.push_back(k);
+                k.ca = -1; k.pad[0] = 1; k.slot = (uint32_t)ks.size(); a.s1 = k.slot; ks.push_back(k);
+                a.ca = (int8_t)sg; a.cb = (int8_t)sg; a.off = (uint32_t)sg * kMu1;
+            }
+            af.push_back(a);
+        }
+    }
+    BrParams B{};
+    KsParams K{};
+    B.mu = kMu1;
+    if (level == 0) {
+        BrItem* d_br; KsItem* d_ks; AffItem* d_af; uint32_t* t1;
+        if (int r = upload(S, &d_br, br)) return r;
+        if (int r = upload(S, &d_ks, ks)) return r;
+        if (int r = upload(S, &d_af, af)) return r;
+        if (int r = S.get((void**)&t1, br.size() * (size_t)kLvl1Words * 4)) return r;
+        B.in0 = (const uint16_t*)in0; B.in1 = (const uint16_t*)in1; B.in2 = (const uint16_t*)in2;
+        B.out = t1; B.items = d_br; B.count = (int)br.size();
+        if (int r = launch_br(c, B, st)) return r;
+        // Not/Copy read their inputs before any key-switch result lands in `out`
+        if (int r = launch_affine<uint16_t>((uint16_t*)out, (const uint16_t*)in0, nullptr, d_af, (int)af.size(), kLvl0Words, 0, 0, 0u, st)) return r;
+        K.A = t1; K.B = t1; K.out = (uint16_t*)out; K.items = d_ks; K.count = (int)ks.size();
+        return launch_ks(c, K, st);
+    }
+    // level 1: key switch (inputs) -> blind rotate -> final affine into `out`.
+    // A Mux needs the second operand from in1 for branch 1 and in2 for branch 0: two
+    // key-switch launches, one per source array.
+    std::vector<KsItem> ks1, ks2;
+    for (const KsItem& k : ks) (k.pad[0] ? ks2 : ks1).push_back(k);
+    std::vector<AffItem> afin, afout;
+    for (const AffItem& a : af) (a.pad[0] ? afin : afout).push_back(a);
+    KsItem *d_k1, *d_k2; AffItem *d_ai, *d_ao; uint16_t* t0; uint32_t* e;
+    if (int r = upload(S, &d_k1, ks1)) return r;
+    if (int r = upload(S, &d_k2, ks2)) return r;
+    if (int r = upload(S, &d_ai, afin)) return r;
+    if (int r = upload(S, &d_ao, afout)) return r;
+    if (int r = S.get((void**)&t0, ks.size() * (size_t)kLvl0Words * 2)) return r;
+    if (int r = S.get((void**)&e, ks.size() * (size_t)kLvl1Words * 4)) return r;
+    K.A = (const uint32_t*)in0; K.out = t0;
+    K.B = (const uint32_t*)in1; K.items = d_k1; K.count = (int)ks1.size();
+    if (int r = launch_ks(c, K, st)) return r;
+    K.B = (const uint32_t*)in2; K.items = d_k2; K.count = (int)ks2.size();
+    if (int r = launch_ks(c, K, st)) return r;
+    B.in0 = t0; B.out = e; B.ca = 1; B.cb = 0; B.off = 0; B.count = (int)ks.size();
+    if (int r = launch_br(c, B, st)) return r;
+    if (int r = launch_affine<uint32_t>((uint32_t*)out, (const uint32_t*)in0, nullptr, d_ai, (int)afin.size(), kLvl1Words, 0, 0, 0u, st)) return r;
+    return launch_affine<uint32_t>((uint32_t*)out, e, e, d_ao, (int)afout.size(), kLvl1Words, 0, 0, 0u, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int b2fhe_gate_batch(int device, b2fhe_stream_t stream, int op, int level, void* out, const void* in0,
+                     const void* in1, const void* in2, size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE(op >= 0 && op < B2FHE_NUM_OPS && (level == 0 || level == 1) && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(out && in0, B2FHE_E_BAD_ARGUMENT);
+    return uniform_gate(*c, (cudaStream_t)stream, op, level, out, in0, in1, in2, (int)count);
+}
+
+int b2fhe_gate_batch_mixed(int device, b2fhe_stream_t stream, const uint8_t* ops_host, int level, void* out,
+                           const void* in0, const void* in1, const void* in2, size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE((level == 0 || level == 1) && count < (1u << 29), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(ops_host && out && in0 && in1 && in2, B2FHE_E_BAD_ARGUMENT);
+    return mixed_gate(*c, (cudaStream_t)stream, ops_host, level, out, in0, in1, in2, (int)count);
+}
+
+int b2fhe_gate_batch_host(int device, b2fhe_stream_t stream, int op, const uint8_t* ops_host, int level,
+                          void* out_host, const void* in0_host, const void* in1_host, const void* in2_host,
+                          size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE((level == 0 || level == 1) && count < (1u << 29), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(out_host && in0_host, B2FHE_E_BAD_ARGUMENT);
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t bytes = count * (level == 0 ? (size_t)kLvl0Words * 2 : (size_t)kLvl1Words * 4);
+    Scratch S(st);
+    void *d0 = nullptr, *d1 = nullptr, *d2 = nullptr, *dout = nullptr;
+    if (int r = S.get(&d0, bytes)) return r;
+    if (int r = S.get(&dout, bytes)) return r;
+    CK(cudaMemcpyAsync(d0, in0_host, bytes, cudaMemcpyHostToDevice, st));
+    if (in1_host) {
+        if (int r = S.get(&d1, bytes)) return r;
+        CK(cudaMemcpyAsync(d1, in1_host, bytes, cudaMemcpyHostToDevice, st));
+    }
+    if (in2_host) {
+        if (int r = S.get(&d2, bytes)) return r;
+        CK(cudaMemcpyAsync(d2, in2_host, bytes, cudaMemcpyHostToDevice, st));
+    }
+    int r;
+    if (ops_host) {
+        REQUIRE(d1 && d2, B2FHE_E_BAD_ARGUMENT);
+        r = mixed_gate(*c, st, ops_host, level, dout, d0, d1, d2, (int)count);
+    } else {
+        REQUIRE(op >= 0 && op < B2FHE_NUM_OPS, B2FHE_E_BAD_ARGUMENT);
+        r = uniform_gate(*c, st, op, level, dout, d0, d1, d2, (int)count);
+    }
+    if (r) return r;
+    CK(cudaMemcpyAsync(out_host, dout, bytes, cudaMemcpyDeviceToHost, st));
+    return 0;
+}
+
+int b2fhe_blind_rotate_batch(int device, b2fhe_stream_t stream, uint32_t* out_lvl1, const uint16_t* in_lvl0,
+                             uint32_t mu, size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE(count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(out_lvl1 && in_lvl0, B2FHE_E_BAD_ARGUMENT);
+    BrParams B{};
+    B.in0 = in_lvl0; B.out = out_lvl1; B.count = (int)count; B.ca = 1; B.cb = 0; B.off = 0; B.mu = mu;
+    return launch_br(*c, B, (cudaStream_t)stream);
+}
+
+int b2fhe_keyswitch_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0, const uint32_t* in_lvl1, size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE(count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(out_lvl0 && in_lvl1, B2FHE_E_BAD_ARGUMENT);
+    KsParams K{};
+    K.A = in_lvl1; K.out = out_lvl0; K.count = (int)count; K.ca = 1; K.cb = 0; K.off = 0u;
+    return launch_ks(*c, K, (cudaStream_t)stream);
+}
+
+int b2fhe_ntt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* in, size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    if (count == 0) return 0;
+    REQUIRE(out && in && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    k_ntt_fwd<<<ntt_grid(*c, count), kNttThreads, kNttSmemBytes, (cudaStream_t)stream>>>(in, out, (int)count, 0, 0, c->tab);
+    LAUNCHED();
+    return 0;
+}
+int b2fhe_intt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* in, size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    if (count == 0) return 0;
+    REQUIRE(out && in && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    k_ntt_inv<<<ntt_grid(*c, count), kNttThreads, kNttSmemBytes, (cudaStream_t)stream>>>(in, out, (int)count, c->tab);
+    LAUNCHED();
+    return 0;
+}
+int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* a, const uint32_t* b, size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    if (count == 0) return 0;
+    REQUIRE(out && a && b && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    k_polymul<<<ntt_grid(*c, count), kNttThreads, kNttSmemBytes, (cudaStream_t)stream>>>(a, b, out, (int)count, c->tab);
+    LAUNCHED();
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,135 @@
+// k_keyswitch.cuh -- batched identity key switch lvl1 -> lvl0 with fused linear
+// pre-add, plus the trivial elementwise gates.
+//
+// Replaces KeySwitchFromTLWE / KeySwitch / IdentityKeySwitchPreAdd (reference
+// include/keyswitch_gpu.cuh:25-188): there one thread per OUTPUT column walks
+// 1024 x 7 digits serially with scattered u16 loads.  Here one warp owns a gate,
+// every selected key row is read as ten coalesced 128-byte lines, and two u16
+// columns are accumulated per 32-bit add (exact: arithmetic is mod 2^16).
+//
+// Device key layout (built once by k_ksk_layout): T[j][d][3][320] u32, each word two
+// u16 columns, rows padded to 640 columns and PRE-SIGNED so the kernel only adds:
+//   slot 0: digit 0 (value -2) -> +ksk[j][d][1]
+//   slot 1: digit 1 (value -1) -> +ksk[j][d][0]
+//   slot 2: digit 3 (value +1) -> -ksk[j][d][0]        (digit 2 = value 0: skipped)
+#pragma once
+#include "dev_common.cuh"
+
+namespace b2 {
+
+constexpr int kKsRowWords = 320;                                   // 640 u16 columns
+constexpr size_t kKskDevWords = (size_t)kN * kIksT * 3 * kKsRowWords;
+
+__global__ void k_ksk_layout(const uint16_t* __restrict__ raw /*[1024][7][2][637]*/, uint32_t* __restrict__ T)
+{
+    const size_t total = kKskDevWords;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int w = (int)(idx % kKsRowWords);
+        const size_t r = idx / kKsRowWords;
+        const int slot = (int)(r % 3);
+        const size_t jd = r / 3;
+        const int src = slot == 0 ? 1 : 0;
+        const uint16_t* row = raw + (jd * 2 + src) * kLvl0Words;
+        uint32_t lo = 2 * w < kLvl0Words ? row[2 * w] : 0u;
+        uint32_t hi = 2 * w + 1 < kLvl0Words ? row[2 * w + 1] : 0u;
+        if (slot == 2) { lo = (0u - lo) & 0xFFFFu; hi = (0u - hi) & 0xFFFFu; }
+        T[idx] = lo | (hi << 16);
+    }
+}
+
+// key-switch work item: e = ca*A[s0] + cb*B[s1] + (0, off) over u32, out[slot] (637 u16)
+struct KsItem {
+    uint32_t s0, s1;
+    int8_t ca, cb;
+    int8_t pad[2];
+    uint32_t off;
+    uint32_t slot;
+};
+struct KsParams {
+    const uint32_t* A;      // [*][1025]
+    const uint32_t* B;      // may be null when cb == 0
+    uint16_t* out;          // [*][637]
+    const KsItem* items;    // null: uniform
+    const uint32_t* T;      // device key
+    int count;
+    int ca, cb;
+    uint32_t off;
+};
+
+constexpr int kKsGates = 8;                       // warps (= gates) per CTA
+
+__global__ void __launch_bounds__(32 * kKsGates) k_keyswitch(const KsParams P)
+{
+    __shared__ uint32_t s_t[kKsGates][kN];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int item = blockIdx.x * kKsGates + warp;
+    if (item >= P.count) return;
+    KsItem it;
+    if (P.items) it = P.items[item];
+    else { it.s0 = it.s1 = it.slot = (uint32_t)item; it.ca = (int8_t)P.ca; it.cb = (int8_t)P.cb; it.off = P.off; }
+    const uint32_t* x0 = P.A + (size_t)it.s0 * kLvl1Words;
+    const uint32_t* x1 = (it.cb != 0 && P.B) ? P.B + (size_t)it.s1 * kLvl1Words : nullptr;
+    const uint32_t ca = (uint32_t)(int32_t)it.ca, cb = x1 ? (uint32_t)(int32_t)it.cb : 0u;
+    // pre-add in u32 (keyswitch_gpu.cuh:158,168) + decomposition offset
+    for (int j = lane; j < kN; j += 32) s_t[warp][j] = ca * x0[j] + (x1 ? cb * x1[j] : 0u) + kIksAdd;
+    const uint32_t eb = ca * x0[kN] + (x1 ? cb * x1[kN] : 0u) + it.off;
+    __syncwarp();
+
+    uint32_t accF[10], accH[10];
+#pragma unroll
+    for (int w = 0; w < 10; w++) accF[w] = accH[w] = 0u;
+    const uint32_t* Tl = P.T + lane;
+    for (int j = 0; j < kN; j++) {
+        const uint32_t tj = s_t[warp][j];
+#pragma unroll
+        for (int d = 0; d < kIksT; d++) {
+            const uint32_t dg = iks_digit(tj, d);
+            if (dg != 2u) {
+                const uint32_t* row = Tl + ((size_t)(j * kIksT + d) * 3 + min(dg, 2u)) * kKsRowWords;
+#pragma unroll
+                for (int w = 0; w < 10; w++) {
+                    const uint32_t v = __ldg(row + 32 * w);
+                    accF[w] += v;
+                    accH[w] += v >> 16;
+                }
+            }
+        }
+    }
+    uint16_t* out = P.out + (size_t)it.slot * kLvl0Words;
+#pragma unroll
+    for (int w = 0; w < 10; w++) {
+        const int c0 = 2 * (lane + 32 * w);
+        if (c0 < kLwe) out[c0] = (uint16_t)accF[w];
+        else if (c0 == kLwe) out[c0] = (uint16_t)(accF[w] + iks_round_b(eb));
+        if (c0 + 1 < kLwe) out[c0 + 1] = (uint16_t)accH[w];
+        else if (c0 + 1 == kLwe) out[c0 + 1] = (uint16_t)(accH[w] + iks_round_b(eb));
+    }
+}
+
+// out[slot] = ca*A[s0] + cb*B[s1] + (0,..,0,off) elementwise, T = u16 (637 words) or
+// u32 (1025 words).  Covers Not/Copy (src/bootstrap_gpu.cu:681-703) and the lvl1
+// Mux/NMux combine (:718-741,756-780).
+struct AffItem { uint32_t s0, s1; int8_t ca, cb; int8_t pad[2]; uint32_t off; uint32_t slot; };
+template <typename T>
+__global__ void k_affine(T* __restrict__ out, const T* __restrict__ A, const T* __restrict__ B, const AffItem* items,
+                         int count, int words, int ca_u, int cb_u, uint32_t off_u)
+{
+    const int per = (words + 127) / 128;   // threads cover a ciphertext in chunks of 128
+    (void)per;
+    for (int item = blockIdx.x; item < count; item += gridDim.x) {
+        AffItem it;
+        if (items) it = items[item];
+        else { it.s0 = it.s1 = it.slot = (uint32_t)item; it.ca = (int8_t)ca_u; it.cb = (int8_t)cb_u; it.off = off_u; }
+        const T* x0 = A + (size_t)it.s0 * words;
+        const T* x1 = (it.cb != 0 && B) ? B + (size_t)it.s1 * words : nullptr;
+        T* o = out + (size_t)it.slot * words;
+        for (int i = threadIdx.x; i < words; i += blockDim.x) {
+            uint32_t v = (uint32_t)(int32_t)it.ca * (uint32_t)x0[i];
+            if (x1) v += (uint32_t)(int32_t)it.cb * (uint32_t)x1[i];
+            if (i == words - 1) v += it.off;
+            o[i] = (T)v;
+        }
+    }
+}
+
+}  // namespace b2

@@ -1,0 +1,112 @@
+/*
+ * b2fhe.h -- C ABI of the B200-native TFHE gate-bootstrapping engine.
+ *
+ * This is the drop-in boundary for cuFHE's bootstrapping path: plain
+ * pointers and sizes, no C++/torch types.  The reference has no FFI layer; the
+ * functions below replace its launch wrappers and key upload, which the C++ shim
+ * include/cufhe_b200.hpp (same names/signatures as include/cufhe_gpu.cuh) calls.
+ * Paths cited are relative to the reference repository.
+ *
+ * Conventions: every function returns 0 on success or a non-zero code (CUDA error
+ * code, or B2FHE_E_*); b2fhe_last_error_string() describes the last failure of the
+ * calling thread.  Nothing here ever falls back to a CPU path.
+ *
+ * Ciphertext formats are TFHEpp's raw arrays (default 128-bit parameters):
+ *   level 0: TLWE<lvl0param> = 637 x uint16_t (1274 B), level 1: TLWE<lvl1param> =
+ *   1025 x uint32_t (4100 B); batches are contiguous arrays of those.
+ * Key formats are TFHEpp's raw arrays:
+ *   bk  = BootstrappingKey<lvl01param>  [636][4][2][1024] uint32_t  (20,840,448 B)
+ *   ksk = KeySwitchingKey<lvl10param>   [1024][7][2][637] uint16_t  (18,264,064 B)
+ */
+#ifndef B2FHE_H
+#define B2FHE_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2FHE_E_NOT_INITIALIZED 10001
+#define B2FHE_E_BAD_ARGUMENT    10002
+#define B2FHE_E_NO_DEVICE       10003
+
+/* gate op codes; (casign, cbsign, offset) per src/bootstrap_gpu.cu:424-512,590-679 */
+enum b2fhe_op {
+    B2FHE_NAND = 0, B2FHE_OR, B2FHE_ORYN, B2FHE_ORNY, B2FHE_AND, B2FHE_ANDYN, B2FHE_ANDNY,
+    B2FHE_NOR, B2FHE_XOR, B2FHE_XNOR, B2FHE_MUX, B2FHE_NMUX, B2FHE_NOT, B2FHE_COPY, B2FHE_NUM_OPS
+};
+
+#define B2FHE_LVL0_WORDS 637
+#define B2FHE_LVL1_WORDS 1025
+#define B2FHE_BK_RAW_WORDS   ((size_t)636 * 4 * 2 * 1024)      /* uint32_t */
+#define B2FHE_KSK_RAW_WORDS  ((size_t)1024 * 7 * 2 * 637)      /* uint16_t */
+#define B2FHE_BK_NTT_BYTES   ((size_t)636 * 4 * 2 * 2 * 1024 * 4)   /* 41,680,896 */
+#define B2FHE_KSK_DEV_BYTES  ((size_t)1024 * 7 * 3 * 320 * 4)       /* 27,525,120 */
+
+typedef void* b2fhe_stream_t;   /* a cudaStream_t (0 = default stream) */
+
+/* ---- lifetime ----------------------------------------------------------------
+ * b2fhe_init: replaces Initialize(EvalKey) = InitializeNTThandlers +
+ * BootstrappingKeyToNTT + KeySwitchingKeyToDevice (src/cufhe_gates_gpu.cu:42-47,
+ * src/bootstrap_gpu.cu:97-138, src/keyswitch_gpu.cu:6-16).  Host pointers.  Converts
+ * the key on GPU 0 and replicates it to GPUs 1..ngpu-1 with peer copies. */
+int b2fhe_init(int ngpu, const uint32_t* bk_raw, const uint16_t* ksk_raw);
+/* one device only (one process per GPU): device = CUDA ordinal of this process */
+int b2fhe_init_device(int device, const uint32_t* bk_raw, const uint16_t* ksk_raw);
+/* keys already converted and resident on `device` (after an NCCL broadcast of the
+ * buffers produced on rank 0): adopts the pointers, does not copy or free them. */
+int b2fhe_adopt_keys(int device, const void* bk_ntt_dev, const void* ksk_dev);
+/* device pointers of the converted keys (to broadcast them), sizes B2FHE_*_BYTES */
+int b2fhe_key_pointers(int device, void** bk_ntt_dev, void** ksk_dev);
+/* replaces CleanUp / DeleteBootstrappingKeyNTT / DeleteKeySwitchingKey
+ * (src/bootstrap_gpu.cu:145-155, src/keyswitch_gpu.cu:18-24) */
+int b2fhe_cleanup(void);
+int b2fhe_num_devices(void);
+const char* b2fhe_last_error_string(void);
+
+/* ---- gates on DEVICE buffers (the g* / device-resident path,
+ * include/cufhe_gpu.cuh:229-252, launchers src/bootstrap_gpu.cu:834-1292) --------
+ * out/in0/in1/in2: contiguous batches of `count` ciphertexts of `level` on `device`.
+ * Two-input gates read in0,in1; MUX/NMUX read in0=inc, in1=in1, in2=in0 (reference
+ * argument order Mux(out, inc, in1, in0)); NOT/COPY read in0.  out may alias an input.
+ * Asynchronous on `stream`. */
+int b2fhe_gate_batch(int device, b2fhe_stream_t stream, int op, int level, void* out,
+                     const void* in0, const void* in1, const void* in2, size_t count);
+/* per-gate op codes (host array of `count` bytes); same buffers */
+int b2fhe_gate_batch_mixed(int device, b2fhe_stream_t stream, const uint8_t* ops_host, int level,
+                           void* out, const void* in0, const void* in1, const void* in2, size_t count);
+/* ---- gates on HOST buffers (the copying API path: CtxtCopyH2D + gate + CtxtCopyD2H,
+ * src/cufhe_gates_gpu.cu:148-158).  Copies inputs H2D, runs, copies the result D2H,
+ * all on `stream`; results valid after b2fhe_synchronize / stream sync. */
+int b2fhe_gate_batch_host(int device, b2fhe_stream_t stream, int op, const uint8_t* ops_host, int level,
+                          void* out_host, const void* in0_host, const void* in1_host,
+                          const void* in2_host, size_t count);
+int b2fhe_synchronize(void);   /* Synchronize(): all devices (include/cufhe_gpu.cuh:68-74) */
+
+/* ---- stages (next-tier entry points) ---------------------------------
+ * blind rotation + SampleExtract(0) of c = in (lvl0, device) -> lvl1 TLWE (device):
+ * GateBootstrappingTLWE2TLWE without key switch (gatebootstrapping_gpu.cuh:287-314) */
+int b2fhe_blind_rotate_batch(int device, b2fhe_stream_t stream, uint32_t* out_lvl1,
+                             const uint16_t* in_lvl0, uint32_t mu, size_t count);
+/* identity key switch lvl1 -> lvl0 (SampleExtractAndKeySwitch tail, src/keyswitch_gpu.cu:26-40) */
+int b2fhe_keyswitch_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0,
+                          const uint32_t* in_lvl1, size_t count);
+
+/* ---- NTT microbenchmark entry points (test/test_polynomial_mult_1024.cu:76-99) ------
+ * All device pointers.  ntt: in[count][1024] u32 -> out[count][2][1024] residues mod the
+ * two NTT primes (engine-internal order).  intt: inverse + centred CRT, mod 2^32.
+ * polymul: out = a (*) b negacyclic mod 2^32, exact when |sum a_i b_j| < 2^52 with a read
+ * as unsigned and b as SIGNED int32 (e.g. |b| <= 2^9). */
+int b2fhe_ntt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* in, size_t count);
+int b2fhe_intt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* in, size_t count);
+int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* a,
+                            const uint32_t* b, size_t count);
+
+/* tuning / introspection */
+int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
+uint64_t b2fhe_kernel_launches(void);             /* kernels launched by this library so far */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,127 @@
+"""CPU-side tests (no GPU): the oracle against the reference's own truths, the
+warp-level emulation of the CUDA arithmetic, host logic, and the C-ABI surface."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+N = 1024
+
+
+# --------------------------------------------------------------- the oracle ---
+def test_oracle_polymul_ntt_matches_schoolbook():
+    """The reference's only arithmetic KAT: NTT product == schoolbook negacyclic product
+    mod 2^32 (test/test_polynomial_mult_1024.cu:51-73,209-223; we demand diff 0)."""
+    rng = np.random.default_rng(0)
+    for t in range(6):
+        a = rng.integers(0, 2**32, N, dtype=np.uint64).astype(np.uint32)
+        hi = 256 if t < 3 else 2**18          # the reference's 8-bit and "TFHE-safe" 18-bit shapes
+        b = rng.integers(0, hi, N).astype(np.uint32)
+        assert np.array_equal(orc.polymul(a, b, True), orc.polymul(a, b, False))
+
+
+def test_oracle_polymul_known_answers():
+    a = np.zeros(N, np.uint32); b = np.zeros(N, np.uint32)
+    a[1] = 5; b[N - 1] = 3                      # 5X * 3X^1023 = 15 X^1024 = -15
+    out = orc.polymul(a, b, True)
+    assert out[0] == np.uint32(-15 & 0xFFFFFFFF) and not out[1:].any()
+    a[:] = 0; a[0] = 0xFFFFFFFF; b[:] = 0; b[0] = 2   # wrap mod 2^32
+    assert orc.polymul(a, b, False)[0] == 0xFFFFFFFE
+
+
+def test_oracle_cmux_ntt_matches_schoolbook(keys):
+    rng = np.random.default_rng(1)
+    acc = rng.integers(0, 2**32, (2, N), dtype=np.uint64).astype(np.uint32)
+    bk_i = keys.bk[: 8 * N]
+    for abar in (0, 1, 1023, 1024, 1500, 2047):
+        assert np.array_equal(orc.cmux_step(acc, abar, bk_i, True), orc.cmux_step(acc, abar, bk_i, False))
+    assert np.array_equal(orc.cmux_step(acc, 0, bk_i, False), acc)   # abar = 0 is a no-op
+
+
+@pytest.mark.parametrize("level", [0, 1])
+def test_oracle_gates_decrypt_to_truth_tables(keys, level):
+    """test/plain.h:10-69 through decryption, all 14 ops, all input combinations."""
+    for name in orc.OPS:
+        op = orc.OP[name]
+        combos = [(a, b, c) for a in (0, 1) for b in (0, 1) for c in (0, 1)]
+        x = [orc.encrypt(keys, [cb[k] for cb in combos], level, base_index=100 * op + 10 * k) for k in range(3)]
+        out = orc.gate_batch(keys, op, level, x[0], x[1], x[2])
+        dec = orc.decrypt(keys, out, level)
+        assert list(dec) == [orc.truth(op, *cb) for cb in combos], name
+
+
+def test_oracle_schoolbook_blind_rotate_equals_ntt(keys):
+    c = orc.encrypt(keys, [1], 0, base_index=5)[0]
+    c[40:] = 0     # keep the O(N^2) path short: abar = 0 steps are no-ops either way
+    assert np.array_equal(orc.blind_rotate_extract(keys, c, schoolbook=True),
+                          orc.blind_rotate_extract(keys, c, schoolbook=False))
+
+
+def test_golden_fixture(keys):
+    """Committed fixture (tests/golden/make_golden.py): digests of oracle outputs on the
+    seeded key set -- guards the oracle and the key generator against drift."""
+    import hashlib, json
+    with open(os.path.join(ROOT, "tests", "golden", "golden.json")) as f:
+        G = json.load(f)
+    assert hashlib.sha256(keys.bk.tobytes()).hexdigest() == G["bk_sha256"]
+    assert hashlib.sha256(keys.ksk.tobytes()).hexdigest() == G["ksk_sha256"]
+    for level in (0, 1):
+        x0 = orc.encrypt(keys, [0, 1, 0, 1], level, base_index=1)
+        x1 = orc.encrypt(keys, [0, 0, 1, 1], level, base_index=101)
+        out = orc.gate_batch(keys, orc.OP["NAND"], level, x0, x1)
+        assert hashlib.sha256(out.tobytes()).hexdigest() == G[f"nand_lvl{level}_sha256"]
+        assert out[0, :4].tolist() == G[f"nand_lvl{level}_first_words"]
+
+
+# ------------------------------------- CUDA arithmetic, emulated on the CPU ---
+def test_warp_emulation_of_cuda_ntt_and_cmux(tmp_path):
+    """Compiles the SAME host+device headers the kernels use and runs the warp-level
+    dataflow (radix-32 passes, swizzled exchange, Montgomery MAC, CRT) lane by lane."""
+    orc.build()
+    exe = str(tmp_path / "emul_ntt")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "emul", "emul_ntt.cpp"),
+                           "-L" + os.path.join(ROOT, "oracle"), "-lorc", "-Wl,-rpath," + os.path.join(ROOT, "oracle"),
+                           "-fopenmp"])
+    out = subprocess.check_output([exe, "6"]).decode()
+    assert "polymul mismatches: 0 / 6" in out and "cmux mismatches: 0 / 6" in out
+
+
+# -------------------------------------------------------------- host logic ---
+def test_partition_covers_batch():
+    from cufhe_b200.api import partition
+    for count in (0, 1, 7, 16384, 2**18 + 3):
+        for world in (1, 2, 3, 8):
+            spans = [partition(count, world, r) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == count
+            assert all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
+            sizes = [e - b for b, e in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_abi_exports_every_declared_symbol():
+    """The shared library loads and exports exactly what include/b2fhe.h declares."""
+    from cufhe_b200 import _lib
+    _lib.build()
+    hdr = open(os.path.join(ROOT, "include", "b2fhe.h")).read()
+    declared = set(re.findall(r"\b(b2fhe_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(_lib.SYMBOLS)
+    L = C.CDLL(_lib.LIB_PATH)
+    for s in declared:
+        assert hasattr(L, s), s
+
+
+def test_product_path_never_touches_oracle():
+    """Nothing under cufhe_b200/ or include/ imports, links or calls the oracle."""
+    for top in ("cufhe_b200", "include"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, top)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".inl", ".h", ".hpp")):
+                    src = open(os.path.join(dirpath, f)).read()
+                    for needle in ("import orc", "from oracle", "liborc", "orc_", "cufhe_oracle"):
+                        assert needle not in src, (f, needle)

@@ -1,0 +1,234 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the
+same seeded inputs -- bit-exact, as the hot path is integer-only.
+
+Mirrors the reference's test strategy (test/test_gate_gpu.cc, test_util.h,
+test_polynomial_mult_1024.cu, test_intensive.cc) but compares ciphertext BYTES, not
+just decryptions.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import orc
+
+pytestmark = pytest.mark.gpu
+
+N = 1024
+
+
+def dev_u32(a):
+    return torch.from_numpy(np.ascontiguousarray(a).view(np.int32)).cuda()
+
+
+def to_np(t, dtype):
+    return t.cpu().numpy().view(dtype)
+
+
+def run_gate(cf, op, level, ins, count):
+    st = cf.Stream(0).Create()
+    cts = [cf.Ctxt(count, level).set(x) if x is not None else None for x in ins]
+    out = cf.Ctxt(count, level)
+    for c in cts:
+        if c is not None:
+            cf.CtxtCopyH2D(c, st)
+    cf.api._gate_device(op, out, cts[0], cts[1], cts[2], st)
+    cf.CtxtCopyD2H(out, st)
+    cf.Synchronize()
+    return out.tlwehost.copy()
+
+
+# ---------------------------------------------------------------- NTT layer ---
+def test_ntt_roundtrip_and_polymul(engine):
+    cf = engine
+    L = cf._lib.lib()
+    rng = np.random.default_rng(1)
+    cnt = 300
+    a = rng.integers(0, 2**32, size=(cnt, N), dtype=np.uint64).astype(np.uint32)
+    da = dev_u32(a)
+    dn = torch.empty((cnt, 2, N), dtype=torch.int32, device="cuda")
+    db = torch.empty((cnt, N), dtype=torch.int32, device="cuda")
+    cf._lib.check(L.b2fhe_ntt1024_batch(0, None, dn.data_ptr(), da.data_ptr(), cnt))
+    cf._lib.check(L.b2fhe_intt1024_batch(0, None, db.data_ptr(), dn.data_ptr(), cnt))
+    torch.cuda.synchronize()
+    # INTT(NTT(x)) is the centred representative of x mod P, P ~ 2^54 > 2^32: exact
+    assert np.array_equal(to_np(db, np.uint32), a)
+    res = to_np(dn, np.uint32)
+    assert res[:, 0].max() < 134215681 and res[:, 1].max() < 134203393
+
+    # negacyclic product against the reference's schoolbook truth
+    # (test/test_polynomial_mult_1024.cu:51-73), b = signed gadget digits and 9-bit values
+    for lo, hi in ((-128, 128), (-512, 512)):
+        b = rng.integers(lo, hi, size=(cnt, N)).astype(np.int32).view(np.uint32)
+        dbb = dev_u32(b)
+        dout = torch.empty((cnt, N), dtype=torch.int32, device="cuda")
+        cf._lib.check(L.b2fhe_polymul1024_batch(0, None, dout.data_ptr(), da.data_ptr(), dbb.data_ptr(), cnt))
+        torch.cuda.synchronize()
+        got = to_np(dout, np.uint32)
+        for i in range(0, cnt, 7):
+            assert np.array_equal(got[i], orc.polymul(a[i], b[i], schoolbook=True)), f"poly {i}"
+
+
+def test_polymul_edge_cases(engine):
+    cf = engine
+    L = cf._lib.lib()
+    a = np.zeros((4, N), np.uint32)
+    b = np.zeros((4, N), np.uint32)
+    a[0, :] = 0xFFFFFFFF; b[0, :] = np.int32(-128).astype(np.uint32)     # extreme magnitudes
+    a[1, 0] = 1; b[1, N - 1] = 1                                          # X^1023
+    a[2, N - 1] = 0x80000000; b[2, N - 1] = 127                           # wrap with sign flip
+    a[3, :] = np.arange(N, dtype=np.uint32) * 2654435761 & 0xFFFFFFFF; b[3, 5] = np.uint32(0xFFFFFFFF)  # * -X^5
+    da, db = dev_u32(a), dev_u32(b)
+    dout = torch.empty((4, N), dtype=torch.int32, device="cuda")
+    cf._lib.check(L.b2fhe_polymul1024_batch(0, None, dout.data_ptr(), da.data_ptr(), db.data_ptr(), 4))
+    cf._lib.check(L.b2fhe_polymul1024_batch(0, None, dout.data_ptr(), da.data_ptr(), db.data_ptr(), 0))  # empty batch
+    torch.cuda.synchronize()
+    got = to_np(dout, np.uint32)
+    for i in range(4):
+        assert np.array_equal(got[i], orc.polymul(a[i], b[i], schoolbook=True)), i
+
+
+# ------------------------------------------------------------------ stages ---
+def test_blind_rotate_and_keyswitch_stages(engine, keys):
+    cf = engine
+    L = cf._lib.lib()
+    cnt = 13          # ragged: not a multiple of any gates-per-CTA choice
+    bits = np.arange(cnt) & 1
+    c0 = orc.encrypt(keys, bits, 0)
+    c0[3, :] = 0                      # all-zero ciphertext: every abar = 0, bbar = 2N
+    c0[4, :636] = 0xFFFF              # maximal mask values
+    d0 = torch.from_numpy(c0.view(np.int16)).cuda()
+    d1 = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
+    for g in (0, 1, 2, 4, 6, 8):
+        cf._lib.check(L.b2fhe_set_gates_per_cta(g))
+        d1.zero_()
+        cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, d1.data_ptr(), d0.data_ptr(), 1 << 29, cnt))
+        torch.cuda.synchronize()
+        got = to_np(d1, np.uint32)
+        for i in range(cnt):
+            ref = orc.blind_rotate_extract(keys, c0[i])
+            assert np.array_equal(got[i], ref), f"gates/cta {g}, item {i}"
+    cf._lib.check(L.b2fhe_set_gates_per_cta(0))
+    # key switch of those lvl1 outputs (+ an extreme input)
+    x = got.copy()
+    x[5, :] = 0xFFFFFFFF
+    x[6, :] = 0
+    dx = dev_u32(x)
+    dks = torch.empty((cnt, 637), dtype=torch.int16, device="cuda")
+    cf._lib.check(L.b2fhe_keyswitch_batch(0, None, dks.data_ptr(), dx.data_ptr(), cnt))
+    torch.cuda.synchronize()
+    gk = to_np(dks, np.uint16)
+    for i in range(cnt):
+        assert np.array_equal(gk[i], orc.keyswitch(keys, x[i])), i
+
+
+# ------------------------------------------------------------------- gates ---
+@pytest.mark.parametrize("level", [0, 1])
+def test_all_gates_bit_exact_and_decrypt(engine, keys, level):
+    """13 gates + NMux (test/test_gate_gpu.cc:36-91, truth tables test/plain.h:10-69)."""
+    cf = engine
+    cnt = 12
+    rng = np.random.default_rng(100 + level)
+    for op_name in orc.OPS:
+        op = orc.OP[op_name]
+        b0, b1, b2 = (rng.integers(0, 2, cnt) for _ in range(3))
+        x0 = orc.encrypt(keys, b0, level, base_index=1000 * op)
+        x1 = orc.encrypt(keys, b1, level, base_index=1000 * op + 300)
+        x2 = orc.encrypt(keys, b2, level, base_index=1000 * op + 600)
+        unary = op_name in ("NOT", "COPY")
+        ternary = op_name in ("MUX", "NMUX")
+        ins = [x0, None if unary else x1, x2 if ternary else None]
+        got = run_gate(cf, op_name, level, ins, cnt)
+        ref = orc.gate_batch(keys, op, level, x0, None if unary else x1, x2 if ternary else None)
+        assert np.array_equal(got, ref), f"{op_name} level {level}: ciphertext bytes differ"
+        dec = orc.decrypt(keys, got, level)
+        truth = [orc.truth(op, b0[i], b1[i], b2[i]) for i in range(cnt)]
+        assert list(dec) == truth, f"{op_name} level {level}: wrong plaintext"
+
+
+@pytest.mark.parametrize("level", [0, 1])
+def test_mixed_batch(engine, keys, level):
+    """BASELINE config 4 shape: op[i] = i mod 14 over one batch."""
+    cf = engine
+    cnt = 45
+    rng = np.random.default_rng(7 + level)
+    ops = (np.arange(cnt) % 14).astype(np.uint8)
+    b = [rng.integers(0, 2, cnt) for _ in range(3)]
+    x = [orc.encrypt(keys, b[k], level, base_index=50000 + 1000 * k) for k in range(3)]
+    st = cf.Stream(0).Create()
+    cts = [cf.Ctxt(cnt, level).set(v) for v in x]
+    out = cf.Ctxt(cnt, level)
+    for c in cts:
+        cf.CtxtCopyH2D(c, st)
+    cf.gGateMixed(ops, out, cts[0], cts[1], cts[2], st)
+    cf.CtxtCopyD2H(out, st)
+    cf.Synchronize()
+    ref = orc.gate_batch(keys, 0, level, x[0], x[1], x[2], ops=ops)
+    assert np.array_equal(out.tlwehost, ref)
+    dec = orc.decrypt(keys, out.tlwehost, level)
+    assert list(dec) == [orc.truth(ops[i], b[0][i], b[1][i], b[2][i]) for i in range(cnt)]
+
+
+def test_aliasing_and_stream_chain(engine, keys):
+    """out may alias an input; gates on one stream run in issue order
+    (test/test_intensive.cc:21-54: 20 back-to-back NANDs per stream)."""
+    cf = engine
+    cnt = 6
+    st = cf.Stream(0).Create()
+    a = cf.Ctxt(cnt, 0).set(orc.encrypt(keys, [1] * cnt, 0, base_index=9000))
+    b = cf.Ctxt(cnt, 0).set(orc.encrypt(keys, [0, 1] * (cnt // 2), 0, base_index=9100))
+    cf.CtxtCopyH2D(a, st)
+    cf.CtxtCopyH2D(b, st)
+    ref = a.tlwehost.copy()
+    for _ in range(5):
+        cf.gNand(a, a, b, st)                  # a = NAND(a, b) in place
+        ref = orc.gate_batch(keys, orc.OP["NAND"], 0, ref, b.tlwehost)
+    cf.CtxtCopyD2H(a, st)
+    while not cf.StreamQuery(st):
+        pass
+    assert np.array_equal(a.tlwehost, ref)
+
+
+def test_host_buffer_entry_point(engine, keys):
+    """b2fhe_gate_batch_host = CtxtCopyH2D + gate + CtxtCopyD2H (src/cufhe_gates_gpu.cu:148-158)."""
+    cf = engine
+    L = cf._lib.lib()
+    cnt = 9
+    x0 = orc.encrypt(keys, [0, 1, 1] * 3, 0, base_index=777)
+    x1 = orc.encrypt(keys, [1, 1, 0] * 3, 0, base_index=888)
+    out = np.zeros_like(x0)
+    cf._lib.check(L.b2fhe_gate_batch_host(0, None, orc.OP["XOR"], None, 0, out.ctypes.data, x0.ctypes.data,
+                                          x1.ctypes.data, None, cnt))
+    cf.Synchronize()
+    assert np.array_equal(out, orc.gate_batch(keys, orc.OP["XOR"], 0, x0, x1))
+
+
+def test_error_paths(engine):
+    cf = engine
+    L = cf._lib.lib()
+    assert L.b2fhe_gate_batch(0, None, 99, 0, C.c_void_p(8), C.c_void_p(8), None, None, 1) != 0
+    assert b"b2fhe" in L.b2fhe_last_error_string()
+    assert L.b2fhe_gate_batch(0, None, 0, 0, C.c_void_p(8), C.c_void_p(8), None, None, 1) != 0   # NAND without in1
+    assert L.b2fhe_gate_batch(5, None, 0, 0, None, None, None, None, 1) != 0                      # device not initialised
+
+
+# ------------------------------------------------ full-size property tests ---
+def test_full_batch_16384_nand(engine, keys):
+    """BASELINE config 3: 16384 independent NANDs.  100 % decryption agreement over
+    the whole batch, byte parity with the oracle on a strided sample, and
+    batch-position independence (same inputs at two positions -> same bytes)."""
+    cf = engine
+    cnt = 16384
+    rng = np.random.default_rng(3)
+    b0, b1 = rng.integers(0, 2, cnt), rng.integers(0, 2, cnt)
+    x0 = orc.encrypt(keys, b0, 0, base_index=200000)
+    x1 = orc.encrypt(keys, b1, 0, base_index=300000)
+    x0[-1], x1[-1] = x0[0], x1[0]
+    b0[-1], b1[-1] = b0[0], b1[0]
+    got = run_gate(cf, "NAND", 0, [x0, x1, None], cnt)
+    assert np.array_equal(orc.decrypt(keys, got, 0), 1 - b0 * b1)
+    assert np.array_equal(got[-1], got[0])
+    idx = np.arange(0, cnt, 431)
+    ref = orc.gate_batch(keys, orc.OP["NAND"], 0, x0[idx], x1[idx])
+    assert np.array_equal(got[idx], ref)
