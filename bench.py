@@ -1,0 +1,269 @@
+#!/usr/bin/env python
+"""bench.py -- batched NAND gate bootstraps/s (BASELINE.json metric) on N B200s.
+
+A step = one pass of the hot path over one batch: 16384 independent lvl0 NAND gate
+bootstraps per GPU (BASELINE config 3, "test_perf shape"), synthetic
+random ciphertexts and keys (timing does not depend on the values; correctness is
+what tests/ and smoke() check).
+
+  value  gates/s with inputs resident in HBM (b2fhe_gate_batch on device buffers)
+  e2e    gates/s through the host-buffer entry point b2fhe_gate_batch_host
+         (pinned host buffers, H2D + gate + D2H inside the timed region)
+  roofline / int_pipe / cpu_baseline: see DESIGN.md "Measurement".
+
+--impl reference times the CPU implementation of the same path on the host cores
+(oracle/_ref TFHEpp build when present, else the oracle port).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GATES_PER_GPU = 16384
+METRIC = "gate_bootstraps_per_sec_nand_batched"
+UNIT = "gates/s"
+# algorithmic figures per NAND bootstrap
+KEY_BYTES_PER_GATE = 41_680_896            # NTT-domain bootstrapping key touched per gate
+# integer multiply-pipe slots per gate of OUR formulation (DESIGN.md "integer roofline")
+IMAD_SLOTS_PER_GATE = 636 * 2 * (6 * 5120 * 4 + 2 * 1024 * 4 + 8192 * 5 + 1024 * 5)
+
+
+def clocks_sampler(stop, out):
+    q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    dev = os.environ.get("LOCAL_RANK", "0")
+    while not stop.is_set():
+        try:
+            r = subprocess.run(["nvidia-smi", "-i", dev, f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                               capture_output=True, text=True, timeout=5).stdout.strip().split(",")
+            out.append([x.strip() for x in r])
+        except Exception:
+            pass
+        stop.wait(0.2)
+
+
+def summarize_clocks(samples):
+    sm = sorted(int(s[0]) for s in samples if len(s) >= 6 and s[0].isdigit())
+    if not sm:
+        return {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+    names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    reasons = [n for i, n in enumerate(names) if any(len(s) >= 6 and s[2 + i].lower().startswith("active") for s in samples)]
+    mx = max(int(s[1]) for s in samples if len(s) >= 6 and s[1].isdigit())
+    return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": mx, "reasons": reasons}
+
+
+def cpu_baseline(sample_gates, threads=0):
+    """CPU implementation of the same path, timed on the host cores (bounded sample)."""
+    import numpy as np
+    ref = os.path.join(ROOT, "oracle", "_ref", "libtfhepp_ref.so")
+    cores = threads or os.cpu_count()
+    if os.path.exists(ref):
+        L = C.CDLL(ref)
+        L.ref_bench_nand.restype = C.c_double
+        L.ref_bench_nand.argtypes = [C.c_int, C.c_int]
+        secs = L.ref_bench_nand(sample_gates, cores)
+        return {"value": sample_gates / secs, "unit": UNIT, "cores": cores, "kind": "reference",
+                "sample": f"{sample_gates} lvl0 HomNAND (TFHEpp, spqlios FFT) over {cores} threads"}
+    from oracle import orc
+    keys = orc.Keys(20261104)
+    bits = np.arange(sample_gates) & 1
+    x0 = orc.encrypt(keys, bits, 0, base_index=1)
+    x1 = orc.encrypt(keys, 1 - bits, 0, base_index=100001)
+    orc.gate_batch(keys, orc.OP["NAND"], 0, x0[:cores], x1[:cores], threads=cores)   # warm-up (key NTT)
+    t = time.perf_counter()
+    orc.gate_batch(keys, orc.OP["NAND"], 0, x0, x1, threads=cores)
+    secs = time.perf_counter() - t
+    return {"value": sample_gates / secs, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{sample_gates} lvl0 NAND gate bootstraps, exact-integer oracle (OpenMP, {cores} threads)"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample = max(8, 4 * (os.cpu_count() or 1))
+    vals = []
+    for i in range(args.warmup + args.steps):
+        b = cpu_baseline(sample)
+        if i >= args.warmup:
+            vals.append(b)
+    v = sum(x["value"] for x in vals) / len(vals)
+    b = vals[-1]
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": sample / v * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": f"batched independent NAND gate bootstraps (lvl0 I/O, TFHEpp 128-bit params); "
+                                   f"CPU arm: bounded sample of {sample} gates per step"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": b["cores"], "kind": b["kind"], "sample": b["sample"]},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_product(args):
+    import numpy as np
+    import torch
+    import cufhe_b200 as cf
+    L = cf._lib.lib()      # raises if the CUDA library is missing: no fallback
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+
+    rng = np.random.default_rng(1234)
+    bk = ksk = None
+    if rank == 0 or world == 1:
+        bk = rng.integers(0, 2**32, cf.api.BK_RAW_WORDS, dtype=np.uint64).astype(np.uint32)
+        ksk = rng.integers(0, 2**16, cf.api.KSK_RAW_WORDS, dtype=np.uint64).astype(np.uint16)
+    if world > 1:
+        # rank 0 converts the keys once; every other rank receives them by NCCL broadcast
+        keep = cf.InitializeBroadcast(bk, ksk, device=local, src=0)  # noqa: F841 (owns adopted key memory)
+    else:
+        cf.SetGPUNum(1)
+        cf.Initialize(bk, ksk, device=local)
+
+    cnt = args.gates
+    rng = np.random.default_rng(99 + rank)
+    shape = (cnt, cf.api.LVL0_WORDS)
+    h0 = torch.from_numpy(rng.integers(0, 2**16, shape, dtype=np.uint64).astype(np.uint16).view(np.int16)).pin_memory()
+    h1 = torch.from_numpy(rng.integers(0, 2**16, shape, dtype=np.uint64).astype(np.uint16).view(np.int16)).pin_memory()
+    hout = torch.empty(shape, dtype=torch.int16).pin_memory()
+    d0, d1 = h0.to(dev), h1.to(dev)
+    dout = torch.empty_like(d0)
+    e1 = torch.empty((cnt, cf.api.LVL1_WORDS), dtype=torch.int32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+    st = torch.cuda.current_stream(dev)
+    sp = st.cuda_stream
+    NAND = cf.OP["NAND"]
+
+    def step_dev():
+        cf._lib.check(L.b2fhe_gate_batch(local, sp, NAND, 0, dout.data_ptr(), d0.data_ptr(), d1.data_ptr(), None, cnt))
+
+    def step_host():
+        cf._lib.check(L.b2fhe_gate_batch_host(local, sp, NAND, None, 0, hout.data_ptr(), h0.data_ptr(), h1.data_ptr(), None, cnt))
+
+    def step_br():
+        cf._lib.check(L.b2fhe_blind_rotate_batch(local, sp, e1.data_ptr(), d0.data_ptr(), 1 << 29, cnt))
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(fn, steps, warmup):
+        """device time of exactly `steps` steps (CUDA events on the launching stream; L2
+        flushed between iterations, flush outside the timed intervals); max over ranks."""
+        for _ in range(warmup):
+            fn()
+        barrier()
+        total = 0.0
+        for _ in range(steps):
+            flush.fill_(1)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(st)
+            fn()
+            b.record(st)
+            b.synchronize()
+            total += a.elapsed_time(b)
+        barrier()
+        if dist is not None:
+            t = torch.tensor([total], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            total = float(t.item())
+        return total
+
+    stop, samples = threading.Event(), []
+    th = threading.Thread(target=clocks_sampler, args=(stop, samples), daemon=True)
+    th.start()
+    launches0 = L.b2fhe_kernel_launches()
+    ms = timed(step_dev, args.steps, args.warmup)
+    launches = (L.b2fhe_kernel_launches() - launches0) * args.steps // (args.steps + args.warmup)
+    ms_e2e = timed(step_host, args.steps, max(1, args.warmup // 2))
+    ms_br = timed(step_br, args.steps, 1)
+    stop.set()
+    th.join()
+
+    total_gates = cnt * world
+    value = total_gates * args.steps / (ms * 1e-3)
+    e2e = total_gates * args.steps / (ms_e2e * 1e-3)
+    line = None
+    if rank == 0:
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        br_s = ms_br * 1e-3 / args.steps
+        achieved = KEY_BYTES_PER_GATE * cnt / br_s * 1e-9
+        g0, g1 = C.c_double(), C.c_double()
+        cf._lib.check(L.b2fhe_int_peak(local, 0, C.byref(g0)))
+        cf._lib.check(L.b2fhe_int_peak(local, 1, C.byref(g1)))
+        slots = IMAD_SLOTS_PER_GATE * cnt / br_s * 1e-9
+        cb = cpu_baseline(max(8, 4 * (os.cpu_count() or 1))) if world == 1 else None
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u32", "data": "synthetic",
+            "config": {"workload": f"{cnt} independent NAND gate bootstraps per GPU (lvl0 in/out, TFHEpp 128-bit "
+                                   "params n=636 N=1024 l=2 Bg=2^8 t=7), BASELINE config 3",
+                       "gates_per_gpu": cnt, "partition": "contiguous slices of independent gates, keys replicated "
+                                                          "by one NCCL broadcast at Initialize, no steady-state collective",
+                       "l2": "256 MiB flush write between timed iterations"},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 2 * cnt * 1274 * world,
+                    "d2h_bytes_per_step": cnt * 1274 * world},
+            "gpu_launches": int(launches),
+            "clocks": summarize_clocks(samples),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved / hbm_peak, "traffic": None,
+                         "kernel": "k_blind_rotate", "kernel_ms": br_s * 1e3,
+                         "note": "algorithmic key bytes (41.68 MB x gates per launch) / kernel time, against the "
+                                 "MEASURED HBM copy peak; the batch-major kernel serves each key row to all gates of "
+                                 "a CTA from L1/L2, so this exceeds 1 by design -- the binding resource is the "
+                                 "integer multiply pipe, see int_pipe"},
+            "int_pipe": {"achieved_gslots_per_s": slots, "peak_gslots_per_s": g0.value, "frac": slots / g0.value,
+                         "butterfly_peak_g_per_s": g1.value,
+                         "note": "fma-pipe issue slots (IMAD=1, IMAD.HI/IMAD.WIDE=2) of the algorithm per second vs the "
+                                 "IMAD rate measured on this GPU by b2fhe_int_peak"},
+        }
+        if cb is not None:
+            line["cpu_baseline"] = cb
+    cf.CleanUp()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b2fhe", choices=["b2fhe", "reference"])
+    ap.add_argument("--gates", type=int, default=GATES_PER_GPU, help="gates per GPU per step")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_product(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -72,7 +72,7 @@ int setup_device(int device)
     CK(cudaMemcpyToSymbol(c_fw1, T.fw1, sizeof T.fw1));
     CK(cudaMemcpyToSymbol(c_iv1, T.iv1, sizeof T.iv1));
     CK(cudaMemcpyToSymbol(c_r2, T.r2, sizeof T.r2));
-    CK(cudaMemcpyToSymbol(c_crt_p0inv, &T.crt_p0inv_mont, sizeof(uint32_t)));
+    CK(cudaMemcpyToSymbol(c_crt_p0inv, &T.crt_p0inv, sizeof(Tw)));
     static LaneTables L;
     memcpy(L.fw2, T.fw2, sizeof L.fw2);
     memcpy(L.iv2, T.iv2, sizeof L.iv2);

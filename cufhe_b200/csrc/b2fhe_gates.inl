@@ -351,4 +351,36 @@ int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, co
     return 0;
 }
 
+int b2fhe_int_peak(int device, int mode, double* giga_ops_per_s)
+{
+    // measured integer-pipe ceiling: mode 0 -> 1e9 IMAD lane-ops/s, mode 1 -> 1e9 butterflies/s
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE(giga_ops_per_s && (mode == 0 || mode == 1), B2FHE_E_BAD_ARGUMENT);
+    uint32_t* d;
+    CK(cudaMalloc(&d, 16));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    const int iters = 4096, grid = c->sm_count * 8;
+    double best = 0;
+    for (int rep = 0; rep < 4; rep++) {
+        CK(cudaEventRecord(e0));
+        k_int_peak<<<grid, 256>>>(d, iters, mode, 12345u + rep);
+        LAUNCHED();
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        const double ops = (double)grid * 256 * iters * (mode == 0 ? 16 : 8);
+        const double g = ops / (ms * 1e-3) * 1e-9;
+        if (rep > 0 && g > best) best = g;
+    }
+    *giga_ops_per_s = best;
+    CK(cudaEventDestroy(e0));
+    CK(cudaEventDestroy(e1));
+    CK(cudaFree(d));
+    return 0;
+}
+
 }  // extern "C"

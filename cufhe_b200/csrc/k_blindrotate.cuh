@@ -10,7 +10,8 @@
 // warps, one per NTT prime.  Per step each warp
 //   1. rebuilds the four gadget-digit polynomials from the accumulator (shared memory),
 //   2. forward-transforms each (registers + one warp transpose),
-//   3. multiply-accumulates with the key row into 2 x 32 lazy residues (registers),
+//   3. multiply-accumulates with the key row into 2 x 32 lazy residues (registers;
+//      Montgomery form, the key carries the 2^32 factor),
 //   4. inverse-transforms both outputs,
 // then the two warps swap one residue polynomial through shared memory, each finishes
 // the centred CRT for one output polynomial and updates the accumulator.  The only
@@ -56,9 +57,10 @@ __device__ __forceinline__ void br_gate_loop(const uint32_t* __restrict__ bk, ui
     const uint4* bk4 = reinterpret_cast<const uint4*>(bk) + lane;
     for (int i = 0; i < kLwe; i++) {
         const uint32_t abar = s_abar[i];
-        int32_t sums[2][32];
+        // lazy residues: 4p + four Montgomery products in (-p, p)  ->  (0, 8p)
+        uint32_t sums[2][32];
 #pragma unroll
-        for (int k = 0; k < 32; k++) sums[0][k] = sums[1][k] = 0;
+        for (int k = 0; k < 32; k++) sums[0][k] = sums[1][k] = 4u * Prime<Q>::p;
 
         const uint32_t am = abar & (kN - 1);
         const bool flip = (abar >> kNbit) != 0;
@@ -68,7 +70,7 @@ __device__ __forceinline__ void br_gate_loop(const uint32_t* __restrict__ bk, ui
 #pragma unroll 1
         for (int j = 0; j < 2; j++) {
             const uint32_t* aj = acc + j * kN;
-            int32_t x[32];
+            uint32_t x[32];
             uint32_t dlo[8];
 #pragma unroll
             for (int k = 0; k < 32; k++) {
@@ -76,7 +78,7 @@ __device__ __forceinline__ void br_gate_loop(const uint32_t* __restrict__ bk, ui
                 const bool neg = (k < kth) != flip;
                 rot = neg ? 0u - rot : rot;
                 const uint32_t r = rot - aj[lane + 32 * k] + kDecompAdd;
-                x[k] = (int32_t)(r >> 24) - 128;
+                x[k] = (r >> 24) + (Prime<Q>::p - 128u);           // digit + p in [0, 2p)
                 const uint32_t d1 = (r >> 16) & 0xFFu;
                 if ((k & 3) == 0) dlo[k >> 2] = d1; else dlo[k >> 2] |= d1 << (8 * (k & 3));
             }
@@ -84,7 +86,7 @@ __device__ __forceinline__ void br_gate_loop(const uint32_t* __restrict__ bk, ui
             for (int d = 0; d < 2; d++) {
                 if (d == 1) {
 #pragma unroll
-                    for (int k = 0; k < 32; k++) x[k] = (int32_t)((dlo[k >> 2] >> (8 * (k & 3))) & 0xFFu) - 128;
+                    for (int k = 0; k < 32; k++) x[k] = ((dlo[k >> 2] >> (8 * (k & 3))) & 0xFFu) + (Prime<Q>::p - 128u);
                 }
                 fwd_dev<Q>(x, xbuf, s_tab, lane);
                 // key row (i, 2j+d), my prime: [out][v][lane] uint4
@@ -94,10 +96,10 @@ __device__ __forceinline__ void br_gate_loop(const uint32_t* __restrict__ bk, ui
 #pragma unroll
                     for (int v = 0; v < 8; v++) {
                         const uint4 b = __ldg(row + o * (kN / 4) + v * 32);
-                        sums[o][4 * v + 0] += montmul<Q>(x[4 * v + 0], b.x);
-                        sums[o][4 * v + 1] += montmul<Q>(x[4 * v + 1], b.y);
-                        sums[o][4 * v + 2] += montmul<Q>(x[4 * v + 2], b.z);
-                        sums[o][4 * v + 3] += montmul<Q>(x[4 * v + 3], b.w);
+                        sums[o][4 * v + 0] += (uint32_t)umontmul<Q>(x[4 * v + 0], b.x);
+                        sums[o][4 * v + 1] += (uint32_t)umontmul<Q>(x[4 * v + 1], b.y);
+                        sums[o][4 * v + 2] += (uint32_t)umontmul<Q>(x[4 * v + 2], b.z);
+                        sums[o][4 * v + 3] += (uint32_t)umontmul<Q>(x[4 * v + 3], b.w);
                     }
                 }
             }
@@ -106,15 +108,15 @@ __device__ __forceinline__ void br_gate_loop(const uint32_t* __restrict__ bk, ui
         inv_dev<Q>(sums[mine], xbuf, s_tab, lane);
         __syncwarp();
 #pragma unroll
-        for (int k = 0; k < 32; k++) xbuf[k * 32 + lane] = (uint32_t)sums[other][k];
+        for (int k = 0; k < 32; k++) xbuf[k * 32 + lane] = sums[other][k];
         named_bar_sync(barid, 64);
         uint32_t* am_ = acc + mine * kN + lane;
 #pragma unroll
         for (int k = 0; k < 32; k++) {
-            const int32_t t = (int32_t)xbuf_other[k * 32 + lane];
-            const int32_t s0 = Q == 0 ? sums[mine][k] : t;
-            const int32_t s1 = Q == 0 ? t : sums[mine][k];
-            am_[32 * k] += crt_lift32(s0, s1, c_crt_p0inv);
+            const uint32_t t = xbuf_other[k * 32 + lane];
+            const uint32_t s0 = Q == 0 ? sums[mine][k] : t;
+            const uint32_t s1 = Q == 0 ? t : sums[mine][k];
+            am_[32 * k] += crt_lift32(s0, s1, c_crt_p0inv.w, c_crt_p0inv.ws);
         }
         named_bar_sync(barid, 64);
     }

@@ -65,6 +65,37 @@ B2_HD int32_t montmul(int32_t a, uint32_t bt)
     return (int32_t)(prod >> 32) - t;
 }
 
+// unsigned variant: 0 <= a < 2^32 (lazy residue), 0 <= bt < p; result in (-p, p).
+// Used for the key multiply-accumulate, where only ONE constant per key coefficient
+// is affordable (a Shoup companion would double the 41.7 MB key).
+template <int Q>
+B2_HD int32_t umontmul(uint32_t a, uint32_t bt)
+{
+    const uint64_t prod = (uint64_t)a * (uint64_t)bt;
+    const uint32_t m = (uint32_t)prod * Prime<Q>::pinv;
+#ifdef __CUDA_ARCH__
+    const uint32_t t = __umulhi(m, Prime<Q>::p);
+#else
+    const uint32_t t = (uint32_t)(((uint64_t)m * (uint64_t)Prime<Q>::p) >> 32);
+#endif
+    return (int32_t)((uint32_t)(prod >> 32) - t);
+}
+
+// Shoup multiplication by a constant w < p with companion ws = floor(w * 2^32 / p):
+// v * w mod p in [0, 2p) for ANY 32-bit v.  One IMAD.HI + two IMAD on sm_100a, which
+// measures 1.7x faster than the Montgomery form (profiles/r1_ubench_butterfly_mix.log)
+// because IMAD.WIDE and IMAD.HI are both half-rate.
+template <int Q>
+B2_HD uint32_t shoup_mul(uint32_t v, uint32_t w, uint32_t ws)
+{
+#ifdef __CUDA_ARCH__
+    const uint32_t q = __umulhi(v, ws);
+#else
+    const uint32_t q = (uint32_t)(((uint64_t)v * (uint64_t)ws) >> 32);
+#endif
+    return v * w - q * Prime<Q>::p;
+}
+
 // canonical representative in [0, p) of a value in (-p, p)
 template <int Q>
 B2_HD uint32_t canon(int32_t a)
@@ -81,6 +112,7 @@ inline uint32_t h_powmod(uint32_t b, uint64_t e, uint32_t p)
     return r;
 }
 inline uint32_t h_to_mont(uint32_t a, uint32_t p) { return (uint32_t)((((uint64_t)a) << 32) % p); }
+inline uint32_t h_shoup(uint32_t w, uint32_t p) { return (uint32_t)((((uint64_t)w) << 32) / p); }
 // primitive 2N-th root of unity (smallest generator candidate g with (g^((p-1)/2N))^N == -1)
 inline uint32_t h_psi(uint32_t p)
 {

@@ -20,25 +20,28 @@
 //     pass 1 in layout B (strides 1..16;   twiddles warp-uniform)
 //     pass 2 in layout A (strides 32..512; 31 per-lane twiddles) + 32 per-lane scales
 //
-// Residues are lazy signed int32: every butterfly adds at most p to the magnitude
-// (montmul returns (-p, p)), so with p < 2^27 no correction is ever needed:
-//   forward: |digit| <= 128 (or < p for key conversion) + 10 p  < 2^31
-//   inverse: |sum of 4 products| < 4 p + 10 p = 14 p < 2^31.
+// Butterflies use Shoup multiplication (twiddle w + companion ws) on lazy UNSIGNED
+// residues: t = w*v mod p lands in [0, 2p) for any 32-bit v, and (u + t, u - t + 2p)
+// grows the bound by 2p per stage, so with p < 2^27 no correction is ever needed:
+//   forward: input < 2p (digit + p, or a canonical key residue), + 20p  -> < 22p < 2^32
+//   inverse: input < 8p (sum of 4 Montgomery products + 4p),     + 20p  -> < 28p < 2^32.
 #pragma once
 #include "modarith.cuh"
 
 namespace b2 {
 
+struct alignas(8) Tw { uint32_t w, ws; };     // twiddle and its Shoup companion
+
 // twiddle table layout shared by host generator, device constant/global copies and
-// the CPU emulation.  All entries are in Montgomery form, canonical [0, p).
+// the CPU emulation.
 struct NttTables {
-    uint32_t fw1[2][32];        // forward pass 1, index (2^s - 1) + g           (31 used)
-    uint32_t iv1[2][32];        // inverse pass 1, index (2^u - 1) + j           (31 used)
-    uint32_t fw2[2][31][32];    // forward pass 2, [q][lane]
-    uint32_t iv2[2][31][32];    // inverse pass 2, [q][lane]
-    uint32_t scale[2][32][32];  // n^-1 psi^-(lane + 32 k), [k][lane]
-    uint32_t r2[2];             // 2^64 mod p  (to Montgomery form)
-    uint32_t crt_p0inv_mont;    // p0^-1 mod p1, Montgomery form mod p1
+    Tw fw1[2][32];          // forward pass 1, index (2^s - 1) + g           (31 used)
+    Tw iv1[2][32];          // inverse pass 1, index (2^u - 1) + j           (31 used)
+    Tw fw2[2][31][32];      // forward pass 2, [q][lane]
+    Tw iv2[2][31][32];      // inverse pass 2, [q][lane]
+    Tw scale[2][32][32];    // n^-1 psi^-(lane + 32 k), [k][lane]
+    uint32_t r2[2];         // 2^64 mod p  (to Montgomery form)
+    Tw crt_p0inv;           // p0^-1 mod p1
 };
 
 inline unsigned brv10(unsigned x)
@@ -56,12 +59,12 @@ inline void make_tables(NttTables& T)
         const uint32_t ipsi = h_powmod(psi, p - 2, p);
         const uint32_t iw = h_mulmod(ipsi, ipsi, p);            // w^-1, w = psi^2
         const uint32_t ninv = h_powmod(kN, p - 2, p);
-        auto M = [&](uint32_t v) { return h_to_mont(v, p); };
+        auto M = [&](uint32_t v) { return Tw{v, h_shoup(v, p)}; };
         auto psirev = [&](unsigned idx) { return h_powmod(psi, brv10(idx), p); };
         // forward: stage s (m = 2^s groups), group i uses psi^brv10(m + i)
         for (int s = 0; s < 5; s++)
             for (int g = 0; g < (1 << s); g++) T.fw1[q][(1 << s) - 1 + g] = M(psirev((1u << s) + g));
-        T.fw1[q][31] = 0;
+        T.fw1[q][31] = Tw{0, 0};
         for (int s = 0; s < 5; s++)                              // global stage 5 + s
             for (int g = 0; g < (1 << s); g++)
                 for (int lane = 0; lane < 32; lane++)
@@ -70,7 +73,7 @@ inline void make_tables(NttTables& T)
         for (int u = 0; u < 5; u++)
             for (int j = 0; j < (1 << u); j++)
                 T.iv1[q][(1 << u) - 1 + j] = M(h_powmod(iw, (uint64_t)j * (512 >> u), p));
-        T.iv1[q][31] = 0;
+        T.iv1[q][31] = Tw{0, 0};
         for (int u = 0; u < 5; u++)                              // t = 32 << u
             for (int g = 0; g < (1 << u); g++)
                 for (int lane = 0; lane < 32; lane++)
@@ -80,50 +83,48 @@ inline void make_tables(NttTables& T)
                 T.scale[q][k][lane] = M(h_mulmod(ninv, h_powmod(ipsi, lane + 32 * k, p), p));
         T.r2[q] = (uint32_t)((((unsigned __int128)1) << 64) % p);
     }
-    T.crt_p0inv_mont = h_to_mont(h_powmod(kP[0] % kP[1], kP[1] - 2, kP[1]), kP[1]);
+    {
+        const uint32_t c = h_powmod(kP[0] % kP[1], kP[1] - 2, kP[1]);
+        T.crt_p0inv = Tw{c, h_shoup(c, kP[1])};
+    }
 }
 
 // ---- in-register radix-32 passes --------------------------------------------
 // tw[q * stride] is twiddle q of this lane (stride 1: warp-uniform table; stride 32:
 // per-lane table with the lane offset already applied to the pointer).
 
+template <int Q>
+B2_HD void butterfly(uint32_t& u, uint32_t& v, const Tw t)
+{
+    const uint32_t r = shoup_mul<Q>(v, t.w, t.ws);
+    const uint32_t a = u;
+    u = a + r;
+    v = a - r + 2u * Prime<Q>::p;
+}
+
 // forward ordering: sub-strides 16, 8, 4, 2, 1; one twiddle per group k / (2 tp)
-template <int Q, typename TW>
-B2_HD void pass_fwd(int32_t (&x)[32], const TW* tw, const int stride)
+template <int Q>
+B2_HD void pass_fwd(uint32_t (&x)[32], const Tw* tw, const int stride)
 {
 #pragma unroll
     for (int s = 0; s < 5; s++) {
         const int tp = 16 >> s;
 #pragma unroll
-        for (int k = 0; k < 32; k++) {
-            if ((k & tp) == 0) {
-                const uint32_t w = tw[((1 << s) - 1 + k / (2 * tp)) * stride];
-                const int32_t v = montmul<Q>(x[k + tp], w);
-                const int32_t u = x[k];
-                x[k] = u + v;
-                x[k + tp] = u - v;
-            }
-        }
+        for (int k = 0; k < 32; k++)
+            if ((k & tp) == 0) butterfly<Q>(x[k], x[k + tp], tw[((1 << s) - 1 + k / (2 * tp)) * stride]);
     }
 }
 
 // inverse (DIT) ordering: sub-strides 1, 2, 4, 8, 16; one twiddle per offset k mod tp
-template <int Q, typename TW>
-B2_HD void pass_inv(int32_t (&x)[32], const TW* tw, const int stride)
+template <int Q>
+B2_HD void pass_inv(uint32_t (&x)[32], const Tw* tw, const int stride)
 {
 #pragma unroll
     for (int u = 0; u < 5; u++) {
         const int tp = 1 << u;
 #pragma unroll
-        for (int k = 0; k < 32; k++) {
-            if ((k & tp) == 0) {
-                const uint32_t w = tw[((1 << u) - 1 + (k & (tp - 1))) * stride];
-                const int32_t v = montmul<Q>(x[k + tp], w);
-                const int32_t a = x[k];
-                x[k] = a + v;
-                x[k + tp] = a - v;
-            }
-        }
+        for (int k = 0; k < 32; k++)
+            if ((k & tp) == 0) butterfly<Q>(x[k], x[k + tp], tw[((1 << u) - 1 + (k & (tp - 1))) * stride]);
     }
 }
 

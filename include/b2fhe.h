@@ -105,6 +105,9 @@ int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, co
 /* tuning / introspection */
 int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
 uint64_t b2fhe_kernel_launches(void);             /* kernels launched by this library so far */
+/* measured integer-pipe ceiling of `device` (register-only probe kernel): mode 0 = 1e9
+ * 32-bit IMAD lane-ops/s, mode 1 = 1e9 Montgomery butterflies/s (the NTT's instruction mix) */
+int b2fhe_int_peak(int device, int mode, double* giga_ops_per_s);
 
 #ifdef __cplusplus
 }

@@ -15,16 +15,16 @@ using namespace b2;
 static NttTables T;
 
 // one emulated warp: x[lane][k]
-typedef int32_t Warp[32][32];
+typedef uint32_t Warp[32][32];
 
 static void exchange(Warp x)
 {
     static uint32_t buf[1024];
     for (int lane = 0; lane < 32; lane++)
         for (int v = 0; v < 8; v++)
-            for (int e = 0; e < 4; e++) buf[xchg_wr_word(lane, v) + e] = (uint32_t)x[lane][4 * v + e];
+            for (int e = 0; e < 4; e++) buf[xchg_wr_word(lane, v) + e] = x[lane][4 * v + e];
     for (int lane = 0; lane < 32; lane++)
-        for (int j = 0; j < 32; j++) x[lane][j] = (int32_t)buf[xchg_rd_word(lane, j)];
+        for (int j = 0; j < 32; j++) x[lane][j] = buf[xchg_rd_word(lane, j)];
 }
 template <int Q> static void fwd(Warp x)   // layout A in, layout B out
 {
@@ -38,23 +38,23 @@ template <int Q> static void inv(Warp x)   // layout B in, layout A out (scaled)
     exchange(x);
     for (int lane = 0; lane < 32; lane++) {
         pass_inv<Q>(x[lane], &T.iv2[Q][0][lane], 32);
-        for (int k = 0; k < 32; k++) x[lane][k] = montmul<Q>(x[lane][k], T.scale[Q][k][lane]);
+        for (int k = 0; k < 32; k++) x[lane][k] = shoup_mul<Q>(x[lane][k], T.scale[Q][k][lane].w, T.scale[Q][k][lane].ws);
     }
 }
 template <int Q> static void load_A(Warp x, const int32_t* a)
 {
     for (int lane = 0; lane < 32; lane++)
-        for (int k = 0; k < 32; k++) x[lane][k] = a[lane + 32 * k];
+        for (int k = 0; k < 32; k++) x[lane][k] = (uint32_t)(a[lane + 32 * k] + (int32_t)Prime<Q>::p);
 }
 // NTT-domain key polynomial in Montgomery form, stored at bk_slot()
 template <int Q> static void key_to_ntt(uint32_t* dst, const uint32_t* src)
 {
     Warp x;
     for (int lane = 0; lane < 32; lane++)
-        for (int k = 0; k < 32; k++) x[lane][k] = (int32_t)(src[lane + 32 * k] % Prime<Q>::p);
+        for (int k = 0; k < 32; k++) x[lane][k] = src[lane + 32 * k] % Prime<Q>::p;
     fwd<Q>(x);
     for (int lane = 0; lane < 32; lane++)
-        for (int k = 0; k < 32; k++) dst[bk_slot(lane, k)] = canon<Q>(montmul<Q>(x[lane][k], T.r2[Q]));
+        for (int k = 0; k < 32; k++) dst[bk_slot(lane, k)] = canon<Q>(umontmul<Q>(x[lane][k], T.r2[Q]));
 }
 
 static int check_polymul(std::mt19937_64& rng, int signed_b)
@@ -75,12 +75,12 @@ static int check_polymul(std::mt19937_64& rng, int signed_b)
     load_A<1>(x1, bs); fwd<1>(x1);
     for (int lane = 0; lane < 32; lane++)
         for (int k = 0; k < 32; k++) {
-            x0[lane][k] = montmul<0>(x0[lane][k], an[0][bk_slot(lane, k)]);
-            x1[lane][k] = montmul<1>(x1[lane][k], an[1][bk_slot(lane, k)]);
+            x0[lane][k] = (uint32_t)(umontmul<0>(x0[lane][k], an[0][bk_slot(lane, k)]) + (int32_t)Prime<0>::p);
+            x1[lane][k] = (uint32_t)(umontmul<1>(x1[lane][k], an[1][bk_slot(lane, k)]) + (int32_t)Prime<1>::p);
         }
     inv<0>(x0); inv<1>(x1);
     for (int lane = 0; lane < 32; lane++)
-        for (int k = 0; k < 32; k++) out[lane + 32 * k] = crt_lift32(x0[lane][k], x1[lane][k], T.crt_p0inv_mont);
+        for (int k = 0; k < 32; k++) out[lane + 32 * k] = crt_lift32(x0[lane][k], x1[lane][k], T.crt_p0inv.w, T.crt_p0inv.ws);
     return memcmp(out, ref, sizeof ref) != 0;
 }
 
@@ -113,15 +113,21 @@ static int check_cmux(std::mt19937_64& rng)
             for (int o = 0; o < 2; o++)
                 for (int lane = 0; lane < 32; lane++)
                     for (int k = 0; k < 32; k++) {
-                        sum[0][o][lane][k] += montmul<0>(x0[lane][k], bkn[0][(2 * row + o) * kN + bk_slot(lane, k)]);
-                        sum[1][o][lane][k] += montmul<1>(x1[lane][k], bkn[1][(2 * row + o) * kN + bk_slot(lane, k)]);
+                        sum[0][o][lane][k] += umontmul<0>(x0[lane][k], bkn[0][(2 * row + o) * kN + bk_slot(lane, k)]);
+                        sum[1][o][lane][k] += umontmul<1>(x1[lane][k], bkn[1][(2 * row + o) * kN + bk_slot(lane, k)]);
                     }
         }
     for (int o = 0; o < 2; o++) {
-        inv<0>(sum[0][o]); inv<1>(sum[1][o]);
+        Warp y0, y1;
+        for (int lane = 0; lane < 32; lane++)
+            for (int k = 0; k < 32; k++) {
+                y0[lane][k] = (uint32_t)(sum[0][o][lane][k] + 4 * (int32_t)Prime<0>::p);
+                y1[lane][k] = (uint32_t)(sum[1][o][lane][k] + 4 * (int32_t)Prime<1>::p);
+            }
+        inv<0>(y0); inv<1>(y1);
         for (int lane = 0; lane < 32; lane++)
             for (int k = 0; k < 32; k++)
-                acc[o * kN + lane + 32 * k] += crt_lift32(sum[0][o][lane][k], sum[1][o][lane][k], T.crt_p0inv_mont);
+                acc[o * kN + lane + 32 * k] += crt_lift32(y0[lane][k], y1[lane][k], T.crt_p0inv.w, T.crt_p0inv.ws);
     }
     return memcmp(acc, ref, sizeof ref) != 0;
 }
