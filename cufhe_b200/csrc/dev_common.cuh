@@ -67,6 +67,26 @@ __device__ __forceinline__ void inv_dev(uint32_t (&x)[32], uint32_t* xbuf, const
     }
 }
 
+// run-time-prime forms (one code copy for both primes; q is warp-uniform)
+__device__ __forceinline__ void fwd_dev_rt(uint32_t (&x)[32], uint32_t* xbuf, const uint32_t* s_tab, int lane, int q, uint32_t p)
+{
+    pass_fwd_p(x, c_fw1[q], 1, p);
+    exchange_dev(x, xbuf, lane);
+    pass_fwd_p(x, tab_fw2(s_tab, q, lane), 32, p);
+}
+__device__ __forceinline__ void inv_dev_rt(uint32_t (&x)[32], uint32_t* xbuf, const uint32_t* s_tab, int lane, int q, uint32_t p)
+{
+    pass_inv_p(x, c_iv1[q], 1, p);
+    exchange_dev(x, xbuf, lane);
+    pass_inv_p(x, tab_iv2(s_tab, q, lane), 32, p);
+    const Tw* sc = tab_scale(s_tab, q, lane);
+#pragma unroll
+    for (int k = 0; k < 32; k++) {
+        const Tw f = sc[k * 32];
+        x[k] = shoup_mul_p(x[k], f.w, f.ws, p);
+    }
+}
+
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads)
 {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");

@@ -48,75 +48,90 @@ struct BrParams {
 constexpr int kBrGateSmemWords = 2 * kN + 2 * kN + 640 / 2;   // acc + 2 exchange buffers + abar(u16)
 __host__ __device__ constexpr int br_smem_bytes(int gates) { return (kLaneTableWords + gates * kBrGateSmemWords) * 4; }
 
-template <int Q>
+// One code copy serves both primes (q is warp-uniform): the unrolled transforms are large
+// and two specialised copies thrash the instruction cache (ncu: stall_no_instruction).
+// Register arrays: sa = residues of output polynomial q ("mine", finished by this warp),
+// sb = residues of output polynomial 1-q (handed to the partner warp).
 __device__ __forceinline__ void br_gate_loop(const uint32_t* __restrict__ bk, uint32_t* acc, uint32_t* xbuf,
                                              const uint32_t* xbuf_other, const uint16_t* s_abar,
-                                             const uint32_t* s_tab, const int lane, const int barid)
+                                             const uint32_t* s_tab, const int lane, const int barid, const int q)
 {
-    constexpr int mine = Q, other = 1 - Q;
-    const uint4* bk4 = reinterpret_cast<const uint4*>(bk) + lane;
+    const uint32_t p = q ? Prime<1>::p : Prime<0>::p;
+    const uint32_t pinv = q ? Prime<1>::pinv : Prime<0>::pinv;
+    const uint32_t dig_off = p - 128u;
+    // key row layout [row][prime][out][256 uint4]; this warp reads out = q first, then 1-q
+    const uint4* bk4 = reinterpret_cast<const uint4*>(bk) + lane + (size_t)q * 2 * (kN / 4);
+    const int off_a = q * (kN / 4), off_b = (1 - q) * (kN / 4);
+    uint32_t* acc_mine = acc + q * kN + lane;
     for (int i = 0; i < kLwe; i++) {
         const uint32_t abar = s_abar[i];
         // lazy residues: 4p + four Montgomery products in (-p, p)  ->  (0, 8p)
-        uint32_t sums[2][32];
+        uint32_t sa[32], sb[32];
 #pragma unroll
-        for (int k = 0; k < 32; k++) sums[0][k] = sums[1][k] = 4u * Prime<Q>::p;
+        for (int k = 0; k < 32; k++) sa[k] = sb[k] = 4u * p;
 
         const uint32_t am = abar & (kN - 1);
         const bool flip = (abar >> kNbit) != 0;
         const uint32_t rbase = (lane - abar) & (kN - 1);
         // coefficient c = lane + 32k is negated iff (c < am) xor flip, c < am <=> k < kth
         const int kth = ((int)am - lane + 31) >> 5;
+        uint32_t dlo[8];
 #pragma unroll 1
-        for (int j = 0; j < 2; j++) {
-            const uint32_t* aj = acc + j * kN;
+        for (int r = 0; r < kRows; r++) {           // TRGSW row r = 2 j + d
             uint32_t x[32];
-            uint32_t dlo[8];
+            if ((r & 1) == 0) {
+                const uint32_t* aj = acc + (r >> 1) * kN;
 #pragma unroll
-            for (int k = 0; k < 32; k++) {
-                uint32_t rot = aj[(rbase + 32 * k) & (kN - 1)];
-                const bool neg = (k < kth) != flip;
-                rot = neg ? 0u - rot : rot;
-                const uint32_t r = rot - aj[lane + 32 * k] + kDecompAdd;
-                x[k] = (r >> 24) + (Prime<Q>::p - 128u);           // digit + p in [0, 2p)
-                const uint32_t d1 = (r >> 16) & 0xFFu;
-                if ((k & 3) == 0) dlo[k >> 2] = d1; else dlo[k >> 2] |= d1 << (8 * (k & 3));
+                for (int k = 0; k < 32; k++) {
+                    uint32_t rot = aj[(rbase + 32 * k) & (kN - 1)];
+                    const bool neg = (k < kth) != flip;
+                    rot = neg ? 0u - rot : rot;
+                    const uint32_t t = rot - aj[lane + 32 * k] + kDecompAdd;
+                    x[k] = (t >> 24) + dig_off;                       // digit 0 + p in [0, 2p)
+                    const uint32_t d1 = (t >> 16) & 0xFFu;
+                    if ((k & 3) == 0) dlo[k >> 2] = d1; else dlo[k >> 2] |= d1 << (8 * (k & 3));
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < 32; k++) x[k] = ((dlo[k >> 2] >> (8 * (k & 3))) & 0xFFu) + dig_off;
             }
-#pragma unroll 1
-            for (int d = 0; d < 2; d++) {
-                if (d == 1) {
+            fwd_dev_rt(x, xbuf, s_tab, lane, q, p);
+            const uint4* row = bk4 + (size_t)(i * kRows + r) * (4 * (kN / 4));
 #pragma unroll
-                    for (int k = 0; k < 32; k++) x[k] = ((dlo[k >> 2] >> (8 * (k & 3))) & 0xFFu) + (Prime<Q>::p - 128u);
-                }
-                fwd_dev<Q>(x, xbuf, s_tab, lane);
-                // key row (i, 2j+d), my prime: [out][v][lane] uint4
-                const uint4* row = bk4 + ((size_t)((i * kRows + 2 * j + d) * 2 + Q) * 2) * (kN / 4);
+            for (int v = 0; v < 8; v++) {
+                const uint4 b = __ldg(row + off_a + v * 32);
+                sa[4 * v + 0] += (uint32_t)umontmul_p(x[4 * v + 0], b.x, p, pinv);
+                sa[4 * v + 1] += (uint32_t)umontmul_p(x[4 * v + 1], b.y, p, pinv);
+                sa[4 * v + 2] += (uint32_t)umontmul_p(x[4 * v + 2], b.z, p, pinv);
+                sa[4 * v + 3] += (uint32_t)umontmul_p(x[4 * v + 3], b.w, p, pinv);
+            }
 #pragma unroll
-                for (int o = 0; o < 2; o++) {
-#pragma unroll
-                    for (int v = 0; v < 8; v++) {
-                        const uint4 b = __ldg(row + o * (kN / 4) + v * 32);
-                        sums[o][4 * v + 0] += (uint32_t)umontmul<Q>(x[4 * v + 0], b.x);
-                        sums[o][4 * v + 1] += (uint32_t)umontmul<Q>(x[4 * v + 1], b.y);
-                        sums[o][4 * v + 2] += (uint32_t)umontmul<Q>(x[4 * v + 2], b.z);
-                        sums[o][4 * v + 3] += (uint32_t)umontmul<Q>(x[4 * v + 3], b.w);
-                    }
-                }
+            for (int v = 0; v < 8; v++) {
+                const uint4 b = __ldg(row + off_b + v * 32);
+                sb[4 * v + 0] += (uint32_t)umontmul_p(x[4 * v + 0], b.x, p, pinv);
+                sb[4 * v + 1] += (uint32_t)umontmul_p(x[4 * v + 1], b.y, p, pinv);
+                sb[4 * v + 2] += (uint32_t)umontmul_p(x[4 * v + 2], b.z, p, pinv);
+                sb[4 * v + 3] += (uint32_t)umontmul_p(x[4 * v + 3], b.w, p, pinv);
             }
         }
-        inv_dev<Q>(sums[other], xbuf, s_tab, lane);
-        inv_dev<Q>(sums[mine], xbuf, s_tab, lane);
+        // two inverse transforms through ONE code copy: transform sb, swap, transform (old) sa
+#pragma unroll 1
+        for (int t = 0; t < 2; t++) {
+            inv_dev_rt(sb, xbuf, s_tab, lane, q, p);
+#pragma unroll
+            for (int k = 0; k < 32; k++) { const uint32_t tmp = sa[k]; sa[k] = sb[k]; sb[k] = tmp; }
+        }
+        // now sa = INTT(out q) (mine), sb = INTT(out 1-q): hand sb to the partner
         __syncwarp();
 #pragma unroll
-        for (int k = 0; k < 32; k++) xbuf[k * 32 + lane] = sums[other][k];
+        for (int k = 0; k < 32; k++) xbuf[k * 32 + lane] = sb[k];
         named_bar_sync(barid, 64);
-        uint32_t* am_ = acc + mine * kN + lane;
 #pragma unroll
         for (int k = 0; k < 32; k++) {
-            const uint32_t t = xbuf_other[k * 32 + lane];
-            const uint32_t s0 = Q == 0 ? sums[mine][k] : t;
-            const uint32_t s1 = Q == 0 ? t : sums[mine][k];
-            am_[32 * k] += crt_lift32(s0, s1, c_crt_p0inv.w, c_crt_p0inv.ws);
+            const uint32_t t = xbuf_other[k * 32 + lane];      // partner's residue of out q
+            const uint32_t s0 = q ? t : sa[k];
+            const uint32_t s1 = q ? sa[k] : t;
+            acc_mine[32 * k] += crt_lift32(s0, s1, c_crt_p0inv.w, c_crt_p0inv.ws);
         }
         named_bar_sync(barid, 64);
     }
@@ -164,8 +179,7 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const BrParams P)
     }
     named_bar_sync(barid, 64);
 
-    if (q == 0) br_gate_loop<0>(P.bk, acc, xbuf, xbuf_other, s_abar, s_tab, lane, barid);
-    else br_gate_loop<1>(P.bk, acc, xbuf, xbuf_other, s_abar, s_tab, lane, barid);
+    br_gate_loop(P.bk, acc, xbuf, xbuf_other, s_abar, s_tab, lane, barid, q);
 
     // ---- SampleExtract(0) (src/bootstrap_gpu.cu:366-381) ----
     uint32_t* out = P.out + (size_t)it.slot * kLvl1Words;

@@ -68,33 +68,35 @@ B2_HD int32_t montmul(int32_t a, uint32_t bt)
 // unsigned variant: 0 <= a < 2^32 (lazy residue), 0 <= bt < p; result in (-p, p).
 // Used for the key multiply-accumulate, where only ONE constant per key coefficient
 // is affordable (a Shoup companion would double the 41.7 MB key).
-template <int Q>
-B2_HD int32_t umontmul(uint32_t a, uint32_t bt)
+B2_HD int32_t umontmul_p(uint32_t a, uint32_t bt, uint32_t p, uint32_t pinv)
 {
     const uint64_t prod = (uint64_t)a * (uint64_t)bt;
-    const uint32_t m = (uint32_t)prod * Prime<Q>::pinv;
+    const uint32_t m = (uint32_t)prod * pinv;
 #ifdef __CUDA_ARCH__
-    const uint32_t t = __umulhi(m, Prime<Q>::p);
+    const uint32_t t = __umulhi(m, p);
 #else
-    const uint32_t t = (uint32_t)(((uint64_t)m * (uint64_t)Prime<Q>::p) >> 32);
+    const uint32_t t = (uint32_t)(((uint64_t)m * (uint64_t)p) >> 32);
 #endif
     return (int32_t)((uint32_t)(prod >> 32) - t);
 }
+template <int Q>
+B2_HD int32_t umontmul(uint32_t a, uint32_t bt) { return umontmul_p(a, bt, Prime<Q>::p, Prime<Q>::pinv); }
 
 // Shoup multiplication by a constant w < p with companion ws = floor(w * 2^32 / p):
 // v * w mod p in [0, 2p) for ANY 32-bit v.  One IMAD.HI + two IMAD on sm_100a, which
 // measures 1.7x faster than the Montgomery form (profiles/r1_ubench_butterfly_mix.log)
 // because IMAD.WIDE and IMAD.HI are both half-rate.
-template <int Q>
-B2_HD uint32_t shoup_mul(uint32_t v, uint32_t w, uint32_t ws)
+B2_HD uint32_t shoup_mul_p(uint32_t v, uint32_t w, uint32_t ws, uint32_t p)
 {
 #ifdef __CUDA_ARCH__
     const uint32_t q = __umulhi(v, ws);
 #else
     const uint32_t q = (uint32_t)(((uint64_t)v * (uint64_t)ws) >> 32);
 #endif
-    return v * w - q * Prime<Q>::p;
+    return v * w - q * p;
 }
+template <int Q>
+B2_HD uint32_t shoup_mul(uint32_t v, uint32_t w, uint32_t ws) { return shoup_mul_p(v, w, ws, Prime<Q>::p); }
 
 // canonical representative in [0, p) of a value in (-p, p)
 template <int Q>

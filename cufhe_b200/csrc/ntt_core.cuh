@@ -93,40 +93,47 @@ inline void make_tables(NttTables& T)
 // tw[q * stride] is twiddle q of this lane (stride 1: warp-uniform table; stride 32:
 // per-lane table with the lane offset already applied to the pointer).
 
-template <int Q>
-B2_HD void butterfly(uint32_t& u, uint32_t& v, const Tw t)
+// The prime is a (warp-uniform) run-time value in the *_p forms so that both primes share
+// ONE copy of the unrolled code (instruction-cache footprint halves); the <Q> forms bind
+// it at compile time.
+B2_HD void butterfly_p(uint32_t& u, uint32_t& v, const Tw t, const uint32_t p, const uint32_t p2)
 {
-    const uint32_t r = shoup_mul<Q>(v, t.w, t.ws);
+    const uint32_t r = shoup_mul_p(v, t.w, t.ws, p);
     const uint32_t a = u;
     u = a + r;
-    v = a - r + 2u * Prime<Q>::p;
+    v = a - r + p2;
 }
+template <int Q>
+B2_HD void butterfly(uint32_t& u, uint32_t& v, const Tw t) { butterfly_p(u, v, t, Prime<Q>::p, 2u * Prime<Q>::p); }
 
 // forward ordering: sub-strides 16, 8, 4, 2, 1; one twiddle per group k / (2 tp)
-template <int Q>
-B2_HD void pass_fwd(uint32_t (&x)[32], const Tw* tw, const int stride)
+B2_HD void pass_fwd_p(uint32_t (&x)[32], const Tw* tw, const int stride, const uint32_t p)
 {
+    const uint32_t p2 = 2u * p;
 #pragma unroll
     for (int s = 0; s < 5; s++) {
         const int tp = 16 >> s;
 #pragma unroll
         for (int k = 0; k < 32; k++)
-            if ((k & tp) == 0) butterfly<Q>(x[k], x[k + tp], tw[((1 << s) - 1 + k / (2 * tp)) * stride]);
+            if ((k & tp) == 0) butterfly_p(x[k], x[k + tp], tw[((1 << s) - 1 + k / (2 * tp)) * stride], p, p2);
     }
 }
-
 // inverse (DIT) ordering: sub-strides 1, 2, 4, 8, 16; one twiddle per offset k mod tp
-template <int Q>
-B2_HD void pass_inv(uint32_t (&x)[32], const Tw* tw, const int stride)
+B2_HD void pass_inv_p(uint32_t (&x)[32], const Tw* tw, const int stride, const uint32_t p)
 {
+    const uint32_t p2 = 2u * p;
 #pragma unroll
     for (int u = 0; u < 5; u++) {
         const int tp = 1 << u;
 #pragma unroll
         for (int k = 0; k < 32; k++)
-            if ((k & tp) == 0) butterfly<Q>(x[k], x[k + tp], tw[((1 << u) - 1 + (k & (tp - 1))) * stride]);
+            if ((k & tp) == 0) butterfly_p(x[k], x[k + tp], tw[((1 << u) - 1 + (k & (tp - 1))) * stride], p, p2);
     }
 }
+template <int Q>
+B2_HD void pass_fwd(uint32_t (&x)[32], const Tw* tw, const int stride) { pass_fwd_p(x, tw, stride, Prime<Q>::p); }
+template <int Q>
+B2_HD void pass_inv(uint32_t (&x)[32], const Tw* tw, const int stride) { pass_inv_p(x, tw, stride, Prime<Q>::p); }
 
 // ---- the 32x32 warp transpose through shared memory ---------------------------
 // writer lane L stores its 8 uint4 vectors in row L at swizzled vector slots;
