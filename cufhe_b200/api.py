@@ -67,6 +67,16 @@ def Initialize(bk_raw, ksk_raw, device=None):
         _devices = [int(device)]
 
 
+def broadcast_key_buffers(bk_t, ksk_t, src=0, group=None):
+    """The one collective of the path: the converted bootstrapping key and the key-switching
+    key go from rank `src` to every rank (NCCL over NVLink for CUDA tensors; gloo in the CPU
+    tests).  Steady state has no collective: gates are independent."""
+    import torch.distributed as dist
+    dist.broadcast(bk_t, src=src, group=group)
+    dist.broadcast(ksk_t, src=src, group=group)
+    return bk_t, ksk_t
+
+
 def InitializeBroadcast(bk_raw, ksk_raw, device, group=None, src=0):
     """One process per GPU: rank `src` converts the keys, every other rank receives the
     NTT-domain key and the key-switching key by ONE broadcast each (NCCL over NVLink for
@@ -84,13 +94,11 @@ def InitializeBroadcast(bk_raw, ksk_raw, device, group=None, src=0):
         _lib.check(L.b2fhe_key_pointers(int(device), C.byref(pb), C.byref(pk)))
         bk_t = _wrap_device_bytes(pb.value, BK_NTT_BYTES, dev)
         ksk_t = _wrap_device_bytes(pk.value, KSK_DEV_BYTES, dev)
-        dist.broadcast(bk_t, src=src, group=group)
-        dist.broadcast(ksk_t, src=src, group=group)
+        broadcast_key_buffers(bk_t, ksk_t, src, group)
         return bk_t, ksk_t
     bk_t = torch.empty(BK_NTT_BYTES, dtype=torch.uint8, device=dev)
     ksk_t = torch.empty(KSK_DEV_BYTES, dtype=torch.uint8, device=dev)
-    dist.broadcast(bk_t, src=src, group=group)
-    dist.broadcast(ksk_t, src=src, group=group)
+    broadcast_key_buffers(bk_t, ksk_t, src, group)
     torch.cuda.synchronize(dev)
     _lib.check(L.b2fhe_adopt_keys(int(device), bk_t.data_ptr(), ksk_t.data_ptr()))
     _devices = [int(device)]

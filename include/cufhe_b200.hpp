@@ -1,0 +1,220 @@
+// cufhe_b200.hpp -- header-only C++ shim: cuFHE's public API (namespace cufhe,
+// reference include/cufhe_gpu.cuh:42-315 and src/cufhe_gates_gpu.cu) implemented as
+// thin calls into the C ABI of libb2fhe.so (include/b2fhe.h).  Same names, argument
+// order and semantics, so code written against cuFHE's gate API recompiles unchanged:
+//
+//   SetGPUNum, Initialize(EvalKey), CleanUp, Synchronize, StreamQuery, Stream,
+//   Ctxt<P>, CtxtCopyH2D/D2H, And ... Xnor, Mux, NMux, Not, Copy, CopyOnHost and the
+//   device-resident g* twins, for P = TFHEpp::lvl0param / lvl1param.
+//
+// Added beside it (not in the reference): CtxtBatch<P> + <Gate>Batch(...) -- one call,
+// one batched launch -- which is how the engine reaches its throughput.
+// Error convention of the reference is kept: a failing call prints the message and
+// exit(-1)s (include/details/error_gpu.cuh:30-66).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "b2fhe.h"
+#ifdef B2FHE_WITH_TFHEPP
+#include <tfhe++.hpp>
+#else
+#include "tfhepp_compat.hpp"
+#endif
+
+namespace cufhe {
+
+inline int& _gpuNumRef() { static int n = 1; return n; }
+inline int& _streamCountRef() { static int n = 0; return n; }
+
+inline void _b2check(int rc, const char* file, int line)
+{
+    if (rc != 0) {
+        fprintf(stderr, "cufhe(b2fhe) failed at %s:%i : %s\n", file, line, b2fhe_last_error_string());
+        exit(-1);
+    }
+}
+#define B2CHECK(x) ::cufhe::_b2check((x), __FILE__, __LINE__)
+
+template <class P> constexpr int _level() { return sizeof(typename P::T) == 2 ? 0 : 1; }
+
+inline void SetGPUNum(int gpuNum) { _gpuNumRef() = gpuNum; }
+inline void Initialize(const TFHEpp::EvalKey& ek)
+{
+    B2CHECK(b2fhe_init(_gpuNumRef(), reinterpret_cast<const uint32_t*>(&ek.getbk<TFHEpp::lvl01param>()),
+                       reinterpret_cast<const uint16_t*>(&ek.getiksk<TFHEpp::lvl10param>())));
+}
+inline void CleanUp() { B2CHECK(b2fhe_cleanup()); }
+inline void Synchronize() { B2CHECK(b2fhe_synchronize()); }
+
+class Stream {
+public:
+    Stream() : st_(0), device_id_(_streamCountRef()++ % _gpuNumRef()) {}
+    explicit Stream(int device_id) : st_(0), device_id_(device_id) { _streamCountRef()++; }
+    void Create()
+    {
+        cudaSetDevice(device_id_);
+        cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking);
+    }
+    void Destroy()
+    {
+        cudaSetDevice(device_id_);
+        cudaStreamDestroy(st_);
+        st_ = 0;
+    }
+    cudaStream_t st() const { return st_; }
+    int device_id() const { return device_id_; }
+
+private:
+    cudaStream_t st_;
+    int device_id_;
+};
+inline bool StreamQuery(Stream st)
+{
+    cudaSetDevice(st.device_id());
+    return cudaStreamQuery(st.st()) == cudaSuccess;
+}
+
+// a batch of `count` ciphertexts: pinned host array + one device buffer per GPU
+template <class P>
+struct CtxtBatch {
+    explicit CtxtBatch(size_t count) : count(count)
+    {
+        const size_t bytes = count * sizeof(TFHEpp::TLWE<P>);
+        cudaMallocHost((void**)&tlwehost, bytes);
+        tlwedevices.resize(_gpuNumRef());
+        for (int i = 0; i < _gpuNumRef(); i++) {
+            cudaSetDevice(i);
+            cudaMalloc((void**)&tlwedevices[i], bytes);
+        }
+    }
+    ~CtxtBatch()
+    {
+        cudaFreeHost(tlwehost);
+        for (size_t i = 0; i < tlwedevices.size(); i++) {
+            cudaSetDevice((int)i);
+            cudaFree(tlwedevices[i]);
+        }
+    }
+    CtxtBatch(const CtxtBatch&) = delete;
+    CtxtBatch& operator=(const CtxtBatch&) = delete;
+    size_t bytes() const { return count * sizeof(TFHEpp::TLWE<P>); }
+    size_t count;
+    TFHEpp::TLWE<P>* tlwehost;
+    std::vector<typename P::T*> tlwedevices;
+};
+
+// cufhe::Ctxt<P> (include/cufhe_gpu.cuh:102-121): one ciphertext
+template <class P>
+struct Ctxt {
+    Ctxt()
+    {
+        cudaHostRegister(tlwehost.data(), sizeof(tlwehost), cudaHostRegisterDefault);
+        tlwedevices.resize(_gpuNumRef());
+        for (int i = 0; i < _gpuNumRef(); i++) {
+            cudaSetDevice(i);
+            cudaMalloc((void**)&tlwedevices[i], sizeof(tlwehost));
+        }
+    }
+    ~Ctxt()
+    {
+        cudaHostUnregister(tlwehost.data());
+        for (size_t i = 0; i < tlwedevices.size(); i++) {
+            cudaSetDevice((int)i);
+            cudaFree(tlwedevices[i]);
+        }
+    }
+    Ctxt(const Ctxt&) = delete;
+    Ctxt& operator=(const Ctxt&) = delete;
+    alignas(64) TFHEpp::TLWE<P> tlwehost;
+    std::vector<typename P::T*> tlwedevices;
+};
+
+template <class P> inline void CtxtCopyH2D(Ctxt<P>& c, Stream st)
+{
+    cudaSetDevice(st.device_id());
+    cudaMemcpyAsync(c.tlwedevices[st.device_id()], c.tlwehost.data(), sizeof(c.tlwehost), cudaMemcpyHostToDevice, st.st());
+}
+template <class P> inline void CtxtCopyD2H(Ctxt<P>& c, Stream st)
+{
+    cudaSetDevice(st.device_id());
+    cudaMemcpyAsync(c.tlwehost.data(), c.tlwedevices[st.device_id()], sizeof(c.tlwehost), cudaMemcpyDeviceToHost, st.st());
+}
+template <class P> inline void CtxtCopyH2D(CtxtBatch<P>& c, Stream st)
+{
+    cudaSetDevice(st.device_id());
+    cudaMemcpyAsync(c.tlwedevices[st.device_id()], c.tlwehost, c.bytes(), cudaMemcpyHostToDevice, st.st());
+}
+template <class P> inline void CtxtCopyD2H(CtxtBatch<P>& c, Stream st)
+{
+    cudaSetDevice(st.device_id());
+    cudaMemcpyAsync(c.tlwehost, c.tlwedevices[st.device_id()], c.bytes(), cudaMemcpyDeviceToHost, st.st());
+}
+template <class P> inline void CopyOnHost(Ctxt<P>& out, Ctxt<P>& in) { out.tlwehost = in.tlwehost; }
+
+// ---- gates ---------------------------------------------------------------------------
+template <class P, class C>
+inline void _gate(int op, C& out, C* in0, C* in1, C* in2, size_t count, Stream st, bool copy)
+{
+    const int d = st.device_id();
+    if (copy) {
+        CtxtCopyH2D<P>(*in0, st);
+        if (in1) CtxtCopyH2D<P>(*in1, st);
+        if (in2) CtxtCopyH2D<P>(*in2, st);
+    }
+    B2CHECK(b2fhe_gate_batch(d, (b2fhe_stream_t)st.st(), op, _level<P>(), out.tlwedevices[d], in0->tlwedevices[d],
+                             in1 ? in1->tlwedevices[d] : nullptr, in2 ? in2->tlwedevices[d] : nullptr, count));
+    if (copy) CtxtCopyD2H<P>(out, st);
+}
+
+#define B2_GATE2(Name, OP)                                                                                         \
+    template <class P> inline void Name(Ctxt<P>& out, Ctxt<P>& in0, Ctxt<P>& in1, Stream st)                        \
+    { _gate<P>(OP, out, &in0, &in1, (Ctxt<P>*)nullptr, 1, st, true); }                                              \
+    template <class P> inline void g##Name(Ctxt<P>& out, Ctxt<P>& in0, Ctxt<P>& in1, Stream st)                     \
+    { _gate<P>(OP, out, &in0, &in1, (Ctxt<P>*)nullptr, 1, st, false); }                                             \
+    template <class P> inline void Name##Batch(CtxtBatch<P>& out, CtxtBatch<P>& in0, CtxtBatch<P>& in1, Stream st)  \
+    { _gate<P>(OP, out, &in0, &in1, (CtxtBatch<P>*)nullptr, out.count, st, true); }                                 \
+    template <class P> inline void g##Name##Batch(CtxtBatch<P>& out, CtxtBatch<P>& in0, CtxtBatch<P>& in1, Stream st) \
+    { _gate<P>(OP, out, &in0, &in1, (CtxtBatch<P>*)nullptr, out.count, st, false); }
+B2_GATE2(Nand, B2FHE_NAND)
+B2_GATE2(Or, B2FHE_OR)
+B2_GATE2(OrYN, B2FHE_ORYN)
+B2_GATE2(OrNY, B2FHE_ORNY)
+B2_GATE2(And, B2FHE_AND)
+B2_GATE2(AndYN, B2FHE_ANDYN)
+B2_GATE2(AndNY, B2FHE_ANDNY)
+B2_GATE2(Nor, B2FHE_NOR)
+B2_GATE2(Xor, B2FHE_XOR)
+B2_GATE2(Xnor, B2FHE_XNOR)
+#undef B2_GATE2
+
+#define B2_GATE3(Name, OP)                                                                                          \
+    template <class P> inline void Name(Ctxt<P>& out, Ctxt<P>& inc, Ctxt<P>& in1, Ctxt<P>& in0, Stream st)          \
+    { _gate<P>(OP, out, &inc, &in1, &in0, 1, st, true); }                                                           \
+    template <class P> inline void g##Name(Ctxt<P>& out, Ctxt<P>& inc, Ctxt<P>& in1, Ctxt<P>& in0, Stream st)       \
+    { _gate<P>(OP, out, &inc, &in1, &in0, 1, st, false); }                                                          \
+    template <class P> inline void Name##Batch(CtxtBatch<P>& out, CtxtBatch<P>& inc, CtxtBatch<P>& in1, CtxtBatch<P>& in0, Stream st) \
+    { _gate<P>(OP, out, &inc, &in1, &in0, out.count, st, true); }                                                   \
+    template <class P> inline void g##Name##Batch(CtxtBatch<P>& out, CtxtBatch<P>& inc, CtxtBatch<P>& in1, CtxtBatch<P>& in0, Stream st) \
+    { _gate<P>(OP, out, &inc, &in1, &in0, out.count, st, false); }
+B2_GATE3(Mux, B2FHE_MUX)
+B2_GATE3(NMux, B2FHE_NMUX)
+#undef B2_GATE3
+
+#define B2_GATE1(Name, OP)                                                                                          \
+    template <class P> inline void Name(Ctxt<P>& out, Ctxt<P>& in, Stream st)                                       \
+    { _gate<P>(OP, out, &in, (Ctxt<P>*)nullptr, (Ctxt<P>*)nullptr, 1, st, true); }                                  \
+    template <class P> inline void g##Name(Ctxt<P>& out, Ctxt<P>& in, Stream st)                                    \
+    { _gate<P>(OP, out, &in, (Ctxt<P>*)nullptr, (Ctxt<P>*)nullptr, 1, st, false); }                                 \
+    template <class P> inline void Name##Batch(CtxtBatch<P>& out, CtxtBatch<P>& in, Stream st)                      \
+    { _gate<P>(OP, out, &in, (CtxtBatch<P>*)nullptr, (CtxtBatch<P>*)nullptr, out.count, st, true); }                \
+    template <class P> inline void g##Name##Batch(CtxtBatch<P>& out, CtxtBatch<P>& in, Stream st)                   \
+    { _gate<P>(OP, out, &in, (CtxtBatch<P>*)nullptr, (CtxtBatch<P>*)nullptr, out.count, st, false); }
+B2_GATE1(Not, B2FHE_NOT)
+B2_GATE1(Copy, B2FHE_COPY)
+#undef B2_GATE1
+
+}  // namespace cufhe

@@ -1,0 +1,121 @@
+// C++ port of the reference's gate test (test/test_gate_gpu.cc:36-91, test/test_util.h:8-96,
+// truth tables test/plain.h:10-69) against include/cufhe_b200.hpp -- the SAME user code
+// shape: Ctxt<P>, Stream, Nand(out, in0, in1, st) ..., Synchronize(), decrypt == truth.
+// Keys/encryption/decryption come from the test oracle (the box has no TFHEpp headers).
+// Also exercises the batched calls and checks ciphertext bytes against the oracle.
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "../../include/cufhe_b200.hpp"
+#include "../../oracle/cufhe_oracle.h"
+
+using namespace cufhe;
+using TFHEpp::lvl0param;
+using TFHEpp::lvl1param;
+
+static std::vector<int32_t> sk0(636), sk1(1024);
+static int failures = 0;
+
+template <class P> static void enc(TFHEpp::TLWE<P>& c, int bit, uint64_t idx)
+{
+    if (sizeof(typename P::T) == 2) orc_encrypt_lvl0(7, idx, bit, sk0.data(), (uint16_t*)c.data());
+    else orc_encrypt_lvl1(7, idx, bit, sk1.data(), (uint32_t*)c.data());
+}
+template <class P> static int dec(const TFHEpp::TLWE<P>& c)
+{
+    return sizeof(typename P::T) == 2 ? orc_decrypt_lvl0((const uint16_t*)c.data(), sk0.data())
+                                      : orc_decrypt_lvl1((const uint32_t*)c.data(), sk1.data());
+}
+
+template <class P> static void run_level(const TFHEpp::EvalKey& ek, int kNumSMs)
+{
+    const int level = sizeof(typename P::T) == 2 ? 0 : 1;
+    const int kNumTests = 2 * kNumSMs;        // per-gate launches (legacy path)
+    std::vector<Stream> st(kNumSMs);
+    for (auto& s : st) s.Create();
+    std::vector<Ctxt<P>> a(kNumTests), b(kNumTests), c(kNumTests), r(kNumTests);
+    std::vector<int> pa(kNumTests), pb(kNumTests), pc(kNumTests);
+    for (int op = 0; op < ORC_NUM_OPS; op++) {
+        for (int i = 0; i < kNumTests; i++) {
+            pa[i] = (i * 7 + op) & 1; pb[i] = (i * 5 + op / 2) & 1; pc[i] = (i * 3 + 1) & 1;
+            enc<P>(a[i].tlwehost, pa[i], 1000 * op + i);
+            enc<P>(b[i].tlwehost, pb[i], 100000 + 1000 * op + i);
+            enc<P>(c[i].tlwehost, pc[i], 200000 + 1000 * op + i);
+        }
+        for (int i = 0; i < kNumTests; i++) {
+            Stream s = st[i % kNumSMs];
+            switch (op) {
+                case ORC_NAND: Nand<P>(r[i], a[i], b[i], s); break;
+                case ORC_OR: Or<P>(r[i], a[i], b[i], s); break;
+                case ORC_ORYN: OrYN<P>(r[i], a[i], b[i], s); break;
+                case ORC_ORNY: OrNY<P>(r[i], a[i], b[i], s); break;
+                case ORC_AND: And<P>(r[i], a[i], b[i], s); break;
+                case ORC_ANDYN: AndYN<P>(r[i], a[i], b[i], s); break;
+                case ORC_ANDNY: AndNY<P>(r[i], a[i], b[i], s); break;
+                case ORC_NOR: Nor<P>(r[i], a[i], b[i], s); break;
+                case ORC_XOR: Xor<P>(r[i], a[i], b[i], s); break;
+                case ORC_XNOR: Xnor<P>(r[i], a[i], b[i], s); break;
+                case ORC_MUX: Mux<P>(r[i], a[i], b[i], c[i], s); break;
+                case ORC_NMUX: NMux<P>(r[i], a[i], b[i], c[i], s); break;
+                case ORC_NOT: Not<P>(r[i], a[i], s); break;
+                case ORC_COPY: Copy<P>(r[i], a[i], s); break;
+            }
+        }
+        Synchronize();
+        int bad = 0;
+        for (int i = 0; i < kNumTests; i++) {
+            if (dec<P>(r[i].tlwehost) != orc_truth(op, pa[i], pb[i], pc[i])) bad++;
+            // byte parity with the oracle on a few gates
+            if (i < 3) {
+                TFHEpp::TLWE<P> want;
+                orc_gate(op, level, want.data(), a[i].tlwehost.data(), b[i].tlwehost.data(), c[i].tlwehost.data(),
+                         ek.bk.data(), ek.iksk.data());
+                if (memcmp(want.data(), r[i].tlwehost.data(), sizeof want)) bad++;
+            }
+        }
+        printf("level %d op %2d : %s (%d gates, per-gate API)\n", level, op, bad ? "FAIL" : "PASS", kNumTests);
+        failures += bad;
+    }
+    // batched API: one launch for 8 x SMs NANDs, chained with a device-resident gNand
+    const size_t n = 8 * (size_t)kNumSMs;
+    CtxtBatch<P> A(n), B(n), R(n), R2(n);
+    std::vector<int> qa(n), qb(n);
+    for (size_t i = 0; i < n; i++) {
+        qa[i] = (i >> 1) & 1; qb[i] = i & 1;
+        enc<P>(A.tlwehost[i], qa[i], 900000 + i);
+        enc<P>(B.tlwehost[i], qb[i], 950000 + i);
+    }
+    Stream s = st[0];
+    NandBatch<P>(R, A, B, s);            // H2D + gate + D2H
+    gNandBatch<P>(R2, R, B, s);          // device-resident chain: NAND(NAND(a,b), b)
+    CtxtCopyD2H<P>(R2, s);
+    while (!StreamQuery(s)) {}
+    int bad = 0;
+    for (size_t i = 0; i < n; i++) {
+        const int t1 = 1 - qa[i] * qb[i];
+        if (dec<P>(R.tlwehost[i]) != t1) bad++;
+        if (dec<P>(R2.tlwehost[i]) != 1 - t1 * qb[i]) bad++;
+    }
+    printf("level %d batched NAND chain : %s (%zu gates)\n", level, bad ? "FAIL" : "PASS", n);
+    failures += bad;
+    for (auto& x : st) x.Destroy();
+}
+
+int main()
+{
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, 0) != cudaSuccess) { printf("no CUDA device\n"); return 2; }
+    const int kNumSMs = prop.multiProcessorCount;
+    TFHEpp::EvalKey ek;
+    ek.bk.resize(ORC_BK_WORDS);
+    ek.iksk.resize(ORC_KSK_WORDS);
+    orc_keygen(20261104, sk0.data(), sk1.data(), ek.bk.data(), ek.iksk.data());
+    SetGPUNum(1);
+    Initialize(ek);
+    run_level<lvl1param>(ek, kNumSMs);    // what test/test_gate_gpu.cc runs
+    run_level<lvl0param>(ek, kNumSMs);    // what test/test_gate_gpu_multi.cc / test_intensive.cc run
+    CleanUp();
+    printf(failures ? "FAILED (%d)\n" : "ALL PASS\n", failures);
+    return failures ? 1 : 0;
+}
