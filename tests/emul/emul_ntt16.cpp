@@ -1,0 +1,197 @@
+// CPU emulation of the 64-thread x 16-coefficient team dataflow (cufhe_b200/csrc/ntt16.cuh)
+// used by k_blind_rotate16: same host+device pass functions, same padded exchange slots,
+// thread by thread, checked against the oracle.  Also checks that every exchange
+// store/load is shared-memory bank-conflict free.  Test infrastructure only.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <random>
+#include "../../cufhe_b200/csrc/ntt16.cuh"
+#include "../../cufhe_b200/csrc/tfhe_core.cuh"
+#include "../../oracle/cufhe_oracle.h"
+
+using namespace b2;
+static NttTables T;
+static Lane16Tables L;
+static int g_conflicts = 0;
+
+typedef uint32_t Team[64][16];
+
+// one exchange: every thread stores x[k] at pad(eFrom(T,k)), then loads pad(eTo(T,k))
+template <class EF, class ET, class PAD>
+static void exchange(Team x, EF eFrom, ET eTo, PAD pad)
+{
+    static uint32_t buf[kXbufWords];
+    for (int k = 0; k < 16; k++)
+        for (int w = 0; w < 2; w++) {
+            unsigned banksW = 0, banksR = 0;
+            for (int l = 0; l < 32; l++) {
+                const int t = 32 * w + l;
+                const int sw = pad(eFrom(t, k)), sr = pad(eTo(t, k));
+                if (sw >= kXbufWords || sr >= kXbufWords) { g_conflicts += 1000; continue; }
+                if (banksW & (1u << (sw & 31))) g_conflicts++;
+                if (banksR & (1u << (sr & 31))) g_conflicts++;
+                banksW |= 1u << (sw & 31);
+                banksR |= 1u << (sr & 31);
+            }
+        }
+    for (int t = 0; t < 64; t++)
+        for (int k = 0; k < 16; k++) buf[pad(eFrom(t, k))] = x[t][k];
+    for (int t = 0; t < 64; t++)
+        for (int k = 0; k < 16; k++) x[t][k] = buf[pad(eTo(t, k))];
+}
+
+static void fwd(Team x, int q)   // layout A in, layout C out
+{
+    const uint32_t p = kP[q];
+    for (int t = 0; t < 64; t++) pass16_fwd<4, 8>(x[t], T.fw1[q], 1, p);
+    exchange(x, eA, eB, padAB);
+    for (int t = 0; t < 64; t++) pass16_fwd<4, 8>(x[t], &L.fw2[q][0][t >> 2], 16, p);
+    exchange(x, eB, eC, padC);
+    for (int t = 0; t < 64; t++) pass16_fwd3(x[t], &L.fw3[q][0][t], 64, p);
+}
+static void inv(Team x, int q)   // layout C in, layout A out (scaled, [0, 2p))
+{
+    const uint32_t p = kP[q];
+    for (int t = 0; t < 64; t++) pass16_inv<true>(x[t], T.iv1[q], 1, p);
+    exchange(x, eC, eD, padC);
+    for (int t = 0; t < 64; t++) pass16_inv<false>(x[t], &L.iv2[q][0][t & 15], 16, p);
+    exchange(x, eD, eA, padDA);
+    for (int t = 0; t < 64; t++) {
+        pass16_inv3(x[t], &L.iv3[q][0][t], 64, p);
+        for (int k = 0; k < 16; k++) x[t][k] = shoup_mul_p(x[t][k], L.scale[q][k][t].w, L.scale[q][k][t].ws, p);
+    }
+}
+static void load_A(Team x, const int32_t* a, int q)
+{
+    for (int t = 0; t < 64; t++)
+        for (int k = 0; k < 16; k++) x[t][k] = (uint32_t)(a[eA(t, k)] + (int32_t)kP[q]);
+}
+static void key_to_ntt(uint32_t* dst, const uint32_t* src, int q)
+{
+    Team x;
+    for (int t = 0; t < 64; t++)
+        for (int k = 0; k < 16; k++) x[t][k] = src[eA(t, k)] % kP[q];
+    fwd(x, q);
+    for (int t = 0; t < 64; t++)
+        for (int k = 0; k < 16; k++) {
+            const int32_t m = umontmul_p(x[t][k], T.r2[q], kP[q], q ? Prime<1>::pinv : Prime<0>::pinv);
+            dst[bk16_slot(t, k)] = (uint32_t)(m + ((m >> 31) & (int32_t)kP[q]));
+        }
+}
+static int32_t mm(uint32_t a, uint32_t b, int q) { return umontmul_p(a, b, kP[q], q ? Prime<1>::pinv : Prime<0>::pinv); }
+
+// the 16-thread and the 32-thread formulations must agree position by position
+static int check_same_as_warp(std::mt19937_64& rng)
+{
+    int bad = 0;
+    for (int q = 0; q < 2; q++) {
+        uint32_t a[kN];
+        for (auto& v : a) v = (uint32_t)(rng() % kP[q]);
+        Team x;
+        for (int t = 0; t < 64; t++)
+            for (int k = 0; k < 16; k++) x[t][k] = a[eA(t, k)];
+        fwd(x, q);
+        uint32_t w[32][32];
+        for (int l = 0; l < 32; l++)
+            for (int k = 0; k < 32; k++) w[l][k] = a[l + 32 * k];
+        for (int l = 0; l < 32; l++) pass_fwd_p(w[l], T.fw1[q], 1, kP[q]);
+        {   // plain transpose (the swizzle is checked by emul_ntt.cpp)
+            uint32_t tmp[32][32];
+            for (int l = 0; l < 32; l++)
+                for (int k = 0; k < 32; k++) tmp[k][l] = w[l][k];
+            memcpy(w, tmp, sizeof w);
+        }
+        for (int l = 0; l < 32; l++) pass_fwd_p(w[l], &T.fw2[q][0][l], 32, kP[q]);
+        for (int pos = 0; pos < kN; pos++)
+            if (x[pos >> 4][pos & 15] % kP[q] != w[pos >> 5][pos & 31] % kP[q]) bad++;
+    }
+    return bad;
+}
+
+static int check_polymul(std::mt19937_64& rng, int signed_b)
+{
+    uint32_t a[kN], b[kN], ref[kN], out[kN];
+    for (int i = 0; i < kN; i++) {
+        a[i] = (uint32_t)rng();
+        b[i] = signed_b ? (uint32_t)((int)(rng() & 255) - 128) : (uint32_t)(rng() & 255);
+    }
+    orc_polymul_schoolbook(ref, a, b);
+    static uint32_t an[2][kN];
+    Team x[2];
+    int32_t bs[kN];
+    for (int i = 0; i < kN; i++) bs[i] = (int32_t)b[i];
+    for (int q = 0; q < 2; q++) {
+        key_to_ntt(an[q], a, q);
+        load_A(x[q], bs, q);
+        fwd(x[q], q);
+        for (int t = 0; t < 64; t++)
+            for (int k = 0; k < 16; k++) x[q][t][k] = (uint32_t)(mm(x[q][t][k], an[q][bk16_slot(t, k)], q) + (int32_t)kP[q]);
+        inv(x[q], q);
+    }
+    for (int t = 0; t < 64; t++)
+        for (int k = 0; k < 16; k++) out[eA(t, k)] = crt_lift32(x[0][t][k], x[1][t][k], T.crt_p0inv.w, T.crt_p0inv.ws);
+    return memcmp(out, ref, sizeof ref) != 0;
+}
+
+static int check_cmux(std::mt19937_64& rng)
+{
+    static uint32_t bk[8 * kN], bkn[2][8 * kN], acc[2 * kN], ref[2 * kN];
+    for (auto& v : bk) v = (uint32_t)rng();
+    for (auto& v : acc) v = (uint32_t)rng();
+    uint32_t abar = (uint32_t)(rng() % 2048);
+    memcpy(ref, acc, sizeof acc);
+    orc_cmux_step(ref, abar, bk, 0);
+    for (int pl = 0; pl < 8; pl++)
+        for (int q = 0; q < 2; q++) key_to_ntt(bkn[q] + pl * kN, bk + pl * kN, q);
+    static int32_t sum[2][2][64][16];   // [prime][out][T][k]
+    memset(sum, 0, sizeof sum);
+    for (int j = 0; j < 2; j++)
+        for (int d = 0; d < 2; d++) {
+            int32_t dig[kN];
+            for (uint32_t c = 0; c < (uint32_t)kN; c++) {
+                uint32_t rot = acc[j * kN + ((c - abar) & (kN - 1))];
+                if (rot_neg(c, abar)) rot = 0u - rot;
+                dig[c] = digit(rot - acc[j * kN + c] + kDecompAdd, d);
+            }
+            const int row = 2 * j + d;
+            for (int q = 0; q < 2; q++) {
+                Team x;
+                load_A(x, dig, q);
+                fwd(x, q);
+                for (int o = 0; o < 2; o++)
+                    for (int t = 0; t < 64; t++)
+                        for (int k = 0; k < 16; k++)
+                            sum[q][o][t][k] += mm(x[t][k], bkn[q][(2 * row + o) * kN + bk16_slot(t, k)], q);
+            }
+        }
+    for (int o = 0; o < 2; o++) {
+        Team y[2];
+        for (int q = 0; q < 2; q++) {
+            for (int t = 0; t < 64; t++)
+                for (int k = 0; k < 16; k++) y[q][t][k] = (uint32_t)(sum[q][o][t][k] + 4 * (int32_t)kP[q]);
+            inv(y[q], q);
+        }
+        for (int t = 0; t < 64; t++)
+            for (int k = 0; k < 16; k++)
+                acc[o * kN + eA(t, k)] += crt_lift32(y[0][t][k], y[1][t][k], T.crt_p0inv.w, T.crt_p0inv.ws);
+    }
+    return memcmp(acc, ref, sizeof ref) != 0;
+}
+
+int main(int argc, char** argv)
+{
+    make_tables(T);
+    make_tables16(L);
+    std::mt19937_64 rng(20261104);
+    int trials = argc > 1 ? atoi(argv[1]) : 20;
+    int bad0 = check_same_as_warp(rng);
+    printf("position mismatches vs 32-coefficient transform: %d\n", bad0);
+    int bad = 0, bad2 = 0;
+    for (int i = 0; i < trials; i++) bad += check_polymul(rng, i & 1);
+    printf("polymul mismatches: %d / %d\n", bad, trials);
+    for (int i = 0; i < trials; i++) bad2 += check_cmux(rng);
+    printf("cmux mismatches: %d / %d\n", bad2, trials);
+    printf("bank conflicts: %d\n", g_conflicts);
+    return (bad0 || bad || bad2 || g_conflicts) ? 1 : 0;
+}

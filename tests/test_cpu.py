@@ -92,6 +92,21 @@ def test_warp_emulation_of_cuda_ntt_and_cmux(tmp_path):
     assert "polymul mismatches: 0 / 6" in out and "cmux mismatches: 0 / 6" in out
 
 
+def test_team_emulation_of_16_coefficient_ntt_and_cmux(tmp_path):
+    """Same for the 64-thread x 16-coefficient team formulation (csrc/ntt16.cuh) behind
+    k_blind_rotate16: three passes, two padded exchanges; also checks that every exchange
+    access pattern is shared-memory bank-conflict free."""
+    orc.build()
+    exe = str(tmp_path / "emul_ntt16")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "emul", "emul_ntt16.cpp"),
+                           "-L" + os.path.join(ROOT, "oracle"), "-lorc", "-Wl,-rpath," + os.path.join(ROOT, "oracle"),
+                           "-fopenmp"])
+    out = subprocess.check_output([exe, "6"]).decode()
+    assert "position mismatches vs 32-coefficient transform: 0" in out
+    assert "polymul mismatches: 0 / 6" in out and "cmux mismatches: 0 / 6" in out
+    assert "bank conflicts: 0" in out
+
+
 # -------------------------------------------------------------- host logic ---
 def test_partition_covers_batch():
     from cufhe_b200.api import partition
