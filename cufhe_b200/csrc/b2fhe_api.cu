@@ -10,6 +10,7 @@
 
 #include "../../include/b2fhe.h"
 #include "k_blindrotate.cuh"
+#include "k_blindrotate16.cuh"
 #include "k_keyswitch.cuh"
 #include "k_ntt.cuh"
 
@@ -24,11 +25,14 @@ struct DevCtx {
     uint32_t* bk_ntt = nullptr;     // [636][4][2 primes][2][1024] Montgomery residues
     uint32_t* ksk = nullptr;        // T[1024][7][3][320]
     LaneTables* tab = nullptr;
+    uint32_t* bk_ntt16 = nullptr;   // same key in bk16_slot order (k_blind_rotate16), built lazily
+    Lane16Tables* tab16 = nullptr;
     int sm_count = 0;
 };
 DevCtx g_ctx[kMaxDev];
 std::mutex g_mu;
 int g_gates_per_cta = 0;
+int g_br_variant = 0;            // 0 = default, 16 = k_blind_rotate16, 32 = k_blind_rotate
 std::atomic<uint64_t> g_launches{0};
 thread_local std::string t_err;
 
@@ -56,6 +60,11 @@ template <int G> int set_br_attr()
     CK(cudaFuncSetAttribute(k_blind_rotate<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, br_smem_bytes(G)));
     return 0;
 }
+template <int G> int set_br16_attr()
+{
+    CK(cudaFuncSetAttribute(k_blind_rotate16<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
+    return 0;
+}
 
 // twiddle tables + kernel attributes on `device` (InitializeNTThandlers, src/bootstrap_gpu.cu:97-109)
 int setup_device(int device)
@@ -79,6 +88,10 @@ int setup_device(int device)
     memcpy(L.scale, T.scale, sizeof L.scale);
     CK(cudaMalloc(&c.tab, sizeof(LaneTables)));
     CK(cudaMemcpy(c.tab, &L, sizeof L, cudaMemcpyHostToDevice));
+    static Lane16Tables L16;
+    make_tables16(L16);
+    CK(cudaMalloc(&c.tab16, sizeof(Lane16Tables)));
+    CK(cudaMemcpy(c.tab16, &L16, sizeof L16, cudaMemcpyHostToDevice));
     CK(cudaDeviceGetAttribute(&c.sm_count, cudaDevAttrMultiProcessorCount, device));
     // keep stream-ordered scratch cached between calls
     cudaMemPool_t pool;
@@ -90,6 +103,12 @@ int setup_device(int device)
     if (int r = set_br_attr<4>()) return r;
     if (int r = set_br_attr<6>()) return r;
     if (int r = set_br_attr<8>()) return r;
+    if (int r = set_br16_attr<1>()) return r;
+    if (int r = set_br16_attr<2>()) return r;
+    if (int r = set_br16_attr<3>()) return r;
+    if (int r = set_br16_attr<4>()) return r;
+    if (int r = set_br16_attr<5>()) return r;
+    if (int r = set_br16_attr<6>()) return r;
     CK(cudaFuncSetAttribute(k_ntt_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
     CK(cudaFuncSetAttribute(k_ntt_inv, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
     CK(cudaFuncSetAttribute(k_polymul, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
@@ -101,6 +120,18 @@ int ntt_grid(const DevCtx& c, size_t npoly)
     size_t blocks = (npoly + kNttPolysPerCta - 1) / kNttPolysPerCta;
     size_t cap = (size_t)c.sm_count * 16;
     return (int)(blocks < cap ? (blocks ? blocks : 1) : cap);
+}
+
+// the key in k_blind_rotate16's storage order, permuted on the device from the
+// 32-coefficient order (which stays the interchange format of b2fhe_key_pointers/adopt_keys)
+int build_bk16(DevCtx& c)
+{
+    if (!c.bk_ntt16) CK(cudaMalloc(&c.bk_ntt16, B2FHE_BK_NTT_BYTES));
+    const size_t npoly = (size_t)kLwe * kRows * 2 * 2;
+    k_bk_to_layout16<<<c.sm_count * 8, 256>>>(c.bk_ntt, c.bk_ntt16, npoly);
+    LAUNCHED();
+    CK(cudaDeviceSynchronize());
+    return 0;
 }
 
 // BootstrappingKeyToNTT + KeySwitchingKeyToDevice on one device (src/bootstrap_gpu.cu:111-138,
@@ -126,6 +157,7 @@ int convert_keys(int device, const uint32_t* bk_raw, const uint16_t* ksk_raw)
     CK(cudaDeviceSynchronize());
     CK(cudaFree(d_raw));
     CK(cudaFree(d_kraw));
+    if (int r = build_bk16(c)) return r;
     c.ready = true;
     return 0;
 }
@@ -147,8 +179,14 @@ const char* b2fhe_last_error_string(void) { return t_err.c_str(); }
 uint64_t b2fhe_kernel_launches(void) { return g_launches.load(); }
 int b2fhe_set_gates_per_cta(int gates)
 {
-    REQUIRE(gates == 0 || gates == 1 || gates == 2 || gates == 4 || gates == 6 || gates == 8, B2FHE_E_BAD_ARGUMENT);
+    REQUIRE(gates >= 0 && gates <= 8, B2FHE_E_BAD_ARGUMENT);
     g_gates_per_cta = gates;
+    return 0;
+}
+int b2fhe_set_br_variant(int variant)
+{
+    REQUIRE(variant == 0 || variant == 16 || variant == 32, B2FHE_E_BAD_ARGUMENT);
+    g_br_variant = variant;
     return 0;
 }
 int b2fhe_num_devices(void)
@@ -186,6 +224,7 @@ int b2fhe_init(int ngpu, const uint32_t* bk_raw, const uint16_t* ksk_raw)
         c.owns_keys = true;
         CK(cudaMemcpyPeer(c.bk_ntt, d, g_ctx[0].bk_ntt, 0, B2FHE_BK_NTT_BYTES));
         CK(cudaMemcpyPeer(c.ksk, d, g_ctx[0].ksk, 0, B2FHE_KSK_DEV_BYTES));
+        if (int r = build_bk16(c)) return r;
         c.ready = true;
     }
     return 0;
@@ -201,6 +240,8 @@ int b2fhe_adopt_keys(int device, const void* bk_ntt_dev, const void* ksk_dev)
     c.bk_ntt = (uint32_t*)bk_ntt_dev;
     c.ksk = (uint32_t*)ksk_dev;
     c.owns_keys = false;
+    CK(cudaSetDevice(device));
+    if (int r = build_bk16(c)) return r;
     c.ready = true;
     return 0;
 }
@@ -224,6 +265,8 @@ int b2fhe_cleanup(void)
         CK(cudaDeviceSynchronize());
         if (c.owns_keys) { CK(cudaFree(c.bk_ntt)); CK(cudaFree(c.ksk)); }
         if (c.tab) CK(cudaFree(c.tab));
+        if (c.tab16) CK(cudaFree(c.tab16));
+        if (c.bk_ntt16) CK(cudaFree(c.bk_ntt16));
         c = DevCtx();
     }
     return 0;

@@ -11,17 +11,35 @@ template <int G> int launch_br_g(const BrParams& P, cudaStream_t st)
     LAUNCHED();
     return 0;
 }
+template <int G> int launch_br16_g(const DevCtx& c, const BrParams& P, cudaStream_t st)
+{
+    const int grid = (P.count + G - 1) / G;
+    k_blind_rotate16<G><<<grid, 128 * G, br16_smem_bytes(G), st>>>(P, c.tab16);
+    LAUNCHED();
+    return 0;
+}
 int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
 {
     if (P.count <= 0) return 0;
+    const int variant = g_br_variant ? g_br_variant : 16;
+    int g = g_gates_per_cta;
+    const int per_sm = (P.count + c.sm_count - 1) / c.sm_count;
+    if (variant == 16) {
+        P.bk = c.bk_ntt16;
+        // spread small batches over all SMs; large batches use the widest CTA
+        if (g == 0) g = per_sm >= 6 ? 6 : per_sm >= 1 ? per_sm : 1;
+        switch (g) {
+            case 1: return launch_br16_g<1>(c, P, st);
+            case 2: return launch_br16_g<2>(c, P, st);
+            case 3: return launch_br16_g<3>(c, P, st);
+            case 4: return launch_br16_g<4>(c, P, st);
+            case 5: return launch_br16_g<5>(c, P, st);
+            default: return launch_br16_g<6>(c, P, st);
+        }
+    }
     P.bk = c.bk_ntt;
     P.tab = c.tab;
-    int g = g_gates_per_cta;
-    if (g == 0) {
-        // spread small batches over all SMs; large batches use the widest CTA
-        const int per_sm = (P.count + c.sm_count - 1) / c.sm_count;
-        g = per_sm >= 6 ? 6 : per_sm >= 4 ? 4 : per_sm >= 2 ? 2 : 1;
-    }
+    if (g == 0) g = per_sm >= 6 ? 6 : per_sm >= 4 ? 4 : per_sm >= 2 ? 2 : 1;
     switch (g) {
         case 1: return launch_br_g<1>(P, st);
         case 2: return launch_br_g<2>(P, st);

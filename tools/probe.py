@@ -43,11 +43,14 @@ x0 = torch.from_numpy(rng.integers(0, 2**16, (cnt, 637), dtype=np.uint64).astype
 x1 = torch.from_numpy(rng.integers(0, 2**16, (cnt, 637), dtype=np.uint64).astype(np.uint16).view(np.int16)).cuda()
 e = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
 out = torch.empty_like(x0)
-for g in (4, 6, 8):
-    cf._lib.check(L.b2fhe_set_gates_per_cta(g))
-    best, med = timed(lambda: cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, e.data_ptr(), x0.data_ptr(), 1 << 29, cnt)))
-    print(json.dumps({"probe": "blind_rotate", "gates_per_cta": g, "count": cnt, "ms_best": best, "ms_med": med,
-                      "gates_per_s": cnt / best * 1e3}), flush=True)
+for variant, gs in ((32, (6,)), (16, (3, 4, 5, 6))):
+    cf._lib.check(L.b2fhe_set_br_variant(variant))
+    for g in gs:
+        cf._lib.check(L.b2fhe_set_gates_per_cta(g))
+        best, med = timed(lambda: cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, e.data_ptr(), x0.data_ptr(), 1 << 29, cnt)))
+        print(json.dumps({"probe": "blind_rotate", "variant": variant, "gates_per_cta": g, "count": cnt, "ms_best": best,
+                          "ms_med": med, "gates_per_s": cnt / best * 1e3}), flush=True)
+cf._lib.check(L.b2fhe_set_br_variant(0))
 cf._lib.check(L.b2fhe_set_gates_per_cta(0))
 best, med = timed(lambda: cf._lib.check(L.b2fhe_keyswitch_batch(0, None, out.data_ptr(), e.data_ptr(), cnt)))
 print(json.dumps({"probe": "keyswitch", "count": cnt, "ms_best": best, "gates_per_s": cnt / best * 1e3}), flush=True)
