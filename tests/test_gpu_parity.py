@@ -101,15 +101,20 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     d0 = torch.from_numpy(c0.view(np.int16)).cuda()
     d1 = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
     refs = [orc.blind_rotate_extract(keys, c0[i]) for i in range(cnt)]
-    for g in (0, 1, 2, 4, 6, 8):
-        cf._lib.check(L.b2fhe_set_gates_per_cta(g))
-        d1.zero_()
-        cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, d1.data_ptr(), d0.data_ptr(), 1 << 29, cnt))
-        torch.cuda.synchronize()
-        got = to_np(d1, np.uint32)
-        for i in range(cnt):
-            assert np.array_equal(got[i], refs[i]), f"gates/cta {g}, item {i}"
+    # both blind-rotation kernels (16 = 128 threads/gate, the default; 32 = 64 threads/gate),
+    # every gates-per-CTA instantiation
+    for variant, gs in ((16, (0, 1, 2, 3, 4, 5, 6)), (32, (0, 1, 2, 4, 6, 8))):
+        cf._lib.check(L.b2fhe_set_br_variant(variant))
+        for g in gs:
+            cf._lib.check(L.b2fhe_set_gates_per_cta(g))
+            d1.zero_()
+            cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, d1.data_ptr(), d0.data_ptr(), 1 << 29, cnt))
+            torch.cuda.synchronize()
+            got = to_np(d1, np.uint32)
+            for i in range(cnt):
+                assert np.array_equal(got[i], refs[i]), f"variant {variant}, gates/cta {g}, item {i}"
     cf._lib.check(L.b2fhe_set_gates_per_cta(0))
+    cf._lib.check(L.b2fhe_set_br_variant(0))
     # key switch of those lvl1 outputs (+ an extreme input)
     x = got.copy()
     x[5, :] = 0xFFFFFFFF
