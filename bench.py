@@ -31,6 +31,10 @@ METRIC = "gate_bootstraps_per_sec_nand_batched"
 UNIT = "gates/s"
 # algorithmic figures per NAND bootstrap
 KEY_BYTES_PER_GATE = 41_680_896            # NTT-domain bootstrapping key touched per gate
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE k_blind_rotate16<4> launch over 16384 gates
+# (profiles/r1_ncu_traffic_k_blind_rotate16_16384.csv): keys once + ciphertext I/O, far below the
+# algorithmic key bytes because each key row is served to all gates from L2
+DRAM_TRAFFIC_PER_LAUNCH = 68_316_928 + 48_672_768
 # integer multiply-pipe slots per gate of OUR formulation (DESIGN.md "integer roofline")
 IMAD_SLOTS_PER_GATE = 636 * 2 * (6 * 5120 * 4 + 2 * 1024 * 4 + 8192 * 5 + 1024 * 5)
 
@@ -230,8 +234,8 @@ def run_product(args):
             "gpu_launches": int(launches),
             "clocks": summarize_clocks(samples),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved / hbm_peak, "traffic": None,
-                         "kernel": "k_blind_rotate", "kernel_ms": br_s * 1e3,
+                         "frac": achieved / hbm_peak, "traffic": DRAM_TRAFFIC_PER_LAUNCH if cnt == GATES_PER_GPU else None,
+                         "kernel": "k_blind_rotate16<4>", "kernel_ms": br_s * 1e3,
                          "note": "algorithmic key bytes (41.68 MB x gates per launch) / kernel time, against the "
                                  "MEASURED HBM copy peak; the batch-major kernel serves each key row to all gates of "
                                  "a CTA from L1/L2, so this exceeds 1 by design -- the binding resource is the "
