@@ -24,7 +24,7 @@ SYMBOLS = [
     "b2fhe_num_devices", "b2fhe_last_error_string", "b2fhe_gate_batch", "b2fhe_gate_batch_mixed",
     "b2fhe_gate_batch_host", "b2fhe_synchronize", "b2fhe_blind_rotate_batch", "b2fhe_keyswitch_batch",
     "b2fhe_ntt1024_batch", "b2fhe_intt1024_batch", "b2fhe_polymul1024_batch",
-    "b2fhe_set_gates_per_cta", "b2fhe_set_br_variant", "b2fhe_kernel_launches", "b2fhe_int_peak",
+    "b2fhe_set_gates_per_cta", "b2fhe_set_br_variant", "b2fhe_set_ks_variant", "b2fhe_kernel_launches", "b2fhe_int_peak",
 ]
 
 
@@ -72,6 +72,7 @@ def lib():
     L.b2fhe_polymul1024_batch.argtypes = [i32, vp, vp, vp, vp, sz]
     L.b2fhe_set_gates_per_cta.argtypes = [i32]
     L.b2fhe_set_br_variant.argtypes = [i32]
+    L.b2fhe_set_ks_variant.argtypes = [i32]
     L.b2fhe_kernel_launches.restype = C.c_uint64
     L.b2fhe_int_peak.argtypes = [i32, i32, C.POINTER(C.c_double)]
     _lib = L

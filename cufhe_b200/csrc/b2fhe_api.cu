@@ -11,6 +11,7 @@
 #include "../../include/b2fhe.h"
 #include "k_blindrotate.cuh"
 #include "k_blindrotate16.cuh"
+#include "k_blindrotate_lat.cuh"
 #include "k_keyswitch.cuh"
 #include "k_ntt.cuh"
 
@@ -32,7 +33,9 @@ struct DevCtx {
 DevCtx g_ctx[kMaxDev];
 std::mutex g_mu;
 int g_gates_per_cta = 0;
-int g_br_variant = 0;            // 0 = default, 16 = k_blind_rotate16, 32 = k_blind_rotate
+int g_ks_variant = 0;            // 0 = by batch size, 1 = k_keyswitch_lat, 2 = k_keyswitch
+int g_ks_lat_max_per_sm = 32;    // k_keyswitch_lat up to this many gates per SM (measured faster up to there)
+int g_br_variant = 0;            // 0 = default, 1 = k_blind_rotate_lat, 16 = k_blind_rotate16, 32 = k_blind_rotate
 std::atomic<uint64_t> g_launches{0};
 thread_local std::string t_err;
 
@@ -103,6 +106,7 @@ int setup_device(int device)
     if (int r = set_br_attr<4>()) return r;
     if (int r = set_br_attr<6>()) return r;
     if (int r = set_br_attr<8>()) return r;
+    CK(cudaFuncSetAttribute(k_blind_rotate_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatSmemBytes));
     if (int r = set_br16_attr<1>()) return r;
     if (int r = set_br16_attr<2>()) return r;
     if (int r = set_br16_attr<3>()) return r;
@@ -183,9 +187,15 @@ int b2fhe_set_gates_per_cta(int gates)
     g_gates_per_cta = gates;
     return 0;
 }
+int b2fhe_set_ks_variant(int variant)
+{
+    REQUIRE(variant >= 0 && variant <= 2, B2FHE_E_BAD_ARGUMENT);
+    g_ks_variant = variant;
+    return 0;
+}
 int b2fhe_set_br_variant(int variant)
 {
-    REQUIRE(variant == 0 || variant == 16 || variant == 32, B2FHE_E_BAD_ARGUMENT);
+    REQUIRE(variant == 0 || variant == 1 || variant == 16 || variant == 32, B2FHE_E_BAD_ARGUMENT);
     g_br_variant = variant;
     return 0;
 }

@@ -24,6 +24,14 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
     const int variant = g_br_variant ? g_br_variant : 16;
     int g = g_gates_per_cta;
     const int per_sm = (P.count + c.sm_count - 1) / c.sm_count;
+    // small batches (<= 1 gate per SM; measured faster than k_blind_rotate16 only there): one gate per 512-thread CTA, 1 + 1 transforms on the
+    // critical path of a CMUX step instead of 4 + 2
+    if (variant == 1 || (g_br_variant == 0 && g == 0 && per_sm <= 1)) {
+        P.bk = c.bk_ntt16;
+        k_blind_rotate_lat<<<P.count, kLatThreads, kLatSmemBytes, st>>>(P, c.tab16);
+        LAUNCHED();
+        return 0;
+    }
     if (variant == 16) {
         P.bk = c.bk_ntt16;
         // spread small batches over all SMs; large batches use the widest CTA
@@ -52,6 +60,12 @@ int launch_ks(const DevCtx& c, KsParams P, cudaStream_t st)
 {
     if (P.count <= 0) return 0;
     P.T = c.ksk;
+    if (g_ks_variant == 1 || (g_ks_variant == 0 && P.count <= g_ks_lat_max_per_sm * c.sm_count)) {
+        // small batch: 16 warps per gate instead of one
+        k_keyswitch_lat<<<P.count, 32 * kKsLatWarps, 0, st>>>(P);
+        LAUNCHED();
+        return 0;
+    }
     k_keyswitch<<<(P.count + kKsGates - 1) / kKsGates, 32 * kKsGates, 0, st>>>(P);
     LAUNCHED();
     return 0;

@@ -60,18 +60,18 @@ __device__ __forceinline__ X16 make_x16(int T)
 // forward transform: layout A in, layout C out.  bufA / bufB: the team's two exchange
 // buffers; `bar` = the gate's named barrier (all 128 threads of the gate call this).
 __device__ __forceinline__ void fwd16(uint32_t (&x)[16], uint32_t* bufA, uint32_t* bufB, const uint32_t* s_tab,
-                                      const X16& a, int T, int q, uint32_t p, int bar)
+                                      const X16& a, int T, int q, uint32_t p, int bar, int barn = 128)
 {
     pass16_fwd<4, 8>(x, c_fw1[q], 1, p);
 #pragma unroll
     for (int k = 0; k < 16; k++) bufA[a.wA + 68 * k] = x[k];
-    named_bar_sync(bar, 128);
+    named_bar_sync(bar, barn);
 #pragma unroll
     for (int k = 0; k < 16; k++) x[k] = bufA[a.rB + 4 * k];
     pass16_fwd<4, 8>(x, t16_fw2(s_tab, q, T >> 2), 16, p);
 #pragma unroll
     for (int k = 0; k < 16; k++) bufB[a.wB + 4 * k + (k >> 2)] = x[k];
-    named_bar_sync(bar, 128);
+    named_bar_sync(bar, barn);
 #pragma unroll
     for (int k = 0; k < 16; k++) x[k] = bufB[a.rC + k];
     pass16_fwd3(x, t16_fw3(s_tab, q, T), 64, p);
@@ -79,18 +79,18 @@ __device__ __forceinline__ void fwd16(uint32_t (&x)[16], uint32_t* bufA, uint32_
 
 // inverse transform incl. n^-1 psi^-e scaling: layout C in, layout A out, values in [0, 2p)
 __device__ __forceinline__ void inv16(uint32_t (&x)[16], uint32_t* bufA, uint32_t* bufB, const uint32_t* s_tab,
-                                      const X16& a, int T, int q, uint32_t p, int bar)
+                                      const X16& a, int T, int q, uint32_t p, int bar, int barn = 128)
 {
     pass16_inv<true>(x, c_iv1[q], 1, p);
 #pragma unroll
     for (int k = 0; k < 16; k++) bufA[a.rC + k] = x[k];
-    named_bar_sync(bar, 128);
+    named_bar_sync(bar, barn);
 #pragma unroll
     for (int k = 0; k < 16; k++) x[k] = bufA[a.rD + 17 * k];
     pass16_inv<false>(x, t16_iv2(s_tab, q, T & 15), 16, p);
 #pragma unroll
     for (int k = 0; k < 16; k++) bufB[a.wD + 16 * k] = x[k];
-    named_bar_sync(bar, 128);
+    named_bar_sync(bar, barn);
 #pragma unroll
     for (int k = 0; k < 16; k++) x[k] = bufB[T + 64 * k + 16 * (k >> 2)];
     pass16_inv3(x, t16_iv3(s_tab, q, T), 64, p);

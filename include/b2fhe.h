@@ -104,9 +104,13 @@ int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, co
 
 /* tuning / introspection */
 int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
-/* blind-rotation kernel: 0 = default (16), 16 = k_blind_rotate16 (128 threads x 16
- * coefficients per gate), 32 = k_blind_rotate (64 threads x 32 coefficients per gate) */
+/* blind-rotation kernel: 0 = default (k_blind_rotate_lat for batches of at most 2 gates per
+ * SM, else k_blind_rotate16), 1 = k_blind_rotate_lat (one gate per 512-thread CTA), 16 =
+ * k_blind_rotate16 (128 threads x 16 coefficients per gate), 32 = k_blind_rotate (64 threads
+ * x 32 coefficients per gate).  All produce identical bits. */
 int b2fhe_set_br_variant(int variant);
+/* key-switch kernel: 0 = by batch size, 1 = k_keyswitch_lat (16 warps per gate), 2 = k_keyswitch */
+int b2fhe_set_ks_variant(int variant);
 uint64_t b2fhe_kernel_launches(void);             /* kernels launched by this library so far */
 /* measured integer-pipe ceiling of `device` (register-only probe kernel): mode 0 = 1e9
  * 32-bit IMAD lane-ops/s, mode 1 = 1e9 Montgomery butterflies/s (the NTT's instruction mix) */

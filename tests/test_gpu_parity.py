@@ -101,9 +101,9 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     d0 = torch.from_numpy(c0.view(np.int16)).cuda()
     d1 = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
     refs = [orc.blind_rotate_extract(keys, c0[i]) for i in range(cnt)]
-    # both blind-rotation kernels (16 = 128 threads/gate, the default; 32 = 64 threads/gate),
+    # all blind-rotation kernels (1 = latency kernel, 16 = 128 threads/gate, 32 = 64 threads/gate),
     # every gates-per-CTA instantiation
-    for variant, gs in ((16, (0, 1, 2, 3, 4, 5, 6)), (32, (0, 1, 2, 4, 6, 8))):
+    for variant, gs in ((1, (0,)), (16, (0, 1, 2, 3, 4, 5, 6)), (32, (0, 1, 2, 4, 6, 8))):
         cf._lib.check(L.b2fhe_set_br_variant(variant))
         for g in gs:
             cf._lib.check(L.b2fhe_set_gates_per_cta(g))
@@ -121,11 +121,15 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     x[6, :] = 0
     dx = dev_u32(x)
     dks = torch.empty((cnt, 637), dtype=torch.int16, device="cuda")
-    cf._lib.check(L.b2fhe_keyswitch_batch(0, None, dks.data_ptr(), dx.data_ptr(), cnt))
-    torch.cuda.synchronize()
-    gk = to_np(dks, np.uint16)
-    for i in range(cnt):
-        assert np.array_equal(gk[i], orc.keyswitch(keys, x[i])), i
+    want = [orc.keyswitch(keys, x[i]) for i in range(cnt)]
+    for ks_variant in (1, 2, 0):        # 16 warps per gate / one warp per gate / by batch size
+        cf._lib.check(L.b2fhe_set_ks_variant(ks_variant))
+        dks.zero_()
+        cf._lib.check(L.b2fhe_keyswitch_batch(0, None, dks.data_ptr(), dx.data_ptr(), cnt))
+        torch.cuda.synchronize()
+        gk = to_np(dks, np.uint16)
+        for i in range(cnt):
+            assert np.array_equal(gk[i], want[i]), (ks_variant, i)
 
 
 # ------------------------------------------------------------------- gates ---

@@ -56,9 +56,12 @@ best, med = timed(lambda: cf._lib.check(L.b2fhe_keyswitch_batch(0, None, out.dat
 print(json.dumps({"probe": "keyswitch", "count": cnt, "ms_best": best, "gates_per_s": cnt / best * 1e3}), flush=True)
 best, med = timed(lambda: cf._lib.check(L.b2fhe_gate_batch(0, None, 0, 0, out.data_ptr(), x0.data_ptr(), x1.data_ptr(), None, cnt)))
 print(json.dumps({"probe": "nand_lvl0", "count": cnt, "ms_best": best, "gates_per_s": cnt / best * 1e3}), flush=True)
-for small in (1, 148, 148 * 6):
-    best, med = timed(lambda: cf._lib.check(L.b2fhe_gate_batch(0, None, 0, 0, out.data_ptr(), x0.data_ptr(), x1.data_ptr(), None, small)))
-    print(json.dumps({"probe": "nand_lvl0", "count": small, "ms_best": best, "gates_per_s": small / best * 1e3}), flush=True)
+for small in (1, 148, 296, 444, 592, 148 * 6):
+    for variant in (1, 16):
+        cf._lib.check(L.b2fhe_set_br_variant(variant))
+        best, med = timed(lambda: cf._lib.check(L.b2fhe_gate_batch(0, None, 0, 0, out.data_ptr(), x0.data_ptr(), x1.data_ptr(), None, small)))
+        print(json.dumps({"probe": "nand_lvl0", "variant": variant, "count": small, "ms_best": best, "gates_per_s": small / best * 1e3}), flush=True)
+cf._lib.check(L.b2fhe_set_br_variant(0))
 
 npoly = 65536
 a = torch.randint(-2**31, 2**31 - 1, (npoly, 1024), dtype=torch.int32, device="cuda")
