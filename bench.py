@@ -272,16 +272,158 @@ def run_product(args):
         real_stdout.flush()
 
 
+def run_extra(args):
+    """BASELINE configs 4 and 5 (not the default bench line): --workload mixed = all 14 ops
+    over one batch of 2^18 gates, --workload adder = 32-bit ripple-carry adder over 2^14
+    instances; the batch / the instances are partitioned across ranks (strong scaling)."""
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    import numpy as np
+    import torch
+    import cufhe_b200 as cf
+    from cufhe_b200 import circuits
+    L = cf._lib.lib()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    rng = np.random.default_rng(1234)
+    bk = ksk = None
+    if rank == 0 or world == 1:
+        bk = rng.integers(0, 2**32, cf.api.BK_RAW_WORDS, dtype=np.uint64).astype(np.uint32)
+        ksk = rng.integers(0, 2**16, cf.api.KSK_RAW_WORDS, dtype=np.uint64).astype(np.uint16)
+    if world > 1:
+        keep = cf.InitializeBroadcast(bk, ksk, device=local, src=0)  # noqa: F841
+    else:
+        cf.SetGPUNum(1)
+        cf.Initialize(bk, ksk, device=local)
+    st = torch.cuda.current_stream(dev)
+    sp = st.cuda_stream
+    rng = np.random.default_rng(99 + rank)
+
+    def rand_ct(*lead):
+        a = rng.integers(0, 2**16, (*lead, cf.api.LVL0_WORDS), dtype=np.uint64).astype(np.uint16).view(np.int16)
+        return torch.from_numpy(a).pin_memory()
+
+    if args.workload == "mixed":
+        total = args.gates if args.gates != GATES_PER_GPU else 1 << 18
+        b, e = cf.api.partition(total, world, rank)
+        cnt = e - b
+        ops = (np.arange(b, e) % 14).astype(np.uint8)              # NAND .. COPY round-robin
+        h = [rand_ct(cnt) for _ in range(3)]
+        hout = torch.empty_like(h[0]).pin_memory()
+        d = [x.to(dev) for x in h]
+        dout = torch.empty_like(d[0])
+        boots = int(np.sum(np.where(ops >= 12, 0, np.where(ops >= 10, 2, 1))))
+        units, unit_name = total, "gates"
+        desc = f"all 13 gates + NMux round-robin over one batch of {total} gates (BASELINE config 4), lvl0 I/O"
+
+        def step_dev():
+            cf._lib.check(L.b2fhe_gate_batch_mixed(local, sp, ops.ctypes.data, 0, dout.data_ptr(), d[0].data_ptr(),
+                                                   d[1].data_ptr(), d[2].data_ptr(), cnt))
+
+        def step_host():
+            cf._lib.check(L.b2fhe_gate_batch_host(local, sp, 0, ops.ctypes.data, 0, hout.data_ptr(), h[0].data_ptr(),
+                                                  h[1].data_ptr(), h[2].data_ptr(), cnt))
+        h2d, d2h = 3 * total * 1274, total * 1274
+        extra = {"bootstraps_per_step_this_rank": boots}
+    else:
+        total = args.gates if args.gates != GATES_PER_GPU else 1 << 14
+        b, e = cf.api.partition(total, world, rank)
+        inst, nbits = e - b, 32
+        ha, hb = rand_ct(nbits, inst), rand_ct(nbits, inst)
+        hs = torch.empty_like(ha).pin_memory()
+        wa, wb = circuits.Wires(nbits, inst, 0, local), circuits.Wires(nbits, inst, 0, local)
+        wa.t.copy_(ha)
+        wb.t.copy_(hb)
+        stream = cf.Stream(local)
+        stream._st = st                                              # run on torch's current stream
+        units, unit_name = total * circuits.adder_gate_count(nbits), "gates"
+        desc = (f"32-bit ripple-carry adder over {total} instances (BASELINE config 5): "
+                f"{circuits.adder_gate_count(nbits)} bootstraps per instance in 65 batched levels, device-resident")
+
+        def step_dev():
+            circuits.ripple_carry_add(wa, wb, stream)
+
+        def step_host():
+            wa.t.copy_(ha, non_blocking=True)
+            wb.t.copy_(hb, non_blocking=True)
+            s, _ = circuits.ripple_carry_add(wa, wb, stream)
+            hs.copy_(s.t, non_blocking=True)
+        h2d, d2h = 2 * nbits * total * 1274, nbits * total * 1274
+        extra = {"levels": 65}
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        a, bq = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(st)
+        for _ in range(steps):
+            fn()
+        bq.record(st)
+        bq.synchronize()
+        total_ms = a.elapsed_time(bq)
+        barrier()
+        if dist is not None:
+            t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            total_ms = float(t.item())
+        return total_ms
+
+    stop, samples = threading.Event(), []
+    th = threading.Thread(target=clocks_sampler, args=(stop, samples), daemon=True)
+    th.start()
+    l0 = L.b2fhe_kernel_launches()
+    ms = timed(step_dev, args.steps, args.warmup)
+    launches = (L.b2fhe_kernel_launches() - l0) * args.steps // (args.steps + args.warmup)
+    ms_e2e = timed(step_host, args.steps, 1)
+    stop.set()
+    th.join()
+    if rank == 0:
+        line = {"metric": METRIC.replace("nand_batched", args.workload), "value": units * args.steps / (ms * 1e-3),
+                "unit": f"{unit_name}/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "u32", "data": "synthetic",
+                "config": {"workload": desc, "l2": "working set per step exceeds L2 (inputs > 126 MB)", **extra},
+                "e2e": {"value": units * args.steps / (ms_e2e * 1e-3), "unit": f"{unit_name}/s",
+                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                "gpu_launches": int(launches), "clocks": summarize_clocks(samples)}
+        real_stdout.write(json.dumps(line) + "\n")
+        real_stdout.flush()
+    cf.CleanUp()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b2fhe", choices=["b2fhe", "reference"])
-    ap.add_argument("--gates", type=int, default=GATES_PER_GPU, help="gates per GPU per step")
+    ap.add_argument("--gates", type=int, default=GATES_PER_GPU, help="gates per GPU per step (nand); total gates "
+                    "(mixed) / total instances (adder)")
+    ap.add_argument("--workload", default="nand", choices=["nand", "mixed", "adder"],
+                    help="nand = BASELINE config 3 (the bench line); mixed = config 4; adder = config 5")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload != "nand":
+        run_extra(args)
     else:
         run_product(args)
 
