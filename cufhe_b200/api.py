@@ -278,6 +278,64 @@ def gGateMixed(ops, out, in0, in1, in2, st):
         out.device, st.st(), ops.ctypes.data, out.level, out.ptr(), in0.ptr(), in1.ptr(), in2.ptr(), out.count))
 
 
+class cuFHETRLWElvl1:
+    """A batch of TRLWE<lvl1param> ([a(X)][b(X)], 2 x 1024 u32): pinned host array + device
+    buffer (cufhe::cuFHETRLWElvl1, include/cufhe_gpu.cuh:123-134)."""
+
+    def __init__(self, count, device=0):
+        self.count, self.device = int(count), int(device)
+        self._host_t = torch.empty((self.count, 2 * 1024), dtype=torch.int32).pin_memory()
+        self.trlwehost = self._host_t.numpy().view(np.uint32)
+        self.trlwedevice = torch.empty((self.count, 2 * 1024), dtype=torch.int32, device=torch.device("cuda", self.device))
+
+    def set(self, array):
+        self.trlwehost[...] = np.asarray(array, dtype=np.uint32).reshape(self.trlwehost.shape)
+        return self
+
+    def ptr(self):
+        return self.trlwedevice.data_ptr()
+
+
+def gGateBootstrappingTLWE2TRLWElvl01NTT(out, in0, st, mu=1 << 29):
+    """cufhe::gGateBootstrappingTLWE2TRLWElvl01NTT (src/cufhe_gates_gpu.cu:101-108)."""
+    _lib.check(_lib.lib().b2fhe_bootstrap_tlwe2trlwe_batch(out.device, st.st(), out.ptr(), in0.ptr(), mu, out.count))
+
+
+def GateBootstrappingTLWE2TRLWElvl01NTT(out, in0, st, mu=1 << 29):
+    """copying variant (src/cufhe_gates_gpu.cu:88-99)."""
+    CtxtCopyH2D(in0, st)
+    gGateBootstrappingTLWE2TRLWElvl01NTT(out, in0, st, mu)
+    with torch.cuda.stream(st.torch_stream()):
+        out._host_t.copy_(out.trlwedevice, non_blocking=True)
+
+
+def gSampleExtractAndKeySwitch(out, in0, st):
+    """cufhe::gSampleExtractAndKeySwitch on a device-resident TRLWE batch."""
+    _lib.check(_lib.lib().b2fhe_sample_extract_keyswitch_batch(out.device, st.st(), out.ptr(), in0.ptr(), out.count))
+
+
+def SampleExtractAndKeySwitch(out, in0, st):
+    """cufhe::SampleExtractAndKeySwitch (src/cufhe_gates_gpu.cu:128-137)."""
+    with torch.cuda.stream(st.torch_stream()):
+        in0.trlwedevice.copy_(in0._host_t, non_blocking=True)
+    gSampleExtractAndKeySwitch(out, in0, st)
+    CtxtCopyD2H(out, st)
+
+
+def gRefresh(out, in0, st, mu=1 << 29):
+    """cufhe::gRefresh with the reference's body-term bug fixed (include/b2fhe.h)."""
+    _lib.check(_lib.lib().b2fhe_refresh_batch(out.device, st.st(), out.ptr(), in0.ptr(), mu, out.count))
+
+
+def Refresh(out, in0, st, mu=1 << 29):
+    """cufhe::Refresh (src/cufhe_gates_gpu.cu:110-119)."""
+    with torch.cuda.stream(st.torch_stream()):
+        in0.trlwedevice.copy_(in0._host_t, non_blocking=True)
+    gRefresh(out, in0, st, mu)
+    with torch.cuda.stream(st.torch_stream()):
+        out._host_t.copy_(out.trlwedevice, non_blocking=True)
+
+
 def partition(count, world, rank):
     """Static contiguous partition of a gate batch across GPUs:
     returns (begin, end) of this rank's slice; sizes differ by at most one."""

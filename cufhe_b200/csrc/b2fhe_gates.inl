@@ -340,6 +340,52 @@ int b2fhe_blind_rotate_batch(int device, b2fhe_stream_t stream, uint32_t* out_lv
     return launch_br(*c, B, (cudaStream_t)stream);
 }
 
+int b2fhe_bootstrap_tlwe2trlwe_batch(int device, b2fhe_stream_t stream, uint32_t* out_trlwe, const uint16_t* in_lvl0,
+                                     uint32_t mu, size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE(count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(out_trlwe && in_lvl0, B2FHE_E_BAD_ARGUMENT);
+    BrParams B{};
+    B.in0 = in_lvl0; B.out = out_trlwe; B.count = (int)count; B.ca = 1; B.cb = 0; B.off = 0; B.mu = mu; B.trlwe = 1;
+    return launch_br(*c, B, (cudaStream_t)stream);
+}
+
+int b2fhe_sample_extract_keyswitch_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0, const uint32_t* in_trlwe,
+                                         size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE(count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(out_lvl0 && in_trlwe, B2FHE_E_BAD_ARGUMENT);
+    KsParams K{};
+    K.A = in_trlwe; K.out = out_lvl0; K.count = (int)count; K.ca = 1; K.cb = 0; K.off = 0u; K.trlwe = 1;
+    return launch_ks(*c, K, (cudaStream_t)stream);
+}
+
+int b2fhe_refresh_batch(int device, b2fhe_stream_t stream, uint32_t* out_trlwe, const uint32_t* in_trlwe, uint32_t mu,
+                        size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE(count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(out_trlwe && in_trlwe, B2FHE_E_BAD_ARGUMENT);
+    cudaStream_t st = (cudaStream_t)stream;
+    Scratch scratch(st);
+    void* t0 = nullptr;
+    if (int r = scratch.get(&t0, count * kLvl0Words * sizeof(uint16_t))) return r;
+    KsParams K{};
+    K.A = in_trlwe; K.out = (uint16_t*)t0; K.count = (int)count; K.ca = 1; K.cb = 0; K.off = 0u; K.trlwe = 1;
+    if (int r = launch_ks(*c, K, st)) return r;
+    BrParams B{};
+    B.in0 = (const uint16_t*)t0; B.out = out_trlwe; B.count = (int)count; B.ca = 1; B.cb = 0; B.off = 0; B.mu = mu; B.trlwe = 1;
+    return launch_br(*c, B, st);      // ~Scratch frees t0 in stream order
+}
+
 int b2fhe_keyswitch_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0, const uint32_t* in_lvl1, size_t count)
 {
     DevCtx* c;

@@ -43,6 +43,7 @@ struct BrParams {
     int count;
     int ca, cb, off;        // uniform coefficients
     uint32_t mu;            // test-vector constant (lvl1param::mu)
+    int trlwe;              // 0: out[slot] = SampleExtract(0) (1025 words); 1: out[slot] = the TRLWE (2 x 1024 words)
 };
 
 constexpr int kBrGateSmemWords = 2 * kN + 2 * kN + 640 / 2;   // acc + 2 exchange buffers + abar(u16)
@@ -182,6 +183,11 @@ __global__ void __launch_bounds__(64 * G, 1) k_blind_rotate(const BrParams P)
     br_gate_loop(P.bk, acc, xbuf, xbuf_other, s_abar, s_tab, lane, barid, q);
 
     // ---- SampleExtract(0) (src/bootstrap_gpu.cu:366-381) ----
+    if (P.trlwe) {          // BootstrapTLWE2TRLWE (src/bootstrap_gpu.cu:316-322): no extraction
+        uint32_t* out = P.out + (size_t)it.slot * 2 * kN;
+        for (int m = t64; m < 2 * kN; m += 64) out[m] = acc[m];
+        return;
+    }
     uint32_t* out = P.out + (size_t)it.slot * kLvl1Words;
     for (int m = t64; m < kN; m += 64) out[m] = m == 0 ? acc[0] : 0u - acc[kN - m];
     if (t64 == 0) out[kN] = acc[kN];

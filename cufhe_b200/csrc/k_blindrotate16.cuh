@@ -235,6 +235,11 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate16(const BrParams P,
     br16_gate_loop(P.bk, acc, bufA, bufB, bufA_other, s_abar, s_tab, T, q, bar);
 
     // ---- SampleExtract(0) (src/bootstrap_gpu.cu:366-381) ----
+    if (P.trlwe) {          // BootstrapTLWE2TRLWE (src/bootstrap_gpu.cu:316-322): no extraction
+        uint32_t* out = P.out + (size_t)it.slot * 2 * kN;
+        for (int m = t128; m < 2 * kN; m += 128) out[m] = acc[m];
+        return;
+    }
     uint32_t* out = P.out + (size_t)it.slot * kLvl1Words;
     for (int m = t128; m < kN; m += 128) out[m] = m == 0 ? acc[0] : 0u - acc[kN - m];
     if (t128 == 0) out[kN] = acc[kN];

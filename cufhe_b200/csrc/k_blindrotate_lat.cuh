@@ -128,6 +128,11 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_blind_rotate_lat(const BrPar
     }
 
     // ---- SampleExtract(0) (src/bootstrap_gpu.cu:366-381) ----
+    if (P.trlwe) {          // BootstrapTLWE2TRLWE (src/bootstrap_gpu.cu:316-322): no extraction
+        uint32_t* out = P.out + (size_t)it.slot * 2 * kN;
+        for (int m = tid; m < 2 * kN; m += kLatThreads) out[m] = acc[m];
+        return;
+    }
     uint32_t* out = P.out + (size_t)it.slot * kLvl1Words;
     for (int m = tid; m < kN; m += kLatThreads) out[m] = m == 0 ? acc[0] : 0u - acc[kN - m];
     if (tid == 0) out[kN] = acc[kN];

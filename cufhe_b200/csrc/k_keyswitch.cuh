@@ -54,7 +54,17 @@ struct KsParams {
     int count;
     int ca, cb;
     uint32_t off;
+    int trlwe;              // 1: A holds TRLWEs (2 x 1024 words); SampleExtract(0) is fused into the
+                            //    read (SEIandKS, include/keyswitch_gpu.cuh:25-78); B must be null
 };
+
+// coefficient j of the lvl1 TLWE operand `x` (j = 1024: the body): plain TLWE or the
+// on-the-fly SampleExtract(0) of a TRLWE [a(X)][b(X)]
+__device__ __forceinline__ uint32_t ks_operand(const uint32_t* x, int j, int trlwe)
+{
+    if (!trlwe) return x[j];
+    return j == 0 ? x[0] : j == kN ? x[kN] : 0u - x[kN - j];
+}
 
 constexpr int kKsGates = 8;                       // warps (= gates) per CTA
 
@@ -67,12 +77,12 @@ __global__ void __launch_bounds__(32 * kKsGates) k_keyswitch(const KsParams P)
     KsItem it;
     if (P.items) it = P.items[item];
     else { it.s0 = it.s1 = it.slot = (uint32_t)item; it.ca = (int8_t)P.ca; it.cb = (int8_t)P.cb; it.off = P.off; }
-    const uint32_t* x0 = P.A + (size_t)it.s0 * kLvl1Words;
+    const uint32_t* x0 = P.A + (size_t)it.s0 * (P.trlwe ? 2 * kN : kLvl1Words);
     const uint32_t* x1 = (it.cb != 0 && P.B) ? P.B + (size_t)it.s1 * kLvl1Words : nullptr;
     const uint32_t ca = (uint32_t)(int32_t)it.ca, cb = x1 ? (uint32_t)(int32_t)it.cb : 0u;
     // pre-add in u32 (keyswitch_gpu.cuh:158,168) + decomposition offset
-    for (int j = lane; j < kN; j += 32) s_t[warp][j] = ca * x0[j] + (x1 ? cb * x1[j] : 0u) + kIksAdd;
-    const uint32_t eb = ca * x0[kN] + (x1 ? cb * x1[kN] : 0u) + it.off;
+    for (int j = lane; j < kN; j += 32) s_t[warp][j] = ca * ks_operand(x0, j, P.trlwe) + (x1 ? cb * x1[j] : 0u) + kIksAdd;
+    const uint32_t eb = ca * ks_operand(x0, kN, P.trlwe) + (x1 ? cb * x1[kN] : 0u) + it.off;
     __syncwarp();
 
     uint32_t accF[10], accH[10];
@@ -119,11 +129,11 @@ __global__ void __launch_bounds__(32 * kKsLatWarps) k_keyswitch_lat(const KsPara
     KsItem it;
     if (P.items) it = P.items[item];
     else { it.s0 = it.s1 = it.slot = (uint32_t)item; it.ca = (int8_t)P.ca; it.cb = (int8_t)P.cb; it.off = P.off; }
-    const uint32_t* x0 = P.A + (size_t)it.s0 * kLvl1Words;
+    const uint32_t* x0 = P.A + (size_t)it.s0 * (P.trlwe ? 2 * kN : kLvl1Words);
     const uint32_t* x1 = (it.cb != 0 && P.B) ? P.B + (size_t)it.s1 * kLvl1Words : nullptr;
     const uint32_t ca = (uint32_t)(int32_t)it.ca, cb = x1 ? (uint32_t)(int32_t)it.cb : 0u;
-    for (int j = threadIdx.x; j < kN; j += blockDim.x) s_t[j] = ca * x0[j] + (x1 ? cb * x1[j] : 0u) + kIksAdd;
-    const uint32_t eb = ca * x0[kN] + (x1 ? cb * x1[kN] : 0u) + it.off;
+    for (int j = threadIdx.x; j < kN; j += blockDim.x) s_t[j] = ca * ks_operand(x0, j, P.trlwe) + (x1 ? cb * x1[j] : 0u) + kIksAdd;
+    const uint32_t eb = ca * ks_operand(x0, kN, P.trlwe) + (x1 ? cb * x1[kN] : 0u) + it.off;
     __syncthreads();
 
     uint32_t accF[10], accH[10];

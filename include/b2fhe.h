@@ -92,6 +92,22 @@ int b2fhe_blind_rotate_batch(int device, b2fhe_stream_t stream, uint32_t* out_lv
 int b2fhe_keyswitch_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0,
                           const uint32_t* in_lvl1, size_t count);
 
+/* ---- TRLWE-level entry points.  A TRLWE<lvl1param> is [a(X)][b(X)] =
+ * 2 x 1024 uint32_t (8192 B); batches are contiguous.  Device pointers.
+ * BootstrapTLWE2TRLWE / GateBootstrappingTLWE2TRLWElvl01NTT (src/bootstrap_gpu.cu:316-322,
+ * 806-815; src/cufhe_gates_gpu.cu:88-108): blind rotation WITHOUT SampleExtract */
+int b2fhe_bootstrap_tlwe2trlwe_batch(int device, b2fhe_stream_t stream, uint32_t* out_trlwe,
+                                     const uint16_t* in_lvl0, uint32_t mu, size_t count);
+/* SEIandKS / SampleExtractAndKeySwitch (src/keyswitch_gpu.cu:26-40, src/cufhe_gates_gpu.cu:
+ * 128-146): SampleExtract(0) fused into the identity key switch, TRLWE -> lvl0 TLWE */
+int b2fhe_sample_extract_keyswitch_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0,
+                                         const uint32_t* in_trlwe, size_t count);
+/* Refresh (src/cufhe_gates_gpu.cu:110-126) = the two above in sequence.  NOTE: the reference's
+ * __SEIandBootstrap2TRLWE__ reads the body term from an uninitialised buffer
+ * (src/bootstrap_gpu.cu:342-348); this computes the intended result. */
+int b2fhe_refresh_batch(int device, b2fhe_stream_t stream, uint32_t* out_trlwe,
+                        const uint32_t* in_trlwe, uint32_t mu, size_t count);
+
 /* ---- NTT microbenchmark entry points (test/test_polynomial_mult_1024.cu:76-99) ------
  * All device pointers.  ntt: in[count][1024] u32 -> out[count][2][1024] residues mod the
  * two NTT primes (engine-internal order).  intt: inverse + centred CRT, mod 2^32.

@@ -217,4 +217,75 @@ B2_GATE1(Not, B2FHE_NOT)
 B2_GATE1(Copy, B2FHE_COPY)
 #undef B2_GATE1
 
+// ---- TRLWE-level entry points (include/cufhe_gpu.cuh:123-146,209-216,282-285) -------------
+struct cuFHETRLWElvl1 {
+    cuFHETRLWElvl1()
+    {
+        cudaHostRegister(trlwehost.data(), sizeof(trlwehost), cudaHostRegisterDefault);
+        trlwedevices.resize(_gpuNumRef());
+        for (int i = 0; i < _gpuNumRef(); i++) {
+            cudaSetDevice(i);
+            cudaMalloc((void**)&trlwedevices[i], sizeof(trlwehost));
+        }
+    }
+    ~cuFHETRLWElvl1()
+    {
+        cudaHostUnregister(trlwehost.data());
+        for (size_t i = 0; i < trlwedevices.size(); i++) {
+            cudaSetDevice((int)i);
+            cudaFree(trlwedevices[i]);
+        }
+    }
+    cuFHETRLWElvl1(const cuFHETRLWElvl1&) = delete;
+    cuFHETRLWElvl1& operator=(const cuFHETRLWElvl1&) = delete;
+    TFHEpp::TRLWE<TFHEpp::lvl1param> trlwehost;
+    std::vector<TFHEpp::lvl1param::T*> trlwedevices;
+};
+inline void _trlweH2D(const cuFHETRLWElvl1& c, Stream st)
+{
+    cudaMemcpyAsync(c.trlwedevices[st.device_id()], c.trlwehost.data(), sizeof(c.trlwehost), cudaMemcpyHostToDevice, st.st());
+}
+inline void _trlweD2H(cuFHETRLWElvl1& c, Stream st)
+{
+    cudaMemcpyAsync(c.trlwehost.data(), c.trlwedevices[st.device_id()], sizeof(c.trlwehost), cudaMemcpyDeviceToHost, st.st());
+}
+inline void gGateBootstrappingTLWE2TRLWElvl01NTT(cuFHETRLWElvl1& out, Ctxt<TFHEpp::lvl0param>& in, Stream st)
+{
+    const int d = st.device_id();
+    cudaSetDevice(d);
+    B2CHECK(b2fhe_bootstrap_tlwe2trlwe_batch(d, (b2fhe_stream_t)st.st(), out.trlwedevices[d], in.tlwedevices[d],
+                                             TFHEpp::lvl1param::μ, 1));
+}
+inline void GateBootstrappingTLWE2TRLWElvl01NTT(cuFHETRLWElvl1& out, Ctxt<TFHEpp::lvl0param>& in, Stream st)
+{
+    CtxtCopyH2D<TFHEpp::lvl0param>(in, st);
+    gGateBootstrappingTLWE2TRLWElvl01NTT(out, in, st);
+    _trlweD2H(out, st);
+}
+inline void gSampleExtractAndKeySwitch(Ctxt<TFHEpp::lvl0param>& out, const cuFHETRLWElvl1& in, Stream st)
+{
+    const int d = st.device_id();
+    cudaSetDevice(d);
+    _trlweH2D(in, st);      // the reference's g-variant copies too (src/cufhe_gates_gpu.cu:139-146)
+    B2CHECK(b2fhe_sample_extract_keyswitch_batch(d, (b2fhe_stream_t)st.st(), out.tlwedevices[d], in.trlwedevices[d], 1));
+}
+inline void SampleExtractAndKeySwitch(Ctxt<TFHEpp::lvl0param>& out, const cuFHETRLWElvl1& in, Stream st)
+{
+    gSampleExtractAndKeySwitch(out, in, st);
+    CtxtCopyD2H<TFHEpp::lvl0param>(out, st);
+}
+inline void gRefresh(cuFHETRLWElvl1& out, cuFHETRLWElvl1& in, Stream st)
+{
+    const int d = st.device_id();
+    cudaSetDevice(d);
+    B2CHECK(b2fhe_refresh_batch(d, (b2fhe_stream_t)st.st(), out.trlwedevices[d], in.trlwedevices[d], TFHEpp::lvl1param::μ, 1));
+}
+inline void Refresh(cuFHETRLWElvl1& out, cuFHETRLWElvl1& in, Stream st)
+{
+    cudaSetDevice(st.device_id());
+    _trlweH2D(in, st);
+    gRefresh(out, in, st);
+    _trlweD2H(out, st);
+}
+
 }  // namespace cufhe

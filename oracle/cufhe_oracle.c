@@ -289,10 +289,9 @@ static void cmux_step_pre(uint32_t *acc, uint32_t abar, const uint64_t *bkn_i)
     }
 }
 
-static void blind_rotate_extract_impl(uint32_t *out, const uint16_t *c, uint32_t mu,
-                                      const uint32_t *bk, const uint64_t *bkn, int use_schoolbook)
+static void blind_rotate_trlwe_impl(uint32_t *acc /*[2][1024]*/, const uint16_t *c, uint32_t mu,
+                                    const uint32_t *bk, const uint64_t *bkn, int use_schoolbook)
 {
-    uint32_t acc[2 * ORC_N];
     /* modSwitchFromTorus: u16 phase >> (16-1-10) (gatebootstrapping_gpu.cuh:10-15);
      * NO rounding offset on b (:296-299,327-331) */
     uint32_t bbar = 2 * ORC_N - ((uint32_t)c[ORC_n] >> 5);
@@ -308,10 +307,43 @@ static void blind_rotate_extract_impl(uint32_t *out, const uint16_t *c, uint32_t
         if (bkn) cmux_step_pre(acc, abar, bkn + (size_t)i * 8 * ORC_N);
         else orc_cmux_step(acc, abar, bk + (size_t)i * 8 * ORC_N, use_schoolbook);
     }
+}
+static void sample_extract0(uint32_t *out, const uint32_t *acc)
+{
     /* __SampleExtractIndex__<P,0> (src/bootstrap_gpu.cu:366-381) */
     out[0] = acc[0];
     for (unsigned i = 1; i < ORC_N; i++) out[i] = 0u - acc[ORC_N - i];
     out[ORC_N] = acc[ORC_N];
+}
+static void blind_rotate_extract_impl(uint32_t *out, const uint16_t *c, uint32_t mu,
+                                      const uint32_t *bk, const uint64_t *bkn, int use_schoolbook)
+{
+    uint32_t acc[2 * ORC_N];
+    blind_rotate_trlwe_impl(acc, c, mu, bk, bkn, use_schoolbook);
+    sample_extract0(out, acc);
+}
+/* BootstrapTLWE2TRLWE = __BlindRotateGlobal__ (src/bootstrap_gpu.cu:316-322,806-815):
+ * blind rotation without SampleExtract, out = TRLWE [a(X)][b(X)] */
+void orc_blind_rotate_trlwe(uint32_t *out, const uint16_t *c, uint32_t mu, const uint32_t *bk)
+{
+    blind_rotate_trlwe_impl(out, c, mu, bk, bk_ntt_get(bk), 0);
+}
+/* SEIandKS = KeySwitch<lvl10param> on a TRLWE (include/keyswitch_gpu.cuh:25-78,
+ * src/keyswitch_gpu.cu:26-40): SampleExtract(0) fused into the key switch */
+void orc_sample_extract_keyswitch(uint16_t *out, const uint32_t *trlwe, const uint16_t *ksk)
+{
+    uint32_t t[ORC_LVL1_WORDS];
+    sample_extract0(t, trlwe);
+    orc_keyswitch(out, t, ksk);
+}
+/* Refresh = SEIandBootstrap2TRLWE with the reference's b-term bug fixed (it
+ * reads the body from an uninitialised buffer, src/bootstrap_gpu.cu:342-348): key switch of
+ * SampleExtract(0), then blind rotation to a fresh TRLWE */
+void orc_refresh(uint32_t *out, const uint32_t *trlwe, uint32_t mu, const uint32_t *bk, const uint16_t *ksk)
+{
+    uint16_t c[ORC_LVL0_WORDS];
+    orc_sample_extract_keyswitch(c, trlwe, ksk);
+    orc_blind_rotate_trlwe(out, c, mu, bk);
 }
 void orc_blind_rotate_extract(uint32_t *out, const uint16_t *c, uint32_t mu,
                               const uint32_t *bk, int use_schoolbook)

@@ -76,6 +76,13 @@ void orc_cmux_step(uint32_t *acc /*[2][1024]*/, uint32_t abar,
  * (gatebootstrapping_gpu.cuh:287-345, bootstrap_gpu.cu:366-381) */
 void orc_blind_rotate_extract(uint32_t *out, const uint16_t *c, uint32_t mu,
                               const uint32_t *bk, int use_schoolbook);
+/* TRLWE-level entry points: blind rotation without SampleExtract
+ * (BootstrapTLWE2TRLWE, src/bootstrap_gpu.cu:316-322,806-815), SampleExtract(0)+key switch
+ * (SEIandKS, src/keyswitch_gpu.cu:26-40), and Refresh = both in sequence (the reference's
+ * __SEIandBootstrap2TRLWE__ with its b-term bug fixed) */
+void orc_blind_rotate_trlwe(uint32_t *out /*[2][1024]*/, const uint16_t *c, uint32_t mu, const uint32_t *bk);
+void orc_sample_extract_keyswitch(uint16_t *out, const uint32_t *trlwe, const uint16_t *ksk);
+void orc_refresh(uint32_t *out, const uint32_t *trlwe, uint32_t mu, const uint32_t *bk, const uint16_t *ksk);
 /* identity key switch lvl1 -> lvl0 (keyswitch_gpu.cuh:83-134) */
 void orc_keyswitch(uint16_t *out, const uint32_t *in, const uint16_t *ksk);
 

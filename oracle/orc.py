@@ -109,6 +109,27 @@ def blind_rotate_extract(keys, c, mu=MU1, schoolbook=False):
     return out
 
 
+def blind_rotate_trlwe(keys, c, mu=MU1):
+    c = np.ascontiguousarray(c, dtype=np.uint16)
+    out = np.zeros(2 * N, np.uint32)
+    lib().orc_blind_rotate_trlwe(_p(out), _p(c), C.c_uint32(mu), _p(keys.bk))
+    return out
+
+
+def sample_extract_keyswitch(keys, trlwe):
+    t = np.ascontiguousarray(trlwe, dtype=np.uint32)
+    out = np.zeros(LVL0_WORDS, np.uint16)
+    lib().orc_sample_extract_keyswitch(_p(out), _p(t), _p(keys.ksk))
+    return out
+
+
+def refresh(keys, trlwe, mu=MU1):
+    t = np.ascontiguousarray(trlwe, dtype=np.uint32)
+    out = np.zeros(2 * N, np.uint32)
+    lib().orc_refresh(_p(out), _p(t), C.c_uint32(mu), _p(keys.bk), _p(keys.ksk))
+    return out
+
+
 def keyswitch(keys, x):
     x = np.ascontiguousarray(x, dtype=np.uint32)
     out = np.zeros(LVL0_WORDS, np.uint16)

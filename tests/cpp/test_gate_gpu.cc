@@ -102,6 +102,37 @@ template <class P> static void run_level(const TFHEpp::EvalKey& ek, int kNumSMs)
     for (auto& x : st) x.Destroy();
 }
 
+// TRLWE-level entry points (reference test/test_perf.cc shape: Refresh; plus
+// GateBootstrappingTLWE2TRLWElvl01NTT and SampleExtractAndKeySwitch), bytes vs the oracle
+static void run_trlwe(const TFHEpp::EvalKey& ek)
+{
+    Stream s;
+    s.Create();
+    int bad = 0;
+    for (int bit = 0; bit < 2; bit++) {
+        Ctxt<lvl0param> in, out;
+        cuFHETRLWElvl1 t, t2;
+        enc<lvl0param>(in.tlwehost, bit, 777 + bit);
+        GateBootstrappingTLWE2TRLWElvl01NTT(t, in, s);
+        Synchronize();
+        std::vector<uint32_t> want(2 * 1024), want2(2 * 1024);
+        orc_blind_rotate_trlwe(want.data(), in.tlwehost.data(), ORC_MU1, ek.bk.data());
+        if (memcmp(want.data(), t.trlwehost.data(), 8192)) bad++;
+        Refresh(t2, t, s);
+        SampleExtractAndKeySwitch(out, t2, s);
+        Synchronize();
+        orc_refresh(want2.data(), want.data(), ORC_MU1, ek.bk.data(), ek.iksk.data());
+        if (memcmp(want2.data(), t2.trlwehost.data(), 8192)) bad++;
+        TFHEpp::TLWE<lvl0param> w0;
+        orc_sample_extract_keyswitch(w0.data(), want2.data(), ek.iksk.data());
+        if (memcmp(w0.data(), out.tlwehost.data(), sizeof w0)) bad++;
+        if (dec<lvl0param>(out.tlwehost) != bit) bad++;
+    }
+    printf("TRLWE-level API (TLWE2TRLWE, Refresh, SampleExtractAndKeySwitch) : %s\n", bad ? "FAIL" : "PASS");
+    failures += bad;
+    s.Destroy();
+}
+
 int main()
 {
     cudaDeviceProp prop;
@@ -115,6 +146,7 @@ int main()
     Initialize(ek);
     run_level<lvl1param>(ek, kNumSMs);    // what test/test_gate_gpu.cc runs
     run_level<lvl0param>(ek, kNumSMs);    // what test/test_gate_gpu_multi.cc / test_intensive.cc run
+    run_trlwe(ek);
     CleanUp();
     printf(failures ? "FAILED (%d)\n" : "ALL PASS\n", failures);
     return failures ? 1 : 0;

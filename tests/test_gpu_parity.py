@@ -132,6 +132,33 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
             assert np.array_equal(gk[i], want[i]), (ks_variant, i)
 
 
+def test_trlwe_level_entry_points(engine, keys):
+    """BootstrapTLWE2TRLWE, SampleExtractAndKeySwitch, Refresh through the
+    mirrored API, bytes against the oracle, ragged batch."""
+    cf = engine
+    cnt = 5
+    bits = np.array([1, 0, 1, 1, 0], np.uint8)
+    c0 = orc.encrypt(keys, bits, 0, base_index=4242)
+    st = cf.Stream(0).Create()
+    cin = cf.Ctxt(cnt, 0).set(c0)
+    t1, t2 = cf.cuFHETRLWElvl1(cnt), cf.cuFHETRLWElvl1(cnt)
+    out = cf.Ctxt(cnt, 0)
+    cf.GateBootstrappingTLWE2TRLWElvl01NTT(t1, cin, st)
+    cf.gRefresh(t2, t1, st)
+    cf.gSampleExtractAndKeySwitch(out, t2, st)
+    cf.CtxtCopyD2H(out, st)
+    with torch.cuda.stream(st.torch_stream()):
+        t2._host_t.copy_(t2.trlwedevice, non_blocking=True)
+    cf.Synchronize()
+    for i in range(cnt):
+        w1 = orc.blind_rotate_trlwe(keys, c0[i])
+        assert np.array_equal(t1.trlwehost[i], w1), i
+        w2 = orc.refresh(keys, w1)
+        assert np.array_equal(t2.trlwehost[i], w2), i
+        assert np.array_equal(out.tlwehost[i], orc.sample_extract_keyswitch(keys, w2)), i
+    assert list(orc.decrypt(keys, out.tlwehost, 0)) == list(bits)
+
+
 # ------------------------------------------------------------------- gates ---
 @pytest.mark.parametrize("level", [0, 1])
 def test_all_gates_bit_exact_and_decrypt(engine, keys, level):
