@@ -23,7 +23,7 @@ SYMBOLS = [
     "b2fhe_init", "b2fhe_init_device", "b2fhe_adopt_keys", "b2fhe_key_pointers", "b2fhe_cleanup",
     "b2fhe_num_devices", "b2fhe_last_error_string", "b2fhe_gate_batch", "b2fhe_gate_batch_mixed",
     "b2fhe_gate_batch_host", "b2fhe_synchronize", "b2fhe_blind_rotate_batch", "b2fhe_keyswitch_batch",
-    "b2fhe_bootstrap_tlwe2trlwe_batch", "b2fhe_sample_extract_keyswitch_batch", "b2fhe_refresh_batch",
+    "b2fhe_bootstrap_tlwe2trlwe_batch", "b2fhe_sample_extract_keyswitch_batch", "b2fhe_refresh_batch", "b2fhe_trgsw2ntt_batch", "b2fhe_cmux_ntt_batch",
     "b2fhe_ntt1024_batch", "b2fhe_intt1024_batch", "b2fhe_polymul1024_batch",
     "b2fhe_set_gates_per_cta", "b2fhe_set_br_variant", "b2fhe_set_ks_variant", "b2fhe_kernel_launches", "b2fhe_int_peak",
 ]
@@ -71,6 +71,8 @@ def lib():
     L.b2fhe_bootstrap_tlwe2trlwe_batch.argtypes = [i32, vp, vp, vp, C.c_uint32, sz]
     L.b2fhe_sample_extract_keyswitch_batch.argtypes = [i32, vp, vp, vp, sz]
     L.b2fhe_refresh_batch.argtypes = [i32, vp, vp, vp, C.c_uint32, sz]
+    L.b2fhe_trgsw2ntt_batch.argtypes = [i32, vp, vp, vp, sz]
+    L.b2fhe_cmux_ntt_batch.argtypes = [i32, vp, vp, vp, vp, vp, sz, i32]
     L.b2fhe_ntt1024_batch.argtypes = [i32, vp, vp, vp, sz]
     L.b2fhe_intt1024_batch.argtypes = [i32, vp, vp, vp, sz]
     L.b2fhe_polymul1024_batch.argtypes = [i32, vp, vp, vp, vp, sz]

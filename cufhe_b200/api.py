@@ -336,6 +336,47 @@ def Refresh(out, in0, st, mu=1 << 29):
         out._host_t.copy_(out.trlwedevice, non_blocking=True)
 
 
+class cuFHETRGSWNTTlvl1:
+    """A batch of NTT-domain TRGSWs in this engine's format (B2FHE_TRGSW_NTT_BYTES each);
+    produced only by TRGSW2NTT (cufhe::cuFHETRGSWNTTlvl1, include/cufhe_gpu.cuh:136-146)."""
+
+    def __init__(self, count, device=0):
+        self.count, self.device = int(count), int(device)
+        self.trgswdevice = torch.empty((self.count, 16384), dtype=torch.int32, device=torch.device("cuda", self.device))
+
+    def ptr(self):
+        return self.trgswdevice.data_ptr()
+
+
+def TRGSW2NTT(trgswntt, trgsw_raw, st):
+    """cufhe::TRGSW2NTT (src/bootstrap_gpu.cu:75-95): raw TRGSW<lvl1param> [count][4][2][1024]
+    u32 (host numpy) -> NTT domain on the device."""
+    raw = np.ascontiguousarray(trgsw_raw, dtype=np.uint32).reshape(trgswntt.count, 8192)
+    with torch.cuda.stream(st.torch_stream()):
+        d = torch.from_numpy(raw.view(np.int32)).to(trgswntt.trgswdevice.device, non_blocking=False)
+        _lib.check(_lib.lib().b2fhe_trgsw2ntt_batch(trgswntt.device, st.st(), trgswntt.ptr(), d.data_ptr(), trgswntt.count))
+        d.record_stream(st.torch_stream())
+
+
+def gCMUXNTT(res, cs, c1, c0, st):
+    """cufhe::CMUXNTT on device-resident operands: res = c0 + (c1 - c0) [.] cs.  One TRGSW per
+    item if cs.count == res.count, one shared TRGSW if cs.count == 1."""
+    if cs.count not in (1, res.count):
+        raise ValueError("cs must hold one TRGSW or one per item")
+    _lib.check(_lib.lib().b2fhe_cmux_ntt_batch(res.device, st.st(), res.ptr(), cs.ptr(), c1.ptr(), c0.ptr(), res.count,
+                                               1 if cs.count == res.count and res.count > 1 else 0))
+
+
+def CMUXNTT(res, cs, c1, c0, st):
+    """copying variant (src/cufhe_gates_gpu.cu:69-85)."""
+    with torch.cuda.stream(st.torch_stream()):
+        c1.trlwedevice.copy_(c1._host_t, non_blocking=True)
+        c0.trlwedevice.copy_(c0._host_t, non_blocking=True)
+    gCMUXNTT(res, cs, c1, c0, st)
+    with torch.cuda.stream(st.torch_stream()):
+        res._host_t.copy_(res.trlwedevice, non_blocking=True)
+
+
 def partition(count, world, rank):
     """Static contiguous partition of a gate batch across GPUs:
     returns (begin, end) of this rank's slice; sizes differ by at most one."""

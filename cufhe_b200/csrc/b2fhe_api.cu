@@ -12,6 +12,7 @@
 #include "k_blindrotate.cuh"
 #include "k_blindrotate16.cuh"
 #include "k_blindrotate_lat.cuh"
+#include "k_cmux.cuh"
 #include "k_keyswitch.cuh"
 #include "k_ntt.cuh"
 
@@ -107,6 +108,8 @@ int setup_device(int device)
     if (int r = set_br_attr<6>()) return r;
     if (int r = set_br_attr<8>()) return r;
     CK(cudaFuncSetAttribute(k_blind_rotate_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatSmemBytes));
+    CK(cudaFuncSetAttribute(k_cmux16<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(1)));
+    CK(cudaFuncSetAttribute(k_cmux16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(4)));
     if (int r = set_br16_attr<1>()) return r;
     if (int r = set_br16_attr<2>()) return r;
     if (int r = set_br16_attr<3>()) return r;

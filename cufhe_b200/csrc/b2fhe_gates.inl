@@ -386,6 +386,41 @@ int b2fhe_refresh_batch(int device, b2fhe_stream_t stream, uint32_t* out_trlwe, 
     return launch_br(*c, B, st);      // ~Scratch frees t0 in stream order
 }
 
+int b2fhe_trgsw2ntt_batch(int device, b2fhe_stream_t stream, uint32_t* out_ntt, const uint32_t* in_raw, size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE(count < (1u << 24), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(out_ntt && in_raw, B2FHE_E_BAD_ARGUMENT);
+    cudaStream_t st = (cudaStream_t)stream;
+    Scratch scratch(st);
+    void* tmp = nullptr;
+    if (int r = scratch.get(&tmp, count * B2FHE_TRGSW_NTT_BYTES)) return r;
+    const int npoly = (int)count * kRows * 2;
+    k_ntt_fwd<<<ntt_grid(*c, npoly), kNttThreads, kNttSmemBytes, st>>>(in_raw, (uint32_t*)tmp, npoly, 1, 0, c->tab);
+    LAUNCHED();
+    k_bk_to_layout16<<<c->sm_count * 8, 256, 0, st>>>((const uint32_t*)tmp, out_ntt, (size_t)npoly * 2);
+    LAUNCHED();
+    return 0;
+}
+
+int b2fhe_cmux_ntt_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* cs_ntt, const uint32_t* c1,
+                         const uint32_t* c0, size_t count, int cs_per_item)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE(count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(out && cs_ntt && c1 && c0, B2FHE_E_BAD_ARGUMENT);
+    CmuxParams P{out, cs_ntt, c1, c0, (int)count, cs_per_item ? 1 : 0};
+    cudaStream_t st = (cudaStream_t)stream;
+    if ((int)count >= 4 * c->sm_count) k_cmux16<4><<<((int)count + 3) / 4, 512, cmux_smem_bytes(4), st>>>(P, c->tab16);
+    else k_cmux16<1><<<(int)count, 128, cmux_smem_bytes(1), st>>>(P, c->tab16);
+    LAUNCHED();
+    return 0;
+}
+
 int b2fhe_keyswitch_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0, const uint32_t* in_lvl1, size_t count)
 {
     DevCtx* c;

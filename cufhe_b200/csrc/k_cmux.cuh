@@ -1,0 +1,117 @@
+// k_cmux.cuh -- batched CMUX with a caller-supplied NTT-domain TRGSW:
+//     out = c0 + (c1 - c0) [.] TRGSW            (TRLWE<lvl1param> operands)
+// Replaces __CMUXNTT__ / TRLWESubAndDecomposition and __TRGSW2NTT__ (reference
+// src/bootstrap_gpu.cu:43-70,162-285; API src/cufhe_gates_gpu.cu:69-85), which run one
+// CMUX per 512-thread block.  Here an item is 128 threads (two 64-thread teams, one per
+// prime, 16 coefficients per thread: the external-product step of k_blind_rotate16 with the
+// rotation replaced by c1 - c0), G items per CTA.
+//
+// NTT-domain TRGSW format (this engine's, produced by b2fhe_trgsw2ntt_batch): per TRGSW
+// [4 rows][2 primes][2 outputs][1024] u32 Montgomery residues in bk16_slot order (65536 B)
+// -- the layout of one bootstrapping-key row.
+#pragma once
+#include "k_blindrotate16.cuh"
+
+namespace b2 {
+
+struct CmuxParams {
+    uint32_t* out;            // [count][2][1024]
+    const uint32_t* cs;       // NTT-domain TRGSWs
+    const uint32_t* c1;       // [count][2][1024]
+    const uint32_t* c0;       // [count][2][1024]
+    int count;
+    int cs_per_item;          // 1: item i uses TRGSW i; 0: all items share TRGSW 0
+};
+
+constexpr int kCmuxItemSmemWords = 4 * kXbufWords;
+__host__ __device__ constexpr int cmux_smem_bytes(int items) { return (kLane16TableWords + items * kCmuxItemSmemWords) * 4; }
+
+template <int G>
+__global__ void __launch_bounds__(128 * G, 1) k_cmux16(const CmuxParams P, const Lane16Tables* __restrict__ tab16)
+{
+    extern __shared__ __align__(16) uint32_t smem[];
+    uint32_t* s_tab = smem;
+    stage_tables16(s_tab, tab16);
+    __syncthreads();
+    const int gs = threadIdx.x >> 7, t128 = threadIdx.x & 127;
+    const int q = t128 >> 6, T = t128 & 63;
+    const int item = blockIdx.x * G + gs;
+    if (item >= P.count) return;
+    uint32_t* gbase = smem + kLane16TableWords + gs * kCmuxItemSmemWords;
+    uint32_t* bufA = gbase + q * 2 * kXbufWords;
+    uint32_t* bufB = bufA + kXbufWords;
+    const uint32_t* bufA_other = gbase + (q ^ 1) * 2 * kXbufWords;
+    const int bar = 1 + gs;
+
+    const uint32_t p = q ? Prime<1>::p : Prime<0>::p;
+    const uint32_t pinv = q ? Prime<1>::pinv : Prime<0>::pinv;
+    const uint32_t dig_off = p - 128u;
+    const X16 xa = make_x16(T);
+    const uint32_t* c1 = P.c1 + (size_t)item * 2 * kN;
+    const uint32_t* c0 = P.c0 + (size_t)item * 2 * kN;
+    const uint4* cs4 = reinterpret_cast<const uint4*>(P.cs) + (size_t)(P.cs_per_item ? item : 0) * (kRows * 4 * (kN / 4)) + T +
+                       (size_t)q * 2 * (kN / 4);
+    const int off_a = q * (kN / 4), off_b = (1 - q) * (kN / 4);
+
+    uint32_t sa[16], sb[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) sa[k] = sb[k] = 4u * p;
+    uint32_t dlo[4];
+#pragma unroll 1
+    for (int r = 0; r < kRows; r++) {
+        uint32_t x[16];
+        if ((r & 1) == 0) {
+            const uint32_t* a1 = c1 + (r >> 1) * kN + T;
+            const uint32_t* a0 = c0 + (r >> 1) * kN + T;
+#pragma unroll
+            for (int k = 0; k < 16; k++) {
+                const uint32_t t = a1[64 * k] - a0[64 * k] + kDecompAdd;   // :162-194 (plain loads: out may alias)
+                x[k] = (t >> 24) + dig_off;
+                const uint32_t d1 = (t >> 16) & 0xFFu;
+                if ((k & 3) == 0) dlo[k >> 2] = d1; else dlo[k >> 2] |= d1 << (8 * (k & 3));
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 16; k++) x[k] = ((dlo[k >> 2] >> (8 * (k & 3))) & 0xFFu) + dig_off;
+        }
+        fwd16(x, bufA, bufB, s_tab, xa, T, q, p, bar);
+        const uint4* row = cs4 + (size_t)r * (4 * (kN / 4));
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+            const uint4 b = __ldg(row + off_a + v * 64);
+            sa[4 * v + 0] += (uint32_t)umontmul_p(x[4 * v + 0], b.x, p, pinv);
+            sa[4 * v + 1] += (uint32_t)umontmul_p(x[4 * v + 1], b.y, p, pinv);
+            sa[4 * v + 2] += (uint32_t)umontmul_p(x[4 * v + 2], b.z, p, pinv);
+            sa[4 * v + 3] += (uint32_t)umontmul_p(x[4 * v + 3], b.w, p, pinv);
+        }
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+            const uint4 b = __ldg(row + off_b + v * 64);
+            sb[4 * v + 0] += (uint32_t)umontmul_p(x[4 * v + 0], b.x, p, pinv);
+            sb[4 * v + 1] += (uint32_t)umontmul_p(x[4 * v + 1], b.y, p, pinv);
+            sb[4 * v + 2] += (uint32_t)umontmul_p(x[4 * v + 2], b.z, p, pinv);
+            sb[4 * v + 3] += (uint32_t)umontmul_p(x[4 * v + 3], b.w, p, pinv);
+        }
+    }
+#pragma unroll 1
+    for (int t = 0; t < 2; t++) {
+        inv16(sb, bufA, bufB, s_tab, xa, T, q, p, bar);
+#pragma unroll
+        for (int k = 0; k < 16; k++) { const uint32_t tmp = sa[k]; sa[k] = sb[k]; sb[k] = tmp; }
+    }
+    // sa = INTT(output q) (this team finishes it), sb = INTT(output 1-q) -> other team
+#pragma unroll
+    for (int k = 0; k < 16; k++) bufA[T + 64 * k] = sb[k];
+    named_bar_sync(bar, 128);
+    uint32_t* out = P.out + (size_t)item * 2 * kN + q * kN + T;
+    const uint32_t* base = c0 + q * kN + T;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        const uint32_t t = bufA_other[T + 64 * k];
+        const uint32_t s0 = q ? t : sa[k];
+        const uint32_t s1 = q ? sa[k] : t;
+        out[64 * k] = base[64 * k] + crt_lift32(s0, s1, c_crt_p0inv.w, c_crt_p0inv.ws);
+    }
+}
+
+}  // namespace b2

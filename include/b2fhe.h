@@ -41,6 +41,8 @@ enum b2fhe_op {
 #define B2FHE_BK_RAW_WORDS   ((size_t)636 * 4 * 2 * 1024)      /* uint32_t */
 #define B2FHE_KSK_RAW_WORDS  ((size_t)1024 * 7 * 2 * 637)      /* uint16_t */
 #define B2FHE_BK_NTT_BYTES   ((size_t)636 * 4 * 2 * 2 * 1024 * 4)   /* 41,680,896 */
+#define B2FHE_TRGSW_RAW_WORDS ((size_t)4 * 2 * 1024)              /* TFHEpp::TRGSW<lvl1param>, uint32_t */
+#define B2FHE_TRGSW_NTT_BYTES ((size_t)4 * 2 * 2 * 1024 * 4)       /* 65,536: NTT-domain TRGSW */
 #define B2FHE_KSK_DEV_BYTES  ((size_t)1024 * 7 * 3 * 320 * 4)       /* 27,525,120 */
 
 typedef void* b2fhe_stream_t;   /* a cudaStream_t (0 = default stream) */
@@ -107,6 +109,17 @@ int b2fhe_sample_extract_keyswitch_batch(int device, b2fhe_stream_t stream, uint
  * (src/bootstrap_gpu.cu:342-348); this computes the intended result. */
 int b2fhe_refresh_batch(int device, b2fhe_stream_t stream, uint32_t* out_trlwe,
                         const uint32_t* in_trlwe, uint32_t mu, size_t count);
+
+/* ---- CMUX with a caller-supplied TRGSW.  Device pointers.
+ * TRGSW2NTT (src/bootstrap_gpu.cu:43-95): raw TRGSW<lvl1param> [count][4][2][1024] u32 ->
+ * this engine's NTT-domain form, B2FHE_TRGSW_NTT_BYTES each (opaque; two 27-bit primes,
+ * Montgomery residues -- NOT the reference's single-prime FFP words). */
+int b2fhe_trgsw2ntt_batch(int device, b2fhe_stream_t stream, uint32_t* out_ntt, const uint32_t* in_raw, size_t count);
+/* CMUXNTT (src/bootstrap_gpu.cu:162-285, src/cufhe_gates_gpu.cu:69-85): out = c0 + (c1 - c0) [.] cs
+ * on TRLWEs; cs_per_item != 0: item i uses TRGSW i, else every item uses TRGSW 0.
+ * out may alias c0 or c1. */
+int b2fhe_cmux_ntt_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* cs_ntt,
+                         const uint32_t* c1, const uint32_t* c0, size_t count, int cs_per_item);
 
 /* ---- NTT microbenchmark entry points (test/test_polynomial_mult_1024.cu:76-99) ------
  * All device pointers.  ntt: in[count][1024] u32 -> out[count][2][1024] residues mod the

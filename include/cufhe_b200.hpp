@@ -14,6 +14,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <array>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -286,6 +287,64 @@ inline void Refresh(cuFHETRLWElvl1& out, cuFHETRLWElvl1& in, Stream st)
     _trlweH2D(in, st);
     gRefresh(out, in, st);
     _trlweD2H(out, st);
+}
+
+// ---- CMUX with a caller-supplied TRGSW (include/cufhe_gpu.cuh:136-146,209-216) -------------
+// trgswhost holds this engine's NTT-domain form (B2FHE_TRGSW_NTT_BYTES, opaque) instead of
+// TFHEpp::TRGSWNTT<lvl1param>: like the reference's, it is only ever produced by TRGSW2NTT.
+struct cuFHETRGSWNTTlvl1 {
+    cuFHETRGSWNTTlvl1()
+    {
+        cudaHostRegister(trgswhost.data(), sizeof(trgswhost), cudaHostRegisterDefault);
+        trgswdevices.resize(_gpuNumRef());
+        for (int i = 0; i < _gpuNumRef(); i++) {
+            cudaSetDevice(i);
+            cudaMalloc((void**)&trgswdevices[i], sizeof(trgswhost));
+        }
+    }
+    ~cuFHETRGSWNTTlvl1()
+    {
+        cudaHostUnregister(trgswhost.data());
+        for (size_t i = 0; i < trgswdevices.size(); i++) {
+            cudaSetDevice((int)i);
+            cudaFree(trgswdevices[i]);
+        }
+    }
+    cuFHETRGSWNTTlvl1(const cuFHETRGSWNTTlvl1&) = delete;
+    cuFHETRGSWNTTlvl1& operator=(const cuFHETRGSWNTTlvl1&) = delete;
+    std::array<uint32_t, B2FHE_TRGSW_NTT_BYTES / 4> trgswhost;
+    std::vector<uint32_t*> trgswdevices;
+};
+// TRGSW2NTT (src/bootstrap_gpu.cu:75-95): raw TRGSW -> NTT domain on the device, result also
+// copied back to trgswhost
+inline void TRGSW2NTT(cuFHETRGSWNTTlvl1& trgswntt, const TFHEpp::TRGSW<TFHEpp::lvl1param>& trgsw, Stream st)
+{
+    const int d = st.device_id();
+    cudaSetDevice(d);
+    uint32_t* raw = nullptr;
+    cudaMallocAsync((void**)&raw, sizeof(trgsw), st.st());
+    cudaMemcpyAsync(raw, trgsw.data(), sizeof(trgsw), cudaMemcpyHostToDevice, st.st());
+    B2CHECK(b2fhe_trgsw2ntt_batch(d, (b2fhe_stream_t)st.st(), trgswntt.trgswdevices[d], raw, 1));
+    cudaFreeAsync(raw, st.st());
+    cudaMemcpyAsync(trgswntt.trgswhost.data(), trgswntt.trgswdevices[d], sizeof(trgswntt.trgswhost), cudaMemcpyDeviceToHost, st.st());
+}
+inline void gCMUXNTT(cuFHETRLWElvl1& res, cuFHETRGSWNTTlvl1& cs, cuFHETRLWElvl1& c1, cuFHETRLWElvl1& c0, Stream st)
+{
+    const int d = st.device_id();
+    cudaSetDevice(d);
+    B2CHECK(b2fhe_cmux_ntt_batch(d, (b2fhe_stream_t)st.st(), res.trlwedevices[d], cs.trgswdevices[d], c1.trlwedevices[d],
+                                 c0.trlwedevices[d], 1, 0));
+}
+// CMUXNTT (src/cufhe_gates_gpu.cu:69-85): H2D of cs, c1, c0; CMUX; D2H of res
+inline void CMUXNTT(cuFHETRLWElvl1& res, cuFHETRGSWNTTlvl1& cs, cuFHETRLWElvl1& c1, cuFHETRLWElvl1& c0, Stream st)
+{
+    const int d = st.device_id();
+    cudaSetDevice(d);
+    cudaMemcpyAsync(cs.trgswdevices[d], cs.trgswhost.data(), sizeof(cs.trgswhost), cudaMemcpyHostToDevice, st.st());
+    _trlweH2D(c1, st);
+    _trlweH2D(c0, st);
+    gCMUXNTT(res, cs, c1, c0, st);
+    _trlweD2H(res, st);
 }
 
 }  // namespace cufhe

@@ -191,17 +191,43 @@ static inline uint32_t rotated_minus_one(const uint32_t *poly, unsigned c, uint3
     return temp + DECOMP_OFFSET + DECOMP_ROUND;
 }
 
+static void ext_product_accumulate(uint32_t *acc, int32_t (*dig)[ORC_N], const uint32_t *bk_i, int use_schoolbook);
+
 void orc_cmux_step(uint32_t *acc, uint32_t abar, const uint32_t *bk_i, int use_schoolbook)
 {
     /* Accumulate<P> (gatebootstrapping_gpu.cuh:115-285): rows j*l+digit, outputs out_k,
      * BK index ((k+1)*row + out_k) * N + coeff (:217) */
-    int32_t dig[4][ORC_N];
+    static _Thread_local int32_t dig[4][ORC_N];
     for (int j = 0; j < 2; j++)
         for (unsigned c = 0; c < ORC_N; c++) {
             uint32_t t = rotated_minus_one(acc + j * ORC_N, c, abar);
             dig[2 * j + 0][c] = gadget_digit(t, 0);
             dig[2 * j + 1][c] = gadget_digit(t, 1);
         }
+    ext_product_accumulate(acc, dig, bk_i, use_schoolbook);
+}
+
+/* CMUXNTT (src/bootstrap_gpu.cu:162-285, src/cufhe_gates_gpu.cu:69-85):
+ * out = c0 + (c1 - c0) [.] TRGSW, decomposition with the same offsets as the blind rotation
+ * (TRLWESubAndDecomposition :162-194); trgsw = raw TRGSW<lvl1param> [4 rows][2][1024] */
+void orc_cmux(uint32_t *out, const uint32_t *trgsw, const uint32_t *c1, const uint32_t *c0, int use_schoolbook)
+{
+    static _Thread_local int32_t dig[4][ORC_N];
+    for (int j = 0; j < 2; j++)
+        for (unsigned c = 0; c < ORC_N; c++) {
+            uint32_t t = c1[j * ORC_N + c] - c0[j * ORC_N + c] + DECOMP_OFFSET + DECOMP_ROUND;
+            dig[2 * j + 0][c] = gadget_digit(t, 0);
+            dig[2 * j + 1][c] = gadget_digit(t, 1);
+        }
+    uint32_t acc[2 * ORC_N];
+    memcpy(acc, c0, sizeof acc);
+    ext_product_accumulate(acc, dig, trgsw, use_schoolbook);
+    memcpy(out, acc, sizeof acc);
+}
+
+/* acc += sum_row dig[row] (*) bk_i[row][out]  (negacyclic, exact, mod 2^32) */
+static void ext_product_accumulate(uint32_t *acc, int32_t (*dig)[ORC_N], const uint32_t *bk_i, int use_schoolbook)
+{
     if (use_schoolbook) {
         /* exact integer convolution; wrapping u32 accumulation == (sum mod 2^32) */
         for (int o = 0; o < 2; o++) {

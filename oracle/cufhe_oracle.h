@@ -71,6 +71,10 @@ void orc_polymul_ntt(uint32_t *out, const uint32_t *a, const uint32_t *b);
 void orc_cmux_step(uint32_t *acc /*[2][1024]*/, uint32_t abar,
                    const uint32_t *bk_i /*[4][2][1024]*/, int use_schoolbook);
 
+/* CMUXNTT (src/bootstrap_gpu.cu:162-285): out = c0 + (c1 - c0) [.] TRGSW on TRLWEs [2][1024],
+ * trgsw = raw TFHEpp::TRGSW<lvl1param> [4][2][1024] */
+void orc_cmux(uint32_t *out, const uint32_t *trgsw, const uint32_t *c1, const uint32_t *c0, int use_schoolbook);
+
 /* blind rotation of the lvl0 TLWE c (already the linear combination) with test
  * vector mu, followed by SampleExtract(0): out is a lvl1 TLWE.
  * (gatebootstrapping_gpu.cuh:287-345, bootstrap_gpu.cu:366-381) */

@@ -144,6 +144,16 @@ def cmux_step(acc, abar, bk_i, schoolbook=False):
     return acc.reshape(2, N)
 
 
+def cmux(trgsw, c1, c0, schoolbook=False):
+    """CMUXNTT: c0 + (c1 - c0) [.] trgsw on TRLWEs (2 x 1024 u32); trgsw raw [4][2][1024]."""
+    trgsw = np.ascontiguousarray(trgsw, dtype=np.uint32)
+    c1 = np.ascontiguousarray(c1, dtype=np.uint32)
+    c0 = np.ascontiguousarray(c0, dtype=np.uint32)
+    out = np.zeros(2 * N, np.uint32)
+    lib().orc_cmux(_p(out), _p(trgsw), _p(c1), _p(c0), int(schoolbook))
+    return out
+
+
 def polymul(a, b, schoolbook=True):
     a = np.ascontiguousarray(a, dtype=np.uint32)
     b = np.ascontiguousarray(b, dtype=np.uint32)

@@ -159,6 +159,35 @@ def test_trlwe_level_entry_points(engine, keys):
     assert list(orc.decrypt(keys, out.tlwehost, 0)) == list(bits)
 
 
+@pytest.mark.parametrize("cnt,shared", [(3, False), (3, True), (600, False)])
+def test_cmux_ntt(engine, cnt, shared):
+    """TRGSW2NTT + CMUXNTT (res = c0 + (c1 - c0) [.] cs), bytes against the
+    oracle's exact product; per-item and shared TRGSW; both kernel instantiations; extreme
+    operands; out aliasing c0."""
+    cf = engine
+    rng = np.random.default_rng(11 + cnt)
+    ncs = 1 if shared else cnt
+    tg = rng.integers(0, 2**32, (ncs, 4, 2, 1024), dtype=np.uint64).astype(np.uint32)
+    c1 = rng.integers(0, 2**32, (cnt, 2048), dtype=np.uint64).astype(np.uint32)
+    c0 = rng.integers(0, 2**32, (cnt, 2048), dtype=np.uint64).astype(np.uint32)
+    tg[0, 1] = 0xFFFFFFFF                   # maximal key coefficients in one row
+    c1[1], c0[1] = 0x7FFFFFFF, 0x80000000   # every digit extreme
+    c1[2] = c0[2]                           # c1 - c0 = 0: digits = rounding only
+    st = cf.Stream(0).Create()
+    cs = cf.cuFHETRGSWNTTlvl1(ncs)
+    cf.TRGSW2NTT(cs, tg, st)
+    t1, t0, res = cf.cuFHETRLWElvl1(cnt).set(c1), cf.cuFHETRLWElvl1(cnt).set(c0), cf.cuFHETRLWElvl1(cnt)
+    cf.CMUXNTT(res, cs, t1, t0, st)
+    cf.gCMUXNTT(t0, cs, t1, t0, st)         # in place: out aliases c0
+    with torch.cuda.stream(st.torch_stream()):
+        t0._host_t.copy_(t0.trlwedevice, non_blocking=True)
+    cf.Synchronize()
+    for i in (range(cnt) if cnt < 10 else (0, 1, 2, 3, 299, 598, 599)):
+        want = orc.cmux(tg[0 if shared else i], c1[i], c0[i])
+        assert np.array_equal(res.trlwehost[i], want), i
+        assert np.array_equal(t0.trlwehost[i], want), ("alias", i)
+
+
 # ------------------------------------------------------------------- gates ---
 @pytest.mark.parametrize("level", [0, 1])
 def test_all_gates_bit_exact_and_decrypt(engine, keys, level):
