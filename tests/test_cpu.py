@@ -79,6 +79,38 @@ def test_golden_fixture(keys):
         assert out[0, :4].tolist() == G[f"nand_lvl{level}_first_words"]
 
 
+def test_oracle_trlwe_level_and_cmux(keys):
+    """SURVEY.md 8f ranks 2-3 on the oracle: TLWE2TRLWE / SampleExtract+KeySwitch / Refresh keep
+    the plaintext; CMUX by exact NTT == schoolbook, and selects c1 / c0 at decrypt level."""
+    c = orc.encrypt(keys, [1, 0], 0, base_index=31)
+    for i, bit in enumerate((1, 0)):
+        t = orc.blind_rotate_trlwe(keys, c[i])
+        e = orc.blind_rotate_extract(keys, c[i])
+        assert e[0] == t[0] and e[N] == t[N] and e[1] == (-int(t[N - 1])) % 2**32
+        back = orc.sample_extract_keyswitch(keys, orc.refresh(keys, t))
+        assert orc.decrypt(keys, back[None], 0)[0] == bit
+    rng = np.random.default_rng(5)
+    tg = rng.integers(0, 2**32, (4, 2, N), dtype=np.uint64).astype(np.uint32)
+    c1 = rng.integers(0, 2**32, 2 * N, dtype=np.uint64).astype(np.uint32)
+    c0 = rng.integers(0, 2**32, 2 * N, dtype=np.uint64).astype(np.uint32)
+    assert np.array_equal(orc.cmux(tg, c1, c0, schoolbook=False), orc.cmux(tg, c1, c0, schoolbook=True))
+    # selector semantics with the real key: BK_i encrypts key bit s_i, so CMUX(BK_i, c1, c0)
+    # decrypts like c1 when s_i = 1 and like c0 when s_i = 0
+    t1 = orc.blind_rotate_trlwe(keys, c[0])          # encrypts +mu pattern (bit 1)
+    t0 = orc.blind_rotate_trlwe(keys, c[1])          # bit 0
+    bk = keys.bk.reshape(636, 4, 2, N)
+    for i in (0, 1, 2, 3):
+        sel = orc.cmux(bk[i], t1, t0)
+        got = orc.decrypt(keys, orc.sample_extract_keyswitch(keys, sel)[None], 0)[0]
+        assert got == (1 if keys.sk0[i] else 0), i
+
+
+def test_adder_netlist_gate_count():
+    from cufhe_b200.circuits import adder_gate_count
+    assert adder_gate_count(32) == 32 + 31 + 2 * 30 + 31
+    assert adder_gate_count(8) == 8 + 7 + 12 + 7
+
+
 # ------------------------------------- CUDA arithmetic, emulated on the CPU ---
 def test_warp_emulation_of_cuda_ntt_and_cmux(tmp_path):
     """Compiles the SAME host+device headers the kernels use and runs the warp-level

@@ -1,0 +1,45 @@
+"""Single-process multi-GPU path (the reference's model, test/test_gate_gpu_multi.cc:36-72):
+SetGPUNum(n) + Initialize replicate the keys with peer copies, gate batches are partitioned
+across the devices, results are byte-identical to the oracle.  Needs >= 2 GPUs (skipped on a
+one-GPU box; run with `gpurun --gpus 2`)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import orc
+
+pytestmark = pytest.mark.gpu
+
+
+def test_partitioned_batch_on_all_gpus(engine, keys):
+    n = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    cf = engine            # session engine (1 GPU): torn down here, restored in `finally`
+    cf.CleanUp()
+    cf.SetGPUNum(n)
+    cf.Initialize(keys.bk, keys.ksk)
+    try:
+        cnt = 4 * n + 1
+        b0 = np.arange(cnt) & 1
+        b1 = (np.arange(cnt) >> 1) & 1
+        x0 = orc.encrypt(keys, b0, 0, base_index=7000)
+        x1 = orc.encrypt(keys, b1, 0, base_index=8000)
+        want = orc.gate_batch(keys, orc.OP["XOR"], 0, x0, x1)
+        outs = []
+        for d in range(n):
+            lo, hi = cf.partition(cnt, n, d)
+            st = cf.Stream(d).Create()
+            a = cf.Ctxt(hi - lo, 0, device=d).set(x0[lo:hi])
+            b = cf.Ctxt(hi - lo, 0, device=d).set(x1[lo:hi])
+            o = cf.Ctxt(hi - lo, 0, device=d)
+            cf.Xor(o, a, b, st)
+            outs.append(o)
+        cf.Synchronize()
+        got = np.concatenate([o.tlwehost for o in outs])
+        assert np.array_equal(got, want)
+        assert list(orc.decrypt(keys, got, 0)) == list(b0 ^ b1)
+    finally:
+        cf.CleanUp()
+        cf.SetGPUNum(1)
+        cf.Initialize(keys.bk, keys.ksk)
