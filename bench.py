@@ -92,7 +92,8 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample = max(8, 4 * (os.cpu_count() or 1))
+    # a bounded sample of the same workload: ~3 s of CPU work per step on a 16-core host
+    sample = max(64, 256 * (os.cpu_count() or 1))
     vals = []
     for i in range(args.warmup + args.steps):
         b = cpu_baseline(sample)
@@ -233,7 +234,8 @@ def run_product(args):
         cf._lib.check(L.b2fhe_int_peak(local, 0, C.byref(g0)))
         cf._lib.check(L.b2fhe_int_peak(local, 1, C.byref(g1)))
         slots = IMAD_SLOTS_PER_GATE * cnt / br_s * 1e-9
-        cb = cpu_baseline(max(8, 4 * (os.cpu_count() or 1))) if world == 1 else None
+        # ~10-15 s of CPU work: 1024 gates per host thread
+        cb = cpu_baseline(max(64, 1024 * (os.cpu_count() or 1))) if world == 1 else None
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
