@@ -24,6 +24,13 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
     const int variant = g_br_variant ? g_br_variant : 16;
     int g = g_gates_per_cta;
     const int per_sm = (P.count + c.sm_count - 1) / c.sm_count;
+    // a handful of gates: one gate per cluster of 8 CTAs on 8 SMs
+    if (variant == 2 || (g_br_variant == 0 && g == 0 && P.count <= g_br_cluster_max)) {
+        P.bk = c.bk_ntt16;
+        k_blind_rotate_cl<<<P.count * kClCtas, 64, kClSmemBytes, st>>>(P, c.tab16);
+        LAUNCHED();
+        return 0;
+    }
     // small batches (<= 1 gate per SM; measured faster than k_blind_rotate16 only there): one gate per 512-thread CTA, 1 + 1 transforms on the
     // critical path of a CMUX step instead of 4 + 2
     if (variant == 1 || (g_br_variant == 0 && g == 0 && per_sm <= 1)) {

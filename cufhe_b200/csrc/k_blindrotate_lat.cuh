@@ -89,13 +89,20 @@ __global__ void __launch_bounds__(kLatThreads, 1) k_blind_rotate_lat(const BrPar
             const uint32_t t = rot - aj[T + 64 * k] + kDecompAdd;
             x[k] = ((t >> dshift) & 0xFFu) + dig_off;                     // digit + p in [0, 2p)
         }
-        fwd16(x, bufA, bufB, s_tab, xa, T, q, p, bar_team, 64);
+        // key row fetched BEFORE the transform (its barriers are compiler memory fences, so the
+        // loads would otherwise be issued only after it and their L2 latency would be exposed)
         const uint4* row = bk4 + (size_t)i * kRows * (4 * (kN / 4));
+        uint4 kb[8];
+#pragma unroll
+        for (int o = 0; o < 2; o++)
+#pragma unroll
+            for (int v = 0; v < 4; v++) kb[4 * o + v] = __ldg(row + o * (kN / 4) + v * 64);
+        fwd16(x, bufA, bufB, s_tab, xa, T, q, p, bar_team, 64);
 #pragma unroll
         for (int o = 0; o < 2; o++)
 #pragma unroll
             for (int v = 0; v < 4; v++) {
-                const uint4 b = __ldg(row + o * (kN / 4) + v * 64);
+                const uint4 b = kb[4 * o + v];
                 uint32_t* dst = my_part + o * kN + (4 * v) * 64;
                 dst[0] = (uint32_t)umontmul_p(x[4 * v + 0], b.x, p, pinv) + p;   // (0, 2p)
                 dst[64] = (uint32_t)umontmul_p(x[4 * v + 1], b.y, p, pinv) + p;

@@ -133,8 +133,9 @@ int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, co
 
 /* tuning / introspection */
 int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
-/* blind-rotation kernel: 0 = default (k_blind_rotate_lat for batches of at most 2 gates per
- * SM, else k_blind_rotate16), 1 = k_blind_rotate_lat (one gate per 512-thread CTA), 16 =
+/* blind-rotation kernel: 0 = default (k_blind_rotate_cl up to 8 gates, k_blind_rotate_lat up
+ * to one gate per SM, else k_blind_rotate16), 1 = k_blind_rotate_lat (one gate per 512-thread
+ * CTA), 2 = k_blind_rotate_cl (one gate per cluster of 8 CTAs on 8 SMs), 16 =
  * k_blind_rotate16 (128 threads x 16 coefficients per gate), 32 = k_blind_rotate (64 threads
  * x 32 coefficients per gate).  All produce identical bits. */
 int b2fhe_set_br_variant(int variant);
