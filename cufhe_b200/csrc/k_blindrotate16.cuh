@@ -169,13 +169,9 @@ __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, 
                 sb[4 * v + 3] += (uint32_t)umontmul_p(x[4 * v + 3], b.w, p, pinv);
             }
         }
-        // two inverse transforms through ONE code copy: transform sb, swap, transform (old) sa
-#pragma unroll 1
-        for (int t = 0; t < 2; t++) {
-            inv16(sb, bufA, bufB, s_tab, xa, T, q, p, bar);
-#pragma unroll
-            for (int k = 0; k < 16; k++) { const uint32_t tmp = sa[k]; sa[k] = sb[k]; sb[k] = tmp; }
-        }
+        // two inverse transforms (two code copies: no register swap between them)
+        inv16(sb, bufA, bufB, s_tab, xa, T, q, p, bar);
+        inv16(sa, bufA, bufB, s_tab, xa, T, q, p, bar);
         // now sa = INTT(out q) (mine), sb = INTT(out 1-q): hand sb to the other team
 #pragma unroll
         for (int k = 0; k < 16; k++) bufA[T + 64 * k] = sb[k];
