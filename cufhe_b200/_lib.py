@@ -22,7 +22,8 @@ NVCC_FLAGS = [
 SYMBOLS = [
     "b2fhe_init", "b2fhe_init_device", "b2fhe_adopt_keys", "b2fhe_key_pointers", "b2fhe_cleanup",
     "b2fhe_num_devices", "b2fhe_last_error_string", "b2fhe_gate_batch", "b2fhe_gate_batch_mixed",
-    "b2fhe_gate_batch_host", "b2fhe_synchronize", "b2fhe_blind_rotate_batch", "b2fhe_keyswitch_batch",
+    "b2fhe_gate_batch_host", "b2fhe_synchronize", "b2fhe_gate_batch_ptrs", "b2fhe_defer_gate", "b2fhe_defer_h2d", "b2fhe_defer_d2h",
+    "b2fhe_defer_flush", "b2fhe_defer_fence", "b2fhe_defer_fence_buffer", "b2fhe_defer_query", "b2fhe_defer_pending", "b2fhe_blind_rotate_batch", "b2fhe_keyswitch_batch",
     "b2fhe_bootstrap_tlwe2trlwe_batch", "b2fhe_sample_extract_keyswitch_batch", "b2fhe_refresh_batch", "b2fhe_trgsw2ntt_batch", "b2fhe_cmux_ntt_batch",
     "b2fhe_ntt1024_batch", "b2fhe_intt1024_batch", "b2fhe_polymul1024_batch",
     "b2fhe_set_gates_per_cta", "b2fhe_set_br_variant", "b2fhe_set_ks_variant", "b2fhe_kernel_launches", "b2fhe_int_peak",
@@ -66,6 +67,15 @@ def lib():
     L.b2fhe_gate_batch.argtypes = [i32, vp, i32, i32, vp, vp, vp, vp, sz]
     L.b2fhe_gate_batch_mixed.argtypes = [i32, vp, vp, i32, vp, vp, vp, vp, sz]
     L.b2fhe_gate_batch_host.argtypes = [i32, vp, i32, vp, i32, vp, vp, vp, vp, sz]
+    L.b2fhe_gate_batch_ptrs.argtypes = [i32, vp, vp, i32, vp, vp, vp, vp, sz]
+    L.b2fhe_defer_gate.argtypes = [i32, vp, i32, i32, vp, vp, vp, vp]
+    L.b2fhe_defer_d2h.argtypes = [i32, vp, vp, sz]
+    L.b2fhe_defer_h2d.argtypes = [i32, vp, vp, sz]
+    L.b2fhe_defer_flush.argtypes = [i32]
+    L.b2fhe_defer_fence.argtypes = [i32, vp]
+    L.b2fhe_defer_fence_buffer.argtypes = [i32, vp, vp]
+    L.b2fhe_defer_query.argtypes = [i32, C.POINTER(i32)]
+    L.b2fhe_defer_pending.argtypes = [i32]
     L.b2fhe_blind_rotate_batch.argtypes = [i32, vp, vp, vp, C.c_uint32, sz]
     L.b2fhe_keyswitch_batch.argtypes = [i32, vp, vp, vp, sz]
     L.b2fhe_bootstrap_tlwe2trlwe_batch.argtypes = [i32, vp, vp, vp, C.c_uint32, sz]

@@ -2,6 +2,7 @@
 // Host-side counterpart of the reference's launch wrappers and key upload
 // (src/bootstrap_gpu.cu:97-155,782-1292, src/keyswitch_gpu.cu, src/cufhe_gates_gpu.cu).
 #include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -38,6 +39,8 @@ int g_gates_per_cta = 0;
 int g_ks_variant = 0;            // 0 = by batch size, 1 = k_keyswitch_lat, 2 = k_keyswitch
 int g_ks_lat_max_per_sm = 32;    // k_keyswitch_lat up to this many gates per SM (measured faster up to there)
 int g_br_cluster_max = 8;        // k_blind_rotate_cl for batches up to this many gates (8 clusters run concurrently on B200)
+int g_br_burst_detect = 1;       // small calls arriving back to back use the throughput kernel
+constexpr int64_t kBurstGapNs = 300000;
 int g_br_variant = 0;            // 0 = default, 1 = k_blind_rotate_lat, 2 = k_blind_rotate_cl, 16 = k_blind_rotate16, 32 = k_blind_rotate
 std::atomic<uint64_t> g_launches{0};
 thread_local std::string t_err;
@@ -172,6 +175,10 @@ int convert_keys(int device, const uint32_t* bk_raw, const uint16_t* ksk_raw)
     return 0;
 }
 
+int defer_flush_all();      // b2fhe_defer.inl
+int defer_destroy_all();
+void defer_mark_idle_all();
+
 int get_ctx(int device, DevCtx*& c)
 {
     REQUIRE(device >= 0 && device < kMaxDev, B2FHE_E_NO_DEVICE);
@@ -273,6 +280,7 @@ int b2fhe_key_pointers(int device, void** bk_ntt_dev, void** ksk_dev)
 
 int b2fhe_cleanup(void)
 {
+    if (int r = defer_flush_all()) return r;
     std::lock_guard<std::mutex> lk(g_mu);
     for (int d = 0; d < kMaxDev; d++) {
         DevCtx& c = g_ctx[d];
@@ -285,16 +293,20 @@ int b2fhe_cleanup(void)
         if (c.bk_ntt16) CK(cudaFree(c.bk_ntt16));
         c = DevCtx();
     }
+    defer_destroy_all();
     return 0;
 }
 
 int b2fhe_synchronize(void)
 {
+    if (int r = defer_flush_all()) return r;      // queued per-gate calls run now
     for (int d = 0; d < kMaxDev; d++)
         if (g_ctx[d].ready) { CK(cudaSetDevice(d)); CK(cudaDeviceSynchronize()); }
+    defer_mark_idle_all();
     return 0;
 }
 
 }  // extern "C"
 
 #include "b2fhe_gates.inl"
+#include "b2fhe_defer.inl"

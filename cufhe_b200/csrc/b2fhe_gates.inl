@@ -24,8 +24,23 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
     const int variant = g_br_variant ? g_br_variant : 16;
     int g = g_gates_per_cta;
     const int per_sm = (P.count + c.sm_count - 1) / c.sm_count;
+    // The two latency kernels spend several SMs (or a whole SM) on one gate: right for an
+    // isolated small call, wrong when small calls arrive back to back on many streams (the
+    // reference's usage, test/test_gate_gpu.cc: one gate per call, one stream per SM) -- then
+    // throughput matters and the 128-thread-per-gate kernel packs 3 gates per SM.  A small
+    // call issued within kBurstGapNs of the previous one on this device counts as a burst.
+    bool burst = false;
+    if (per_sm <= 1) {
+        static std::atomic<int64_t> last_ns[kMaxDev];
+        const int64_t now = std::chrono::duration_cast<std::chrono::nanoseconds>(
+                                std::chrono::steady_clock::now().time_since_epoch()).count();
+        int dev = 0;
+        cudaGetDevice(&dev);
+        const int64_t prev = last_ns[dev].exchange(now, std::memory_order_relaxed);
+        burst = g_br_burst_detect && prev != 0 && now - prev < kBurstGapNs;
+    }
     // a handful of gates: one gate per cluster of 8 CTAs on 8 SMs
-    if (variant == 2 || (g_br_variant == 0 && g == 0 && P.count <= g_br_cluster_max)) {
+    if (variant == 2 || (g_br_variant == 0 && g == 0 && !burst && P.count <= g_br_cluster_max)) {
         P.bk = c.bk_ntt16;
         k_blind_rotate_cl<<<P.count * kClCtas, 64, kClSmemBytes, st>>>(P, c.tab16);
         LAUNCHED();
@@ -33,7 +48,7 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
     }
     // small batches (<= 1 gate per SM; measured faster than k_blind_rotate16 only there): one gate per 512-thread CTA, 1 + 1 transforms on the
     // critical path of a CMUX step instead of 4 + 2
-    if (variant == 1 || (g_br_variant == 0 && g == 0 && per_sm <= 1)) {
+    if (variant == 1 || (g_br_variant == 0 && g == 0 && !burst && per_sm <= 1)) {
         P.bk = c.bk_ntt16;
         k_blind_rotate_lat<<<P.count, kLatThreads, kLatSmemBytes, st>>>(P, c.tab16);
         LAUNCHED();

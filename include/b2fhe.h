@@ -83,7 +83,31 @@ int b2fhe_gate_batch_mixed(int device, b2fhe_stream_t stream, const uint8_t* ops
 int b2fhe_gate_batch_host(int device, b2fhe_stream_t stream, int op, const uint8_t* ops_host, int level,
                           void* out_host, const void* in0_host, const void* in1_host,
                           const void* in2_host, size_t count);
-int b2fhe_synchronize(void);   /* Synchronize(): all devices (include/cufhe_gpu.cuh:68-74) */
+int b2fhe_synchronize(void);   /* Synchronize(): flushes the deferred queues, then waits for all
+                                  devices (include/cufhe_gpu.cuh:68-74) */
+/* gates over SCATTERED device buffers (one pointer per gate; host arrays of device pointers;
+ * in1/in2 entries may be null where the op does not read them): gather -> batch -> scatter */
+int b2fhe_gate_batch_ptrs(int device, b2fhe_stream_t stream, const uint8_t* ops_host, int level,
+                          void* const* out, const void* const* in0, const void* const* in1,
+                          const void* const* in2, size_t count);
+/* ---- deferred per-gate queue: how the legacy one-gate-per-call API (src/cufhe_gates_gpu.cu:
+ * 148-665) gets batch-major execution.  b2fhe_defer_gate queues ONE gate on device buffers
+ * (work already issued on `user_stream`, e.g. the H2D of its operands, is ordered before it);
+ * the queue runs at b2fhe_defer_flush / b2fhe_defer_fence / b2fhe_defer_query /
+ * b2fhe_synchronize as one batched launch sequence per dependency level (a gate that reads a
+ * queued gate's output runs one level later; program order is preserved for write-after-read
+ * and write-after-write).  b2fhe_defer_d2h queues a device-to-host copy after the gates. */
+int b2fhe_defer_gate(int device, b2fhe_stream_t user_stream, int op, int level, void* out,
+                     const void* in0, const void* in1, const void* in2);
+int b2fhe_defer_h2d(int device, void* dev_dst, const void* host_src, size_t bytes);   /* operand
+    upload, done when the queue runs; skipped if a queued or running gate produces dev_dst */
+int b2fhe_defer_d2h(int device, void* host_dst, const void* dev_src, size_t bytes);
+int b2fhe_defer_flush(int device);                          /* asynchronous */
+int b2fhe_defer_fence(int device, b2fhe_stream_t stream);   /* flush; `stream` waits for it */
+int b2fhe_defer_fence_buffer(int device, b2fhe_stream_t stream, const void* buffer); /* the fence, only
+                                                               if a queued gate reads or writes `buffer` */
+int b2fhe_defer_query(int device, int* busy);               /* flush; *busy = 1 while running */
+int b2fhe_defer_pending(int device);                        /* queued operations */
 
 /* ---- stages (next-tier entry points) ---------------------------------
  * blind rotation + SampleExtract(0) of c = in (lvl0, device) -> lvl1 TLWE (device):

@@ -49,7 +49,20 @@ inline void Initialize(const TFHEpp::EvalKey& ek)
                        reinterpret_cast<const uint16_t*>(&ek.getiksk<TFHEpp::lvl10param>())));
 }
 inline void CleanUp() { B2CHECK(b2fhe_cleanup()); }
+// Synchronize(): runs the queued per-gate calls (see SetDeferred) and waits for every device
 inline void Synchronize() { B2CHECK(b2fhe_synchronize()); }
+// Per-gate calls (Nand(out, in0, in1, st) ... on single Ctxt<P>) are QUEUED and executed at
+// Synchronize()/StreamQuery() as batched launches levelised by their data dependencies --
+// one kernel per gate, the reference's execution model, starves this engine's batch-major
+// kernels.  Results are defined exactly when the reference defines them: after
+// Synchronize() or a successful StreamQuery().  SetDeferred(false) restores immediate
+// one-launch-per-call execution (lowest latency for a single isolated gate).
+inline bool& _deferredRef() { static bool on = true; return on; }
+inline void SetDeferred(bool on)
+{
+    if (!on) Synchronize();
+    _deferredRef() = on;
+}
 
 class Stream {
 public:
@@ -75,8 +88,10 @@ private:
 };
 inline bool StreamQuery(Stream st)
 {
+    int busy = 0;
+    B2CHECK(b2fhe_defer_query(st.device_id(), &busy));      // queued gates start now
     cudaSetDevice(st.device_id());
-    return cudaStreamQuery(st.st()) == cudaSuccess;
+    return !busy && cudaStreamQuery(st.st()) == cudaSuccess;
 }
 
 // a batch of `count` ciphertexts: pinned host array + one device buffer per GPU
@@ -122,6 +137,8 @@ struct Ctxt {
     }
     ~Ctxt()
     {
+        for (int i = 0; i < (int)tlwedevices.size(); i++)
+            if (b2fhe_defer_pending(i) > 0) { b2fhe_synchronize(); break; }      // queued gates may use this buffer
         cudaHostUnregister(tlwehost.data());
         for (size_t i = 0; i < tlwedevices.size(); i++) {
             cudaSetDevice((int)i);
@@ -136,31 +153,52 @@ struct Ctxt {
 
 template <class P> inline void CtxtCopyH2D(Ctxt<P>& c, Stream st)
 {
+    // stream order: a copy into a buffer that a queued gate still reads or writes runs after it
+    B2CHECK(b2fhe_defer_fence_buffer(st.device_id(), (b2fhe_stream_t)st.st(), c.tlwedevices[st.device_id()]));
     cudaSetDevice(st.device_id());
     cudaMemcpyAsync(c.tlwedevices[st.device_id()], c.tlwehost.data(), sizeof(c.tlwehost), cudaMemcpyHostToDevice, st.st());
 }
 template <class P> inline void CtxtCopyD2H(Ctxt<P>& c, Stream st)
 {
+    B2CHECK(b2fhe_defer_fence(st.device_id(), (b2fhe_stream_t)st.st()));
     cudaSetDevice(st.device_id());
     cudaMemcpyAsync(c.tlwehost.data(), c.tlwedevices[st.device_id()], sizeof(c.tlwehost), cudaMemcpyDeviceToHost, st.st());
 }
 template <class P> inline void CtxtCopyH2D(CtxtBatch<P>& c, Stream st)
 {
+    B2CHECK(b2fhe_defer_fence_buffer(st.device_id(), (b2fhe_stream_t)st.st(), c.tlwedevices[st.device_id()]));
     cudaSetDevice(st.device_id());
     cudaMemcpyAsync(c.tlwedevices[st.device_id()], c.tlwehost, c.bytes(), cudaMemcpyHostToDevice, st.st());
 }
 template <class P> inline void CtxtCopyD2H(CtxtBatch<P>& c, Stream st)
 {
+    B2CHECK(b2fhe_defer_fence(st.device_id(), (b2fhe_stream_t)st.st()));
     cudaSetDevice(st.device_id());
     cudaMemcpyAsync(c.tlwehost, c.tlwedevices[st.device_id()], c.bytes(), cudaMemcpyDeviceToHost, st.st());
 }
 template <class P> inline void CopyOnHost(Ctxt<P>& out, Ctxt<P>& in) { out.tlwehost = in.tlwehost; }
 
 // ---- gates ---------------------------------------------------------------------------
+template <class P> inline void* _hostptr(Ctxt<P>& c) { return c.tlwehost.data(); }
+template <class P> inline void* _hostptr(CtxtBatch<P>& c) { return c.tlwehost; }
 template <class P, class C>
 inline void _gate(int op, C& out, C* in0, C* in1, C* in2, size_t count, Stream st, bool copy)
 {
     const int d = st.device_id();
+    if (count == 1 && _deferredRef()) {
+        // legacy one-gate call: operand uploads, the gate and the copy-back are all queued and
+        // run as batched transfers + launches when the queue is flushed
+        if (copy) {
+            B2CHECK(b2fhe_defer_h2d(d, in0->tlwedevices[d], _hostptr<P>(*in0), sizeof(TFHEpp::TLWE<P>)));
+            if (in1) B2CHECK(b2fhe_defer_h2d(d, in1->tlwedevices[d], _hostptr<P>(*in1), sizeof(TFHEpp::TLWE<P>)));
+            if (in2) B2CHECK(b2fhe_defer_h2d(d, in2->tlwedevices[d], _hostptr<P>(*in2), sizeof(TFHEpp::TLWE<P>)));
+        }
+        B2CHECK(b2fhe_defer_gate(d, (b2fhe_stream_t)st.st(), op, _level<P>(), out.tlwedevices[d], in0->tlwedevices[d],
+                                 in1 ? in1->tlwedevices[d] : nullptr, in2 ? in2->tlwedevices[d] : nullptr));
+        if (copy) B2CHECK(b2fhe_defer_d2h(d, _hostptr<P>(out), out.tlwedevices[d], sizeof(TFHEpp::TLWE<P>)));
+        return;
+    }
+    B2CHECK(b2fhe_defer_fence(d, (b2fhe_stream_t)st.st()));     // immediate call: after anything queued
     if (copy) {
         CtxtCopyH2D<P>(*in0, st);
         if (in1) CtxtCopyH2D<P>(*in1, st);
@@ -254,6 +292,7 @@ inline void gGateBootstrappingTLWE2TRLWElvl01NTT(cuFHETRLWElvl1& out, Ctxt<TFHEp
 {
     const int d = st.device_id();
     cudaSetDevice(d);
+    B2CHECK(b2fhe_defer_fence(d, (b2fhe_stream_t)st.st()));
     B2CHECK(b2fhe_bootstrap_tlwe2trlwe_batch(d, (b2fhe_stream_t)st.st(), out.trlwedevices[d], in.tlwedevices[d],
                                              TFHEpp::lvl1param::μ, 1));
 }
@@ -268,6 +307,7 @@ inline void gSampleExtractAndKeySwitch(Ctxt<TFHEpp::lvl0param>& out, const cuFHE
     const int d = st.device_id();
     cudaSetDevice(d);
     _trlweH2D(in, st);      // the reference's g-variant copies too (src/cufhe_gates_gpu.cu:139-146)
+    B2CHECK(b2fhe_defer_fence(d, (b2fhe_stream_t)st.st()));
     B2CHECK(b2fhe_sample_extract_keyswitch_batch(d, (b2fhe_stream_t)st.st(), out.tlwedevices[d], in.trlwedevices[d], 1));
 }
 inline void SampleExtractAndKeySwitch(Ctxt<TFHEpp::lvl0param>& out, const cuFHETRLWElvl1& in, Stream st)
@@ -279,6 +319,7 @@ inline void gRefresh(cuFHETRLWElvl1& out, cuFHETRLWElvl1& in, Stream st)
 {
     const int d = st.device_id();
     cudaSetDevice(d);
+    B2CHECK(b2fhe_defer_fence(d, (b2fhe_stream_t)st.st()));
     B2CHECK(b2fhe_refresh_batch(d, (b2fhe_stream_t)st.st(), out.trlwedevices[d], in.trlwedevices[d], TFHEpp::lvl1param::μ, 1));
 }
 inline void Refresh(cuFHETRLWElvl1& out, cuFHETRLWElvl1& in, Stream st)
@@ -324,6 +365,7 @@ inline void TRGSW2NTT(cuFHETRGSWNTTlvl1& trgswntt, const TFHEpp::TRGSW<TFHEpp::l
     uint32_t* raw = nullptr;
     cudaMallocAsync((void**)&raw, sizeof(trgsw), st.st());
     cudaMemcpyAsync(raw, trgsw.data(), sizeof(trgsw), cudaMemcpyHostToDevice, st.st());
+    B2CHECK(b2fhe_defer_fence(d, (b2fhe_stream_t)st.st()));
     B2CHECK(b2fhe_trgsw2ntt_batch(d, (b2fhe_stream_t)st.st(), trgswntt.trgswdevices[d], raw, 1));
     cudaFreeAsync(raw, st.st());
     cudaMemcpyAsync(trgswntt.trgswhost.data(), trgswntt.trgswdevices[d], sizeof(trgswntt.trgswhost), cudaMemcpyDeviceToHost, st.st());
@@ -332,6 +374,7 @@ inline void gCMUXNTT(cuFHETRLWElvl1& res, cuFHETRGSWNTTlvl1& cs, cuFHETRLWElvl1&
 {
     const int d = st.device_id();
     cudaSetDevice(d);
+    B2CHECK(b2fhe_defer_fence(d, (b2fhe_stream_t)st.st()));
     B2CHECK(b2fhe_cmux_ntt_batch(d, (b2fhe_stream_t)st.st(), res.trlwedevices[d], cs.trgswdevices[d], c1.trlwedevices[d],
                                  c0.trlwedevices[d], 1, 0));
 }

@@ -3,6 +3,7 @@
 // shape: Ctxt<P>, Stream, Nand(out, in0, in1, st) ..., Synchronize(), decrypt == truth.
 // Keys/encryption/decryption come from the test oracle (the box has no TFHEpp headers).
 // Also exercises the batched calls and checks ciphertext bytes against the oracle.
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <vector>
@@ -102,6 +103,82 @@ template <class P> static void run_level(const TFHEpp::EvalKey& ek, int kNumSMs)
     for (auto& x : st) x.Destroy();
 }
 
+// Dependent per-gate calls on device-resident ciphertexts (the reference's g-variants, as a
+// circuit built gate by gate would issue them): the deferred queue must respect read-after-
+// write, write-after-write and in-place updates; checked by bytes against the oracle, in
+// deferred and in immediate mode, then the per-gate API is timed.
+template <class P> static void run_chain(const TFHEpp::EvalKey& ek, int kNumSMs, bool deferred)
+{
+    const int level = sizeof(typename P::T) == 2 ? 0 : 1;
+    SetDeferred(deferred);
+    const int n = deferred ? 96 : 6;
+    std::vector<Stream> st(8);
+    for (auto& s : st) s.Create();
+    std::vector<Ctxt<P>> a(n), b(n), c(n), x(n), y(n);
+    int bad = 0;
+    for (int i = 0; i < n; i++) {
+        enc<P>(a[i].tlwehost, i & 1, 300000 + i);
+        enc<P>(b[i].tlwehost, (i >> 1) & 1, 310000 + i);
+        enc<P>(c[i].tlwehost, (i >> 2) & 1, 320000 + i);
+    }
+    std::vector<TFHEpp::TLWE<P>> wx(n), wy(n), wa(n);
+    for (int i = 0; i < n; i++) {
+        Stream s = st[i % st.size()];
+        CtxtCopyH2D<P>(a[i], s); CtxtCopyH2D<P>(b[i], s); CtxtCopyH2D<P>(c[i], s);
+        gNand<P>(x[i], a[i], b[i], s);              // x = NAND(a, b)
+        gXor<P>(y[i], x[i], c[i], s);               // y = XOR(x, c)           read after write
+        gMux<P>(y[i], y[i], x[i], a[i], s);         // y = y ? x : a           in place, after its writer
+        gAnd<P>(a[i], a[i], y[i], s);               // a = AND(a, y)           overwrites an operand of earlier gates
+        gNot<P>(x[i], x[i], s);                     // x = NOT(x)              write after read of x by the Mux
+        CtxtCopyD2H<P>(x[i], s); CtxtCopyD2H<P>(y[i], s); CtxtCopyD2H<P>(a[i], s);
+    }
+    for (auto& s : st) while (!StreamQuery(s)) {}
+    Synchronize();
+    for (int i = 0; i < (deferred ? 8 : n); i++) {
+        TFHEpp::TLWE<P> a0, t, u;
+        enc<P>(a0, i & 1, 300000 + i);
+        orc_gate(ORC_NAND, level, wx[i].data(), a0.data(), b[i].tlwehost.data(), nullptr, ek.bk.data(), ek.iksk.data());
+        orc_gate(ORC_XOR, level, t.data(), wx[i].data(), c[i].tlwehost.data(), nullptr, ek.bk.data(), ek.iksk.data());
+        orc_gate(ORC_MUX, level, wy[i].data(), t.data(), wx[i].data(), a0.data(), ek.bk.data(), ek.iksk.data());
+        orc_gate(ORC_AND, level, wa[i].data(), a0.data(), wy[i].data(), nullptr, ek.bk.data(), ek.iksk.data());
+        orc_gate(ORC_NOT, level, u.data(), wx[i].data(), nullptr, nullptr, ek.bk.data(), ek.iksk.data());
+        if (memcmp(u.data(), x[i].tlwehost.data(), sizeof u)) bad++;
+        if (memcmp(wy[i].data(), y[i].tlwehost.data(), sizeof u)) bad++;
+        if (memcmp(wa[i].data(), a[i].tlwehost.data(), sizeof u)) bad++;
+    }
+    for (int i = 0; i < n; i++) {
+        const int pa = i & 1, pb = (i >> 1) & 1, pc = (i >> 2) & 1;
+        const int px = 1 - pa * pb, t = px ^ pc, py = t ? px : pa;
+        if (dec<P>(x[i].tlwehost) != 1 - px || dec<P>(y[i].tlwehost) != py || dec<P>(a[i].tlwehost) != (pa & py)) bad++;
+    }
+    printf("level %d dependent per-gate chain (%s) : %s (%d chains x 5 gates)\n", level, deferred ? "deferred" : "immediate",
+           bad ? "FAIL" : "PASS", n);
+    failures += bad;
+    if (deferred) {
+        // the reference's benchmark loop (test/test_gate_gpu.cc:68-83): one NAND per call, round-robin streams
+        const int mmax = 64 * kNumSMs;
+        std::vector<Stream> ss(kNumSMs);
+        for (auto& s : ss) s.Create();
+        std::vector<Ctxt<P>> p(mmax), q(mmax), r(mmax);
+        for (int i = 0; i < mmax; i++) { enc<P>(p[i].tlwehost, i & 1, 400000 + i); enc<P>(q[i].tlwehost, (i >> 1) & 1, 500000 + i); }
+        for (int m : {16 * kNumSMs, mmax})
+            for (int rep = 0; rep < 2; rep++) {
+                const auto t0 = std::chrono::steady_clock::now();
+                for (int i = 0; i < m; i++) Nand<P>(r[i], p[i], q[i], ss[i % kNumSMs]);
+                Synchronize();
+                const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+                if (rep) printf("level %d per-gate API, %d NAND calls on %d streams: %.1f ms, %.0f gates/s\n", level, m, kNumSMs, sec * 1e3, m / sec);
+            }
+        int wrong = 0;
+        for (int i = 0; i < mmax; i++) wrong += dec<P>(r[i].tlwehost) != 1 - (i & 1) * ((i >> 1) & 1);
+        if (wrong) printf("level %d per-gate API results: FAIL (%d)\n", level, wrong);
+        failures += wrong;
+        for (auto& s : ss) s.Destroy();
+    }
+    for (auto& s : st) s.Destroy();
+    SetDeferred(true);
+}
+
 // TRLWE-level entry points (reference test/test_perf.cc shape: Refresh; plus
 // GateBootstrappingTLWE2TRLWElvl01NTT and SampleExtractAndKeySwitch), bytes vs the oracle
 static void run_trlwe(const TFHEpp::EvalKey& ek)
@@ -146,6 +223,9 @@ int main()
     Initialize(ek);
     run_level<lvl1param>(ek, kNumSMs);    // what test/test_gate_gpu.cc runs
     run_level<lvl0param>(ek, kNumSMs);    // what test/test_gate_gpu_multi.cc / test_intensive.cc run
+    run_chain<lvl1param>(ek, kNumSMs, true);
+    run_chain<lvl0param>(ek, kNumSMs, true);
+    run_chain<lvl1param>(ek, kNumSMs, false);
     run_trlwe(ek);
     CleanUp();
     printf(failures ? "FAILED (%d)\n" : "ALL PASS\n", failures);
