@@ -22,8 +22,10 @@ NVCC_FLAGS = [
 SYMBOLS = [
     "b2fhe_init", "b2fhe_init_device", "b2fhe_adopt_keys", "b2fhe_key_pointers", "b2fhe_cleanup",
     "b2fhe_num_devices", "b2fhe_last_error_string", "b2fhe_gate_batch", "b2fhe_gate_batch_mixed",
-    "b2fhe_gate_batch_host", "b2fhe_synchronize", "b2fhe_gate_batch_ptrs", "b2fhe_defer_gate", "b2fhe_defer_h2d", "b2fhe_defer_d2h",
-    "b2fhe_defer_flush", "b2fhe_defer_fence", "b2fhe_defer_fence_buffer", "b2fhe_defer_query", "b2fhe_defer_pending", "b2fhe_blind_rotate_batch", "b2fhe_keyswitch_batch",
+    "b2fhe_gate_batch_host", "b2fhe_wire_evalkey_size", "b2fhe_wire_evalkey_write", "b2fhe_wire_evalkey_parse",
+    "b2fhe_init_from_evalkey", "b2fhe_wire_tlwes_size", "b2fhe_wire_tlwes_write", "b2fhe_wire_tlwes_parse",
+    "b2fhe_key_cache_size", "b2fhe_key_cache_export", "b2fhe_init_from_key_cache", "b2fhe_synchronize", "b2fhe_gate_batch_ptrs", "b2fhe_defer_gate", "b2fhe_defer_h2d", "b2fhe_defer_d2h",
+    "b2fhe_defer_flush", "b2fhe_defer_fence", "b2fhe_defer_fence_buffer", "b2fhe_defer_query", "b2fhe_defer_pending", "b2fhe_blind_rotate_batch", "b2fhe_bootstrap_batch", "b2fhe_keyswitch_batch",
     "b2fhe_bootstrap_tlwe2trlwe_batch", "b2fhe_sample_extract_keyswitch_batch", "b2fhe_refresh_batch", "b2fhe_trgsw2ntt_batch", "b2fhe_cmux_ntt_batch",
     "b2fhe_ntt1024_batch", "b2fhe_intt1024_batch", "b2fhe_polymul1024_batch",
     "b2fhe_set_gates_per_cta", "b2fhe_set_br_variant", "b2fhe_set_ks_variant", "b2fhe_kernel_launches", "b2fhe_int_peak",
@@ -68,6 +70,19 @@ def lib():
     L.b2fhe_gate_batch_mixed.argtypes = [i32, vp, vp, i32, vp, vp, vp, vp, sz]
     L.b2fhe_gate_batch_host.argtypes = [i32, vp, i32, vp, i32, vp, vp, vp, vp, sz]
     L.b2fhe_gate_batch_ptrs.argtypes = [i32, vp, vp, i32, vp, vp, vp, vp, sz]
+    L.b2fhe_wire_evalkey_size.restype = sz
+    L.b2fhe_wire_evalkey_size.argtypes = []
+    L.b2fhe_wire_evalkey_write.argtypes = [vp, sz, vp, vp, C.POINTER(sz)]
+    L.b2fhe_wire_evalkey_parse.argtypes = [vp, sz, C.POINTER(sz), C.POINTER(sz)]
+    L.b2fhe_init_from_evalkey.argtypes = [i32, vp, sz]
+    L.b2fhe_wire_tlwes_size.restype = sz
+    L.b2fhe_wire_tlwes_size.argtypes = [i32, sz]
+    L.b2fhe_wire_tlwes_write.argtypes = [vp, sz, i32, vp, sz, C.POINTER(sz)]
+    L.b2fhe_wire_tlwes_parse.argtypes = [vp, sz, i32, C.POINTER(sz), C.POINTER(sz)]
+    L.b2fhe_key_cache_size.restype = sz
+    L.b2fhe_key_cache_size.argtypes = []
+    L.b2fhe_key_cache_export.argtypes = [i32, vp, sz, C.POINTER(sz)]
+    L.b2fhe_init_from_key_cache.argtypes = [i32, vp, sz]
     L.b2fhe_defer_gate.argtypes = [i32, vp, i32, i32, vp, vp, vp, vp]
     L.b2fhe_defer_d2h.argtypes = [i32, vp, vp, sz]
     L.b2fhe_defer_h2d.argtypes = [i32, vp, vp, sz]
@@ -77,6 +92,7 @@ def lib():
     L.b2fhe_defer_query.argtypes = [i32, C.POINTER(i32)]
     L.b2fhe_defer_pending.argtypes = [i32]
     L.b2fhe_blind_rotate_batch.argtypes = [i32, vp, vp, vp, C.c_uint32, sz]
+    L.b2fhe_bootstrap_batch.argtypes = [i32, vp, vp, vp, C.c_uint32, sz]
     L.b2fhe_keyswitch_batch.argtypes = [i32, vp, vp, vp, sz]
     L.b2fhe_bootstrap_tlwe2trlwe_batch.argtypes = [i32, vp, vp, vp, C.c_uint32, sz]
     L.b2fhe_sample_extract_keyswitch_batch.argtypes = [i32, vp, vp, vp, sz]
@@ -97,6 +113,9 @@ def lib():
 
 class B2FheError(RuntimeError):
     pass
+
+
+E_NOT_INITIALIZED, E_BAD_ARGUMENT, E_NO_DEVICE, E_BAD_FORMAT = 10001, 10002, 10003, 10004   # include/b2fhe.h
 
 
 def check(code):

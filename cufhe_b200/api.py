@@ -67,6 +67,61 @@ def Initialize(bk_raw, ksk_raw, device=None):
         _devices = [int(device)]
 
 
+def InitializeFromArchive(blob):
+    """Initialize from a serialised TFHEpp::EvalKey (cereal portable_binary, e.g. the TFHEpp
+    tutorial's cloud.key; TFHEpp/include/cloudkey.hpp:103-107) holding bk<lvl01> + iksk<lvl10>."""
+    global _devices
+    blob = np.ascontiguousarray(np.frombuffer(blob, dtype=np.uint8) if isinstance(blob, (bytes, bytearray, memoryview)) else blob,
+                                dtype=np.uint8)
+    _lib.check(_lib.lib().b2fhe_init_from_evalkey(_gpu_num, blob.ctypes.data, blob.size))
+    _devices = list(range(_gpu_num))
+
+
+def SerializeEvalKey(bk_raw, ksk_raw):
+    """The EvalKey archive TFHEpp itself would write for these raw keys (numpy uint8)."""
+    bk = np.ascontiguousarray(bk_raw, dtype=np.uint32).ravel()
+    ksk = np.ascontiguousarray(ksk_raw, dtype=np.uint16).ravel()
+    if bk.size != BK_RAW_WORDS or ksk.size != KSK_RAW_WORDS:
+        raise ValueError("key arrays have the wrong size for the default 128-bit parameter set")
+    L = _lib.lib()
+    blob = np.zeros(L.b2fhe_wire_evalkey_size(), np.uint8)
+    _lib.check(L.b2fhe_wire_evalkey_write(blob.ctypes.data, blob.size, bk.ctypes.data, ksk.ctypes.data, None))
+    return blob
+
+
+def ExportKeyCache(device=0):
+    """This engine's CONVERTED keys of `device` as one checksummed blob (numpy uint8)."""
+    L = _lib.lib()
+    blob = np.zeros(L.b2fhe_key_cache_size(), np.uint8)
+    _lib.check(L.b2fhe_key_cache_export(int(device), blob.ctypes.data, blob.size, None))
+    return blob
+
+
+def InitializeFromKeyCache(blob):
+    """Initialize without converting: uploads an ExportKeyCache blob and replicates it."""
+    global _devices
+    blob = np.ascontiguousarray(blob, dtype=np.uint8)
+    _lib.check(_lib.lib().b2fhe_init_from_key_cache(_gpu_num, blob.ctypes.data, blob.size))
+    _devices = list(range(_gpu_num))
+
+
+def SerializeCtxts(cts, level):
+    """std::vector<TLWE<P>> archive of a (count, words) array (TFHEpp tutorial cloud.data)."""
+    cts = np.ascontiguousarray(cts, dtype=_np_dtype(level))
+    L = _lib.lib()
+    blob = np.zeros(L.b2fhe_wire_tlwes_size(level, cts.shape[0]), np.uint8)
+    _lib.check(L.b2fhe_wire_tlwes_write(blob.ctypes.data, blob.size, level, cts.ctypes.data, cts.shape[0], None))
+    return blob
+
+
+def DeserializeCtxts(blob, level):
+    blob = np.ascontiguousarray(blob, dtype=np.uint8)
+    n, off = C.c_size_t(), C.c_size_t()
+    _lib.check(_lib.lib().b2fhe_wire_tlwes_parse(blob.ctypes.data, blob.size, level, C.byref(n), C.byref(off)))
+    words = LVL0_WORDS if level == 0 else LVL1_WORDS
+    return blob[off.value:].view(_np_dtype(level)).reshape(n.value, words).copy()
+
+
 def broadcast_key_buffers(bk_t, ksk_t, src=0, group=None):
     """The one collective of the path: the converted bootstrapping key and the key-switching
     key go from rank `src` to every rank (NCCL over NVLink for CUDA tensors; gloo in the CPU
@@ -294,6 +349,12 @@ class cuFHETRLWElvl1:
 
     def ptr(self):
         return self.trlwedevice.data_ptr()
+
+
+def gBootstrap(out, in0, mu, st):
+    """cufhe::Bootstrap (src/bootstrap_gpu.cu:782-789): lvl0 -> lvl0 bootstrapping with a
+    run-time test-vector constant mu, on device-resident batches."""
+    _lib.check(_lib.lib().b2fhe_bootstrap_batch(out.device, st.st(), out.ptr(), in0.ptr(), mu, out.count))
 
 
 def gGateBootstrappingTLWE2TRLWElvl01NTT(out, in0, st, mu=1 << 29):

@@ -179,6 +179,24 @@ int defer_flush_all();      // b2fhe_defer.inl
 int defer_destroy_all();
 void defer_mark_idle_all();
 
+// replicate GPU 0's converted keys device-to-device (NVLink peer copies) instead of
+// re-uploading and re-converting per GPU as the reference does
+int replicate_keys(int ngpu)
+{
+    for (int d = 1; d < ngpu; d++) {
+        DevCtx& c = g_ctx[d];
+        CK(cudaSetDevice(d));
+        CK(cudaMalloc(&c.bk_ntt, B2FHE_BK_NTT_BYTES));
+        CK(cudaMalloc(&c.ksk, B2FHE_KSK_DEV_BYTES));
+        c.owns_keys = true;
+        CK(cudaMemcpyPeer(c.bk_ntt, d, g_ctx[0].bk_ntt, 0, B2FHE_BK_NTT_BYTES));
+        CK(cudaMemcpyPeer(c.ksk, d, g_ctx[0].ksk, 0, B2FHE_KSK_DEV_BYTES));
+        if (int r = build_bk16(c)) return r;
+        c.ready = true;
+    }
+    return 0;
+}
+
 int get_ctx(int device, DevCtx*& c)
 {
     REQUIRE(device >= 0 && device < kMaxDev, B2FHE_E_NO_DEVICE);
@@ -237,20 +255,7 @@ int b2fhe_init(int ngpu, const uint32_t* bk_raw, const uint16_t* ksk_raw)
         REQUIRE(!g_ctx[d].ready, B2FHE_E_BAD_ARGUMENT);
     }
     if (int r = convert_keys(0, bk_raw, ksk_raw)) return r;
-    // replicate the converted keys device-to-device (NVLink peer copies) instead of
-    // re-uploading and re-converting per GPU as the reference does
-    for (int d = 1; d < ngpu; d++) {
-        DevCtx& c = g_ctx[d];
-        CK(cudaSetDevice(d));
-        CK(cudaMalloc(&c.bk_ntt, B2FHE_BK_NTT_BYTES));
-        CK(cudaMalloc(&c.ksk, B2FHE_KSK_DEV_BYTES));
-        c.owns_keys = true;
-        CK(cudaMemcpyPeer(c.bk_ntt, d, g_ctx[0].bk_ntt, 0, B2FHE_BK_NTT_BYTES));
-        CK(cudaMemcpyPeer(c.ksk, d, g_ctx[0].ksk, 0, B2FHE_KSK_DEV_BYTES));
-        if (int r = build_bk16(c)) return r;
-        c.ready = true;
-    }
-    return 0;
+    return replicate_keys(ngpu);
 }
 
 int b2fhe_adopt_keys(int device, const void* bk_ntt_dev, const void* ksk_dev)
@@ -310,3 +315,4 @@ int b2fhe_synchronize(void)
 
 #include "b2fhe_gates.inl"
 #include "b2fhe_defer.inl"
+#include "b2fhe_wire.inl"

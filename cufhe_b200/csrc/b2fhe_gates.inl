@@ -375,6 +375,26 @@ int b2fhe_bootstrap_tlwe2trlwe_batch(int device, b2fhe_stream_t stream, uint32_t
     return launch_br(*c, B, (cudaStream_t)stream);
 }
 
+int b2fhe_bootstrap_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0, const uint16_t* in_lvl0, uint32_t mu,
+                          size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    REQUIRE(count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    if (count == 0) return 0;
+    REQUIRE(out_lvl0 && in_lvl0, B2FHE_E_BAD_ARGUMENT);
+    cudaStream_t st = (cudaStream_t)stream;
+    Scratch S(st);
+    uint32_t* t1;
+    if (int r = S.get((void**)&t1, count * kLvl1Words * 4)) return r;
+    BrParams B{};
+    B.in0 = in_lvl0; B.out = t1; B.count = (int)count; B.ca = 1; B.cb = 0; B.off = 0; B.mu = mu;
+    if (int r = launch_br(*c, B, st)) return r;
+    KsParams K{};
+    K.A = t1; K.out = out_lvl0; K.count = (int)count; K.ca = 1; K.cb = 0; K.off = 0u;
+    return launch_ks(*c, K, st);
+}
+
 int b2fhe_sample_extract_keyswitch_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0, const uint32_t* in_trlwe,
                                          size_t count)
 {

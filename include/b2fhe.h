@@ -29,6 +29,7 @@ extern "C" {
 #define B2FHE_E_NOT_INITIALIZED 10001
 #define B2FHE_E_BAD_ARGUMENT    10002
 #define B2FHE_E_NO_DEVICE       10003
+#define B2FHE_E_BAD_FORMAT      10004   /* wire-format reader: not a blob this engine understands */
 
 /* gate op codes; (casign, cbsign, offset) per src/bootstrap_gpu.cu:424-512,590-679 */
 enum b2fhe_op {
@@ -118,6 +119,11 @@ int b2fhe_blind_rotate_batch(int device, b2fhe_stream_t stream, uint32_t* out_lv
 int b2fhe_keyswitch_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0,
                           const uint32_t* in_lvl1, size_t count);
 
+/* Bootstrap (src/bootstrap_gpu.cu:290-301,782-789): blind rotation with a RUN-TIME test-vector
+ * constant mu, SampleExtract(0), identity key switch: lvl0 TLWE -> lvl0 TLWE.  out may alias in. */
+int b2fhe_bootstrap_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0,
+                          const uint16_t* in_lvl0, uint32_t mu, size_t count);
+
 /* ---- TRLWE-level entry points.  A TRLWE<lvl1param> is [a(X)][b(X)] =
  * 2 x 1024 uint32_t (8192 B); batches are contiguous.  Device pointers.
  * BootstrapTLWE2TRLWE / GateBootstrappingTLWE2TRLWElvl01NTT (src/bootstrap_gpu.cu:316-322,
@@ -154,6 +160,27 @@ int b2fhe_ntt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const 
 int b2fhe_intt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* in, size_t count);
 int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* a,
                             const uint32_t* b, size_t count);
+
+/* ---- wire formats.  Host memory, little-endian hosts. ----------------
+ * TFHEpp's cereal portable_binary archives, default 128-bit parameter set:
+ * EvalKey (TFHEpp/include/cloudkey.hpp:103-107; tutorial/client.cpp writes cloud.key) holding
+ * BootstrappingKey<lvl01param> + KeySwitchingKey<lvl10param> -- exactly what the reference's
+ * Initialize(EvalKey) consumes.  The writer emits that minimal key; the reader also accepts
+ * archives that additionally hold the FFT / NTT forms of the same key and skips them. */
+size_t b2fhe_wire_evalkey_size(void);
+int b2fhe_wire_evalkey_write(void* blob, size_t cap, const uint32_t* bk_raw, const uint16_t* ksk_raw,
+                             size_t* written);
+int b2fhe_wire_evalkey_parse(const void* blob, size_t len, size_t* bk_offset, size_t* ksk_offset);
+int b2fhe_init_from_evalkey(int ngpu, const void* blob, size_t len);   /* parse + b2fhe_init */
+/* std::vector<TLWE<P>> archives (tutorial/client.cpp cloud.data, cloud.cpp result.data) */
+size_t b2fhe_wire_tlwes_size(int level, size_t count);
+int b2fhe_wire_tlwes_write(void* blob, size_t cap, int level, const void* cts, size_t count, size_t* written);
+int b2fhe_wire_tlwes_parse(const void* blob, size_t len, int level, size_t* count, size_t* offset);
+/* cache of this engine's CONVERTED keys (NTT-domain bk + device ksk, checksummed, versioned):
+ * b2fhe_init_from_key_cache skips the conversion of b2fhe_init */
+size_t b2fhe_key_cache_size(void);
+int b2fhe_key_cache_export(int device, void* blob, size_t cap, size_t* written);
+int b2fhe_init_from_key_cache(int ngpu, const void* blob, size_t len);
 
 /* tuning / introspection */
 int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */

@@ -48,6 +48,17 @@ inline void Initialize(const TFHEpp::EvalKey& ek)
     B2CHECK(b2fhe_init(_gpuNumRef(), reinterpret_cast<const uint32_t*>(&ek.getbk<TFHEpp::lvl01param>()),
                        reinterpret_cast<const uint16_t*>(&ek.getiksk<TFHEpp::lvl10param>())));
 }
+// Not in the reference: Initialize from the bytes of a serialised TFHEpp::EvalKey (cereal
+// portable_binary, TFHEpp/include/cloudkey.hpp:103-107 -- e.g. the tutorial's cloud.key) without
+// linking TFHEpp's loader, and from / to a cache of the converted keys (skips the conversion).
+inline void InitializeFromArchive(const void* blob, size_t len) { B2CHECK(b2fhe_init_from_evalkey(_gpuNumRef(), blob, len)); }
+inline void InitializeFromKeyCache(const void* blob, size_t len) { B2CHECK(b2fhe_init_from_key_cache(_gpuNumRef(), blob, len)); }
+inline std::vector<uint8_t> ExportKeyCache(int device = 0)
+{
+    std::vector<uint8_t> blob(b2fhe_key_cache_size());
+    B2CHECK(b2fhe_key_cache_export(device, blob.data(), blob.size(), nullptr));
+    return blob;
+}
 inline void CleanUp() { B2CHECK(b2fhe_cleanup()); }
 // Synchronize(): runs the queued per-gate calls (see SetDeferred) and waits for every device
 inline void Synchronize() { B2CHECK(b2fhe_synchronize()); }
@@ -287,6 +298,14 @@ inline void _trlweH2D(const cuFHETRLWElvl1& c, Stream st)
 inline void _trlweD2H(cuFHETRLWElvl1& c, Stream st)
 {
     cudaMemcpyAsync(c.trlwehost.data(), c.trlwedevices[st.device_id()], sizeof(c.trlwehost), cudaMemcpyDeviceToHost, st.st());
+}
+// Bootstrap (include/bootstrap_gpu.cuh:64-65): lvl0 -> lvl0 with a run-time test-vector constant
+inline void gBootstrap(Ctxt<TFHEpp::lvl0param>& out, Ctxt<TFHEpp::lvl0param>& in, TFHEpp::lvl1param::T mu, Stream st)
+{
+    const int d = st.device_id();
+    cudaSetDevice(d);
+    B2CHECK(b2fhe_defer_fence(d, (b2fhe_stream_t)st.st()));
+    B2CHECK(b2fhe_bootstrap_batch(d, (b2fhe_stream_t)st.st(), out.tlwedevices[d], in.tlwedevices[d], mu, 1));
 }
 inline void gGateBootstrappingTLWE2TRLWElvl01NTT(cuFHETRLWElvl1& out, Ctxt<TFHEpp::lvl0param>& in, Stream st)
 {

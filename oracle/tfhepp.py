@@ -65,3 +65,51 @@ def homnand_lvl0(x0, x1, threads=0):
     lib().ref_homnand_lvl0(out.ctypes.data_as(C.c_void_p), x0.ctypes.data_as(C.c_void_p),
                            x1.ctypes.data_as(C.c_void_p), x0.shape[0], threads or os.cpu_count())
     return out
+
+
+# ---- wire-format pins (TFHEpp's own cereal portable_binary serialisation) -------------------
+def _wire_lib():
+    L = lib()
+    L.ref_serialize_evalkey.restype = C.c_size_t
+    L.ref_serialize_evalkey.argtypes = [C.c_int, C.c_void_p, C.c_size_t]
+    L.ref_deserialize_evalkey.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+    L.ref_serialize_tlwes.restype = C.c_size_t
+    L.ref_serialize_tlwes.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
+    L.ref_deserialize_tlwes.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
+    return L
+
+
+def serialize_evalkey(which=0):
+    """EvalKey archive written by TFHEpp (which=1 also holds the FFT form of the key)."""
+    L = _wire_lib()
+    nbytes = L.ref_serialize_evalkey(which, None, 0)
+    buf = np.zeros(nbytes, np.uint8)
+    L.ref_serialize_evalkey(which, buf.ctypes.data, nbytes)
+    return buf
+
+
+def deserialize_evalkey(blob):
+    """Loads an EvalKey archive with TFHEpp's own reader -> (status, bk, ksk) raw arrays."""
+    L = _wire_lib()
+    blob = np.ascontiguousarray(blob, dtype=np.uint8)
+    bk = np.zeros(n * 4 * 2 * N, np.uint32)
+    ksk = np.zeros(N * 7 * 2 * (n + 1), np.uint16)
+    rc = L.ref_deserialize_evalkey(blob.ctypes.data, blob.size, bk.ctypes.data, ksk.ctypes.data)
+    return rc, bk, ksk
+
+
+def serialize_tlwes(cts, level):
+    L = _wire_lib()
+    cts = np.ascontiguousarray(cts)
+    nbytes = L.ref_serialize_tlwes(level, cts.ctypes.data, cts.shape[0], None, 0)
+    buf = np.zeros(nbytes, np.uint8)
+    L.ref_serialize_tlwes(level, cts.ctypes.data, cts.shape[0], buf.ctypes.data, nbytes)
+    return buf
+
+
+def deserialize_tlwes(blob, level, cap):
+    L = _wire_lib()
+    blob = np.ascontiguousarray(blob, dtype=np.uint8)
+    out = np.zeros((cap, n + 1), np.uint16) if level == 0 else np.zeros((cap, N + 1), np.uint32)
+    cnt = L.ref_deserialize_tlwes(level, blob.ctypes.data, blob.size, out.ctypes.data, cap)
+    return cnt, out

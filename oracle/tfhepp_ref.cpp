@@ -9,9 +9,16 @@
 //     cuFHE's by design, decryption must agree);
 //   * the timed CPU baseline: TFHEpp HomNAND<lvl01param, mu, lvl10param> (lvl0 in/out,
 //     spqlios FFT), the reference's CPU implementation of the same gate
-//     (TFHEpp/include/gate.hpp:60-67, TFHEpp/test/nand.cpp:42-58).
+//     (TFHEpp/include/gate.hpp:60-67, TFHEpp/test/nand.cpp:42-58);
+//   * the wire format: EvalKey and ciphertext vectors written / read by TFHEpp's own cereal
+//     portable_binary serialisation (TFHEpp/include/cloudkey.hpp:103-107,
+//     TFHEpp/tutorial/client.cpp, cloud.cpp), the pin for cufhe_b200's b2fhe_wire_* reader
+//     and writer.
 // None of this file is copied from the reference; it only calls its public API.
 #include <omp.h>
+#include <sstream>
+#include <cereal/archives/portable_binary.hpp>
+#include <cereal/types/vector.hpp>
 #include <chrono>
 #include <cstring>
 #include <memory>
@@ -105,5 +112,82 @@ double ref_bench_nand(int n, int threads)
     ref_homnand_lvl0(r.data(), a.data(), b.data(), n, threads);
     auto t1 = std::chrono::steady_clock::now();
     return std::chrono::duration<double>(t1 - t0).count();
+}
+// ---- wire format pins -------------------------------------------------------------------
+// EvalKey as TFHEpp writes it (tutorial/client.cpp: `ek.serialize(ar)` on a
+// PortableBinaryOutputArchive).  which: 0 = bk<lvl01> + iksk<lvl10> (what cuFHE's tests
+// create), 1 = also bkfft<lvl01> (what the TFHEpp tutorial's cloud.key holds)
+size_t ref_serialize_evalkey(int which, void* buf, size_t cap)
+{
+    if (!g_sk) ref_keygen();
+    EvalKey ek(*g_sk);
+    ek.get<BootstrappingKey<lvl01param>>() = g_ek->get<BootstrappingKey<lvl01param>>();
+    ek.get<KeySwitchingKey<lvl10param>>() = g_ek->get<KeySwitchingKey<lvl10param>>();
+    if (which == 1) ek.get<BootstrappingKeyFFT<lvl01param>>() = g_ek->get<BootstrappingKeyFFT<lvl01param>>();
+    std::ostringstream os(std::ios::binary);
+    {
+        cereal::PortableBinaryOutputArchive ar(os);
+        ek.serialize(ar);
+    }
+    const std::string s = os.str();
+    if (buf && s.size() <= cap) std::memcpy(buf, s.data(), s.size());
+    return s.size();
+}
+// reads an EvalKey blob with TFHEpp's own loader; copies the raw bk / iksk out. 0 = ok
+int ref_deserialize_evalkey(const void* blob, size_t len, void* bk, void* ksk)
+{
+    try {
+        std::istringstream is(std::string((const char*)blob, len), std::ios::binary);
+        cereal::PortableBinaryInputArchive ar(is);
+        EvalKey ek;
+        ek.serialize(ar);
+        if (!ek.get<BootstrappingKey<lvl01param>>() || !ek.get<KeySwitchingKey<lvl10param>>()) return 2;
+        if (!(ek.params == lweParams())) return 3;
+        std::memcpy(bk, ek.get<BootstrappingKey<lvl01param>>().get(), sizeof(BootstrappingKey<lvl01param>));
+        std::memcpy(ksk, ek.get<KeySwitchingKey<lvl10param>>().get(), sizeof(KeySwitchingKey<lvl10param>));
+        return 0;
+    } catch (...) {
+        return 1;
+    }
+}
+// std::vector<TLWE<P>> as tutorial/client.cpp writes cloud.data
+size_t ref_serialize_tlwes(int level, const void* cts, int n, void* buf, size_t cap)
+{
+    std::ostringstream os(std::ios::binary);
+    {
+        cereal::PortableBinaryOutputArchive ar(os);
+        if (level == 0) {
+            std::vector<TLWE<lvl0param>> v(n);
+            std::memcpy((void*)v.data(), cts, (size_t)n * sizeof(TLWE<lvl0param>));
+            ar(v);
+        } else {
+            std::vector<TLWE<lvl1param>> v(n);
+            std::memcpy((void*)v.data(), cts, (size_t)n * sizeof(TLWE<lvl1param>));
+            ar(v);
+        }
+    }
+    const std::string s = os.str();
+    if (buf && s.size() <= cap) std::memcpy(buf, s.data(), s.size());
+    return s.size();
+}
+// returns the element count (or -1); copies at most cap_n ciphertexts out
+int ref_deserialize_tlwes(int level, const void* blob, size_t len, void* out, int cap_n)
+{
+    try {
+        std::istringstream is(std::string((const char*)blob, len), std::ios::binary);
+        cereal::PortableBinaryInputArchive ar(is);
+        if (level == 0) {
+            std::vector<TLWE<lvl0param>> v;
+            ar(v);
+            std::memcpy(out, v.data(), std::min<size_t>(v.size(), cap_n) * sizeof(TLWE<lvl0param>));
+            return (int)v.size();
+        }
+        std::vector<TLWE<lvl1param>> v;
+        ar(v);
+        std::memcpy(out, v.data(), std::min<size_t>(v.size(), cap_n) * sizeof(TLWE<lvl1param>));
+        return (int)v.size();
+    } catch (...) {
+        return -1;
+    }
 }
 }

@@ -163,6 +163,49 @@ def test_abi_exports_every_declared_symbol():
         assert hasattr(L, s), s
 
 
+def test_wire_formats_against_tfhepp_golden(keys):
+    """SURVEY.md 8f rank 4.  tests/golden/wire_golden.json holds framing bytes and whole small
+    archives written by the REAL TFHEpp's cereal serialisation (make_wire_golden.py); the
+    engine's writer must reproduce them and its reader must accept them."""
+    import json
+    from cufhe_b200 import _lib
+    _lib.build()
+    L = _lib.lib()
+    with open(os.path.join(ROOT, "tests", "golden", "wire_golden.json")) as f:
+        G = json.load(f)
+    BK, KSK = keys.bk.nbytes, keys.ksk.nbytes
+    assert L.b2fhe_wire_evalkey_size() == G["evalkey_bytes"]
+    blob = np.zeros(G["evalkey_bytes"], np.uint8)
+    wrote = C.c_size_t()
+    _lib.check(L.b2fhe_wire_evalkey_write(blob.ctypes.data, blob.size, keys.bk.ctypes.data, keys.ksk.ctypes.data, C.byref(wrote)))
+    assert wrote.value == blob.size
+    head = blob[:117].copy(); head[33:41] = 0
+    assert head.tobytes().hex() == G["evalkey_head_hex"]
+    assert blob[117 + BK:117 + BK + 48].tobytes().hex() == G["evalkey_mid_hex"]
+    assert blob[117 + BK + 48 + KSK:].tobytes().hex() == G["evalkey_tail_hex"]
+    ob, ok = C.c_size_t(), C.c_size_t()
+    _lib.check(L.b2fhe_wire_evalkey_parse(blob.ctypes.data, blob.size, C.byref(ob), C.byref(ok)))
+    assert (ob.value, ok.value) == (117, 117 + BK + 48)
+    assert np.array_equal(blob[ob.value:ob.value + BK], keys.bk.view(np.uint8))
+    assert np.array_equal(blob[ok.value:ok.value + KSK], keys.ksk.view(np.uint8))
+    # truncation, trailing bytes, a key type the reader cannot skip
+    assert L.b2fhe_wire_evalkey_parse(blob.ctypes.data, blob.size - 1, C.byref(ob), C.byref(ok)) == _lib.E_BAD_FORMAT
+    more = np.concatenate([blob, np.zeros(1, np.uint8)])
+    assert L.b2fhe_wire_evalkey_parse(more.ctypes.data, more.size, C.byref(ob), C.byref(ok)) == _lib.E_BAD_FORMAT
+    odd = blob.copy(); odd[117 + BK:117 + BK + 4] = np.frombuffer((0x80000002).to_bytes(4, "little"), np.uint8)
+    assert L.b2fhe_wire_evalkey_parse(odd.ctypes.data, odd.size, C.byref(ob), C.byref(ok)) == _lib.E_BAD_FORMAT
+    assert b"cannot skip" in L.b2fhe_last_error_string()
+    for level, words, dt in ((0, 637, np.uint16), (1, 1025, np.uint32)):
+        ref = np.frombuffer(bytes.fromhex(G[f"tlwes_lvl{level}_hex"]), np.uint8)
+        n, off = C.c_size_t(), C.c_size_t()
+        _lib.check(L.b2fhe_wire_tlwes_parse(ref.ctypes.data, ref.size, level, C.byref(n), C.byref(off)))
+        assert (n.value, off.value) == (2, 9)
+        cts = ref[9:].view(dt).reshape(2, words).copy()
+        mine = np.zeros(ref.size, np.uint8)
+        _lib.check(L.b2fhe_wire_tlwes_write(mine.ctypes.data, mine.size, level, cts.ctypes.data, 2, None))
+        assert np.array_equal(mine, ref)
+
+
 def test_product_path_never_touches_oracle():
     """Nothing under cufhe_b200/ or include/ imports, links or calls the oracle."""
     for top in ("cufhe_b200", "include"):

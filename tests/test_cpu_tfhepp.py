@@ -52,3 +52,70 @@ def test_oracle_agrees_with_tfhepp_homnand_at_decrypt_level(tkeys):
     ours = tfhepp.decrypt(orc.gate_batch(tkeys, orc.OP["NAND"], 0, x0, x1), 0)
     theirs = tfhepp.decrypt(tfhepp.homnand_lvl0(x0, x1), 0)
     assert list(ours) == list(theirs) == list(1 - b0 * b1)
+
+
+# ---- wire formats: byte-for-byte against TFHEpp's own cereal output ----
+def _wire():
+    import ctypes as C
+    from cufhe_b200 import _lib
+    _lib.build()
+    return _lib, _lib.lib(), C
+
+
+def test_wire_evalkey_reader_and_writer_match_tfhepp(tkeys):
+    _lib, L, C = _wire()
+    ref = tfhepp.serialize_evalkey(0)                 # bk<lvl01> + iksk<lvl10>, what cuFHE's tests build
+    assert L.b2fhe_wire_evalkey_size() == ref.size
+    # reader: finds TFHEpp's raw arrays inside TFHEpp's archive
+    ob, ok = C.c_size_t(), C.c_size_t()
+    _lib.check(L.b2fhe_wire_evalkey_parse(ref.ctypes.data, ref.size, C.byref(ob), C.byref(ok)))
+    assert np.array_equal(ref[ob.value:ob.value + tkeys.bk.nbytes], tkeys.bk.view(np.uint8))
+    assert np.array_equal(ref[ok.value:ok.value + tkeys.ksk.nbytes], tkeys.ksk.view(np.uint8))
+    # writer: same bytes as TFHEpp's writer (but for the 8 bytes of lvl1.alpha, which TFHEpp never
+    # initialises -- lweParams.hpp:43-50)
+    mine = np.zeros(ref.size, np.uint8)
+    wrote = C.c_size_t()
+    _lib.check(L.b2fhe_wire_evalkey_write(mine.ctypes.data, mine.size, tkeys.bk.ctypes.data, tkeys.ksk.ctypes.data, C.byref(wrote)))
+    assert wrote.value == ref.size
+    a, b = mine.copy(), ref.copy()
+    a[33:41] = 0; b[33:41] = 0
+    assert np.array_equal(a, b)
+    # and TFHEpp's own reader loads what the writer wrote
+    rc, bk2, ksk2 = tfhepp.deserialize_evalkey(mine)
+    assert rc == 0 and np.array_equal(bk2, tkeys.bk) and np.array_equal(ksk2, tkeys.ksk)
+
+
+def test_wire_evalkey_reader_skips_fft_key_and_rejects_garbage(tkeys):
+    _lib, L, C = _wire()
+    big = tfhepp.serialize_evalkey(1)                 # TFHEpp tutorial's cloud.key also carries bkfft
+    ob, ok = C.c_size_t(), C.c_size_t()
+    _lib.check(L.b2fhe_wire_evalkey_parse(big.ctypes.data, big.size, C.byref(ob), C.byref(ok)))
+    assert np.array_equal(big[ob.value:ob.value + tkeys.bk.nbytes], tkeys.bk.view(np.uint8))
+    assert np.array_equal(big[ok.value:ok.value + tkeys.ksk.nbytes], tkeys.ksk.view(np.uint8))
+    small = big[:4096].copy()
+    assert L.b2fhe_wire_evalkey_parse(small.ctypes.data, small.size, C.byref(ob), C.byref(ok)) == _lib.E_BAD_FORMAT
+    bad = big[:200].copy(); bad[1] ^= 0xFF            # lvl0.n
+    assert L.b2fhe_wire_evalkey_parse(bad.ctypes.data, bad.size, C.byref(ob), C.byref(ok)) == _lib.E_BAD_FORMAT
+    assert b"parameter set" in L.b2fhe_last_error_string()
+    be = big[:200].copy(); be[0] = 0
+    assert L.b2fhe_wire_evalkey_parse(be.ctypes.data, be.size, C.byref(ob), C.byref(ok)) == _lib.E_BAD_FORMAT
+
+
+@pytest.mark.parametrize("level", [0, 1])
+def test_wire_ciphertext_vectors_match_tfhepp(tkeys, level):
+    _lib, L, C = _wire()
+    for cnt in (0, 1, 5):
+        cts = tfhepp.encrypt(np.arange(cnt) % 2, level) if cnt else (
+            np.zeros((0, 637), np.uint16) if level == 0 else np.zeros((0, 1025), np.uint32))
+        ref = tfhepp.serialize_tlwes(cts, level)
+        assert L.b2fhe_wire_tlwes_size(level, cnt) == ref.size
+        mine = np.zeros(ref.size, np.uint8)
+        _lib.check(L.b2fhe_wire_tlwes_write(mine.ctypes.data, mine.size, level, cts.ctypes.data, cnt, None))
+        assert np.array_equal(mine, ref)
+        n, off = C.c_size_t(), C.c_size_t()
+        _lib.check(L.b2fhe_wire_tlwes_parse(ref.ctypes.data, ref.size, level, C.byref(n), C.byref(off)))
+        assert n.value == cnt and np.array_equal(ref[off.value:], cts.view(np.uint8).reshape(-1))
+        got_n, got = tfhepp.deserialize_tlwes(mine, level, max(cnt, 1))
+        assert got_n == cnt and np.array_equal(got[:cnt], cts)
+        if cnt:      # a level-0 archive is not a level-1 archive
+            assert L.b2fhe_wire_tlwes_parse(ref.ctypes.data, ref.size, 1 - level, C.byref(n), C.byref(off)) == _lib.E_BAD_FORMAT

@@ -43,3 +43,42 @@ def test_partitioned_batch_on_all_gpus(engine, keys):
         cf.CleanUp()
         cf.SetGPUNum(1)
         cf.Initialize(keys.bk, keys.ksk)
+
+
+def test_initialize_from_archive_and_key_cache(engine, keys):
+    """SURVEY.md 8f rank 4: Initialize from a serialised TFHEpp::EvalKey and from the cache of
+    converted keys; both must give the byte-identical engine (same converted key bytes, same
+    gate outputs as the oracle)."""
+    cf = engine
+    x0 = orc.encrypt(keys, [0, 1, 1, 0, 1], 0, base_index=9100)
+    x1 = orc.encrypt(keys, [1, 1, 0, 0, 1], 0, base_index=9200)
+    want = orc.gate_batch(keys, orc.OP["NAND"], 0, x0, x1)
+
+    def nand():
+        st = cf.Stream(0).Create()
+        a, b, o = cf.Ctxt(5, 0).set(x0), cf.Ctxt(5, 0).set(x1), cf.Ctxt(5, 0)
+        cf.Nand(o, a, b, st)
+        cf.Synchronize()
+        return o.tlwehost.copy()
+
+    cache = cf.ExportKeyCache(0)
+    archive = cf.SerializeEvalKey(keys.bk, keys.ksk)
+    cf.CleanUp()
+    try:
+        cf.SetGPUNum(1)
+        cf.InitializeFromArchive(archive)
+        assert np.array_equal(cf.ExportKeyCache(0), cache)
+        assert np.array_equal(nand(), want)
+        cf.CleanUp()
+        cf.InitializeFromKeyCache(cache)
+        assert np.array_equal(nand(), want)
+        cf.CleanUp()
+        bad = cache.copy(); bad[1000] ^= 1
+        with pytest.raises(cf._lib.B2FheError, match="checksum"):
+            cf.InitializeFromKeyCache(bad)
+        rt = cf.DeserializeCtxts(cf.SerializeCtxts(want, 0), 0)
+        assert np.array_equal(rt, want)
+    finally:
+        cf.CleanUp()
+        cf.SetGPUNum(1)
+        cf.Initialize(keys.bk, keys.ksk)

@@ -157,6 +157,16 @@ def test_trlwe_level_entry_points(engine, keys):
         assert np.array_equal(t2.trlwehost[i], w2), i
         assert np.array_equal(out.tlwehost[i], orc.sample_extract_keyswitch(keys, w2)), i
     assert list(orc.decrypt(keys, out.tlwehost, 0)) == list(bits)
+    # Bootstrap with a run-time test-vector constant (src/bootstrap_gpu.cu:782-789), in place
+    for mu in (1 << 29, 1 << 28, 0x12345678):
+        cf.CtxtCopyH2D(cin, st)
+        cf.gBootstrap(cin, cin, mu, st)
+        cf.CtxtCopyD2H(cin, st)
+        cf.Synchronize()
+        for i in range(cnt):
+            want = orc.keyswitch(keys, orc.blind_rotate_extract(keys, c0[i], mu=mu))
+            assert np.array_equal(cin.tlwehost[i], want), (hex(mu), i)
+        cin.set(c0)
 
 
 @pytest.mark.parametrize("cnt,shared", [(3, False), (3, True), (600, False)])
