@@ -31,6 +31,10 @@ __device__ __forceinline__ const Tw* t16_iv2(const uint32_t* s, int q, int lo) {
 __device__ __forceinline__ const Tw* t16_iv3(const uint32_t* s, int q, int T) { return reinterpret_cast<const Tw*>(s) + 4 * 15 * 16 + 2 * 12 * 64 + q * 12 * 64 + T; }
 __device__ __forceinline__ const Tw* t16_scale(const uint32_t* s, int q, int T) { return reinterpret_cast<const Tw*>(s) + 4 * 15 * 16 + 4 * 12 * 64 + q * 16 * 64 + T; }
 
+__device__ __forceinline__ const uint32_t* t16_lut1(const uint32_t* s, int q) { return s + kLut1Word + q * 256; }
+__device__ __forceinline__ const U2* t16_lut24(const uint32_t* s, int q) { return reinterpret_cast<const U2*>(s + kLut1Word + 512) + q * 256; }
+__device__ __forceinline__ const U2* t16_lut35(const uint32_t* s, int q) { return reinterpret_cast<const U2*>(s + kLut1Word + 512 + 1024) + q * 256; }
+
 __device__ __forceinline__ void stage_tables16(uint32_t* s_tab, const Lane16Tables* g_tab)
 {
     const uint4* src = reinterpret_cast<const uint4*>(g_tab);
@@ -59,10 +63,10 @@ __device__ __forceinline__ X16 make_x16(int T)
 
 // forward transform: layout A in, layout C out.  bufA / bufB: the team's two exchange
 // buffers; `bar` = the gate's named barrier (all 128 threads of the gate call this).
-__device__ __forceinline__ void fwd16(uint32_t (&x)[16], uint32_t* bufA, uint32_t* bufB, const uint32_t* s_tab,
-                                      const X16& a, int T, int q, uint32_t p, int bar, int barn = 128)
+// passes F2 and F3 (after the first pass left layout A in x)
+__device__ __forceinline__ void fwd16_tail(uint32_t (&x)[16], uint32_t* bufA, uint32_t* bufB, const uint32_t* s_tab,
+                                           const X16& a, int T, int q, uint32_t p, int bar, int barn)
 {
-    pass16_fwd<4, 8>(x, c_fw1[q], 1, p);
 #pragma unroll
     for (int k = 0; k < 16; k++) bufA[a.wA + 68 * k] = x[k];
     named_bar_sync(bar, barn);
@@ -75,6 +79,19 @@ __device__ __forceinline__ void fwd16(uint32_t (&x)[16], uint32_t* bufA, uint32_
 #pragma unroll
     for (int k = 0; k < 16; k++) x[k] = bufB[a.rC + k];
     pass16_fwd3(x, t16_fw3(s_tab, q, T), 64, p);
+}
+__device__ __forceinline__ void fwd16(uint32_t (&x)[16], uint32_t* bufA, uint32_t* bufB, const uint32_t* s_tab,
+                                      const X16& a, int T, int q, uint32_t p, int bar, int barn = 128)
+{
+    pass16_fwd<4, 8>(x, c_fw1[q], 1, p);
+    fwd16_tail(x, bufA, bufB, s_tab, a, T, q, p, bar, barn);
+}
+// the same transform of gadget digits: x[k] in [0, 256) stands for x[k] - 128 (pass16_fwd_digits)
+__device__ __forceinline__ void fwd16_digits(uint32_t (&x)[16], uint32_t* bufA, uint32_t* bufB, const uint32_t* s_tab,
+                                             const X16& a, int T, int q, uint32_t p, int bar, int barn = 128)
+{
+    pass16_fwd_digits(x, t16_lut1(s_tab, q), t16_lut24(s_tab, q), t16_lut35(s_tab, q), c_fw1[q], p);
+    fwd16_tail(x, bufA, bufB, s_tab, a, T, q, p, bar, barn);
 }
 
 // inverse transform incl. n^-1 psi^-e scaling: layout C in, layout A out, values in [0, 2p)
@@ -113,7 +130,6 @@ __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, 
 {
     const uint32_t p = q ? Prime<1>::p : Prime<0>::p;
     const uint32_t pinv = q ? Prime<1>::pinv : Prime<0>::pinv;
-    const uint32_t dig_off = p - 128u;
     const X16 xa = make_x16(T);
     // key row layout [row][prime][out][256 uint4] in bk16_slot order; out = q first, then 1-q
     const uint4* bk4 = reinterpret_cast<const uint4*>(bk) + T + (size_t)q * 2 * (kN / 4);
@@ -142,15 +158,15 @@ __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, 
                     const bool neg = (k < kth) != flip;
                     rot = neg ? 0u - rot : rot;
                     const uint32_t t = rot - aj[T + 64 * k] + kDecompAdd;
-                    x[k] = (t >> 24) + dig_off;                       // digit 0 + p in [0, 2p)
+                    x[k] = t >> 24;                                   // digit 0 (raw, stands for x - 128)
                     const uint32_t d1 = (t >> 16) & 0xFFu;
                     if ((k & 3) == 0) dlo[k >> 2] = d1; else dlo[k >> 2] |= d1 << (8 * (k & 3));
                 }
             } else {
 #pragma unroll
-                for (int k = 0; k < 16; k++) x[k] = ((dlo[k >> 2] >> (8 * (k & 3))) & 0xFFu) + dig_off;
+                for (int k = 0; k < 16; k++) x[k] = (dlo[k >> 2] >> (8 * (k & 3))) & 0xFFu;
             }
-            fwd16(x, bufA, bufB, s_tab, xa, T, q, p, bar);
+            fwd16_digits(x, bufA, bufB, s_tab, xa, T, q, p, bar);
             const uint4* row = bk4 + (size_t)(i * kRows + r) * (4 * (kN / 4));
 #pragma unroll
             for (int v = 0; v < 4; v++) {

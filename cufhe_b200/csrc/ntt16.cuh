@@ -34,14 +34,22 @@ namespace b2 {
 
 constexpr int kXbufWords = 1088;                 // padded exchange buffer (max slot 1087)
 
+struct alignas(8) U2 { uint32_t x, y; };
 struct Lane16Tables {
     Tw fw2[2][15][16];      // [q][(1<<s')-1+g][block]
     Tw fw3[2][12][64];      // [q][slot][T]   slots 0..3: stride 2, 4..11: stride 1
     Tw iv2[2][15][16];      // [q][(1<<u')-1+g][T&15]
     Tw iv3[2][12][64];      // [q][slot][T]   slots 0..3: t=256, 4..11: t=512
     Tw scale[2][16][64];    // [q][k][T]      n^-1 psi^-(T + 64 k)
+    // gadget-digit look-up tables for forward stages 0 and 1 (pass16_fwd_digits): entry d stands
+    // for the signed digit d - 128; W1, W2a, W2b = twiddles of stage 0 and of the two stage-1 groups
+    uint32_t lut1[2][256];  // W1 (d-128) mod p
+    U2 lut24[2][256];       // { W2a (d-128), W2b (d-128) } mod p
+    U2 lut35[2][256];       // { W2a W1 (d-128), W2b W1 (d-128) } mod p
 };
-constexpr int kLane16TableWords = sizeof(Lane16Tables) / 4;      // 12160 words = 48640 B
+constexpr int kLane16TableWords = sizeof(Lane16Tables) / 4;      // 14720 words = 58880 B
+constexpr int kLut1Word = (sizeof(Tw) * (2 * 15 * 16 + 2 * 12 * 64 + 2 * 15 * 16 + 2 * 12 * 64 + 2 * 16 * 64)) / 4;
+static_assert(kLut1Word == 12160 && kLane16TableWords == 12160 + 2 * 256 * 5, "table layout");
 
 // F1 / I1 reuse the first 15 entries of NttTables::fw1 / iv1 (same formulas).
 inline void make_tables16(Lane16Tables& L)
@@ -75,6 +83,13 @@ inline void make_tables16(Lane16Tables& L)
         for (int k = 0; k < 16; k++)
             for (int T = 0; T < 64; T++)
                 L.scale[q][k][T] = M(h_mulmod(ninv, h_powmod(ipsi, T + 64 * k, p), p));
+        const uint32_t w1 = psirev(1), w2a = psirev(2), w2b = psirev(3);
+        for (int d = 0; d < 256; d++) {
+            const uint32_t v = d >= 128 ? (uint32_t)(d - 128) : p - (uint32_t)(128 - d);     // d - 128 mod p
+            L.lut1[q][d] = h_mulmod(w1, v, p);
+            L.lut24[q][d] = U2{h_mulmod(w2a, v, p), h_mulmod(w2b, v, p)};
+            L.lut35[q][d] = U2{h_mulmod(h_mulmod(w2a, w1, p), v, p), h_mulmod(h_mulmod(w2b, w1, p), v, p)};
+        }
     }
 }
 
@@ -103,6 +118,36 @@ B2_HD void pass16_fwd(uint32_t (&x)[16], const Tw* tw, const int stride, const u
 #pragma unroll
         for (int k = 0; k < 16; k++)
             if ((k & tp) == 0) butterfly_p(x[k], x[k + tp], tw[((1 << s) - 1 + k / (2 * tp)) * stride], p, p2);
+    }
+}
+// Pass F1 on raw gadget digits x[k] in [0, 256) (meaning x[k] - 128): stages 0 and 1 are linear
+// in the four digits of a radix-4 group, so each term is ONE table entry -- five look-ups and
+// eight additions replace four Shoup butterflies; stages 2 and 3 follow as usual.  Outputs are
+// congruent to pass16_fwd<4, 8> on (digit - 128 + p) and obey its bounds (< 4p + 128 after the
+// table stages, where the butterflies allow 6p).
+B2_HD void pass16_fwd_digits(uint32_t (&x)[16], const uint32_t* l1, const U2* l24, const U2* l35, const Tw* tw,
+                             const uint32_t p)
+{
+    const uint32_t p2 = 2u * p;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t d0 = x[k], t1 = l1[x[k + 8]];
+        const U2 u = l24[x[k + 4]], v = l35[x[k + 12]];
+        const uint32_t A = d0 + (p - 128u) + t1;          // x0 + W1 x2
+        const uint32_t C = d0 + (p2 - 128u) - t1;         // x0 - W1 x2
+        const uint32_t B = u.x + v.x;                     // W2a (x1 + W1 x3)
+        const uint32_t D = u.y - v.y + p;                 // W2b (x1 - W1 x3)
+        x[k] = A + B;
+        x[k + 4] = A - B + p2;
+        x[k + 8] = C + D;
+        x[k + 12] = C - D + p2;
+    }
+#pragma unroll
+    for (int s = 2; s < 4; s++) {
+        const int tp = 8 >> s;
+#pragma unroll
+        for (int k = 0; k < 16; k++)
+            if ((k & tp) == 0) butterfly_p(x[k], x[k + tp], tw[(1 << s) - 1 + k / (2 * tp)], p, p2);
     }
 }
 // F3: sub-strides 2 then 1; slots 0..3 then 4..11

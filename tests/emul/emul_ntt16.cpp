@@ -179,6 +179,29 @@ static int check_cmux(std::mt19937_64& rng)
     return memcmp(acc, ref, sizeof ref) != 0;
 }
 
+// pass F1 from the gadget-digit look-up tables == pass F1 by butterflies, as residues, and within
+// the lazy bound the later passes assume
+static int check_digit_pass(std::mt19937_64& rng)
+{
+    int bad = 0;
+    for (int q = 0; q < 2; q++) {
+        const uint32_t p = kP[q];
+        for (int it = 0; it < 2000; it++) {
+            uint32_t d[16], a[16], b[16];
+            for (int k = 0; k < 16; k++) {
+                d[k] = it == 0 ? 0u : it == 1 ? 255u : (uint32_t)(rng() & 0xFF);
+                a[k] = d[k] + p - 128u;
+                b[k] = d[k];
+            }
+            pass16_fwd<4, 8>(a, T.fw1[q], 1, p);
+            pass16_fwd_digits(b, L.lut1[q], L.lut24[q], L.lut35[q], T.fw1[q], p);
+            for (int k = 0; k < 16; k++)
+                if (a[k] % p != b[k] % p || b[k] >= 8u * p) bad++;
+        }
+    }
+    return bad;
+}
+
 int main(int argc, char** argv)
 {
     make_tables(T);
@@ -187,11 +210,13 @@ int main(int argc, char** argv)
     int trials = argc > 1 ? atoi(argv[1]) : 20;
     int bad0 = check_same_as_warp(rng);
     printf("position mismatches vs 32-coefficient transform: %d\n", bad0);
+    const int bad3 = check_digit_pass(rng);
+    printf("digit look-up pass mismatches: %d\n", bad3);
     int bad = 0, bad2 = 0;
     for (int i = 0; i < trials; i++) bad += check_polymul(rng, i & 1);
     printf("polymul mismatches: %d / %d\n", bad, trials);
     for (int i = 0; i < trials; i++) bad2 += check_cmux(rng);
     printf("cmux mismatches: %d / %d\n", bad2, trials);
     printf("bank conflicts: %d\n", g_conflicts);
-    return (bad0 || bad || bad2 || g_conflicts) ? 1 : 0;
+    return (bad0 || bad || bad2 || bad3 || g_conflicts) ? 1 : 0;
 }

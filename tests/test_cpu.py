@@ -135,6 +135,7 @@ def test_team_emulation_of_16_coefficient_ntt_and_cmux(tmp_path):
                            "-fopenmp"])
     out = subprocess.check_output([exe, "6"]).decode()
     assert "position mismatches vs 32-coefficient transform: 0" in out
+    assert "digit look-up pass mismatches: 0" in out
     assert "polymul mismatches: 0 / 6" in out and "cmux mismatches: 0 / 6" in out
     assert "bank conflicts: 0" in out
 
