@@ -9,6 +9,7 @@
 // data dependencies (a gate that consumes another queued gate's output runs one level
 // later), which is legal because the reference only guarantees results after
 // Synchronize() / a successful StreamQuery (include/cufhe_gpu.cuh:68-74).
+#include <algorithm>
 #include <unordered_map>
 #include <unordered_set>
 
@@ -80,7 +81,7 @@ int gate_ptrs(const DevCtx& c, cudaStream_t st, const uint8_t* ops, int level, v
 
 // ---- deferred queue ----------------------------------------------------------------------
 struct Pending { uint8_t op, level; int lvl; void* out; const void* in[3]; };
-struct PendingCopy { void* host; const void* dev; size_t bytes; };
+struct PendingCopy { void* host; const void* dev; size_t bytes; int lvl = 0; };   // d2h: taken before gate level `lvl` runs
 struct Pinned { void* p = nullptr; size_t cap = 0; std::atomic<int> busy{0}; };
 // runs on the flush stream (cudaLaunchHostFunc) after the staged copy-back has landed
 struct HostJob {
@@ -102,6 +103,7 @@ struct DeferCtx {
     std::vector<PendingCopy> d2h;
     std::vector<PendingCopy> h2d;                            // .host = source, .dev = destination
     std::unordered_map<const void*, size_t> h2d_index;       // destination -> entry of h2d
+    std::unordered_map<const void*, size_t> d2h_index;       // host destination -> entry of d2h
     std::vector<Pinned*> pinned;                             // staging areas, reused
     std::unordered_set<const void*> produced;                // outputs of flushed gates, until the next completed wait
     std::unordered_map<const void*, int> wlevel, rlevel;     // buffer -> level of its pending writer / last reader
@@ -130,7 +132,7 @@ int acquire_pinned(DeferCtx& D, size_t bytes, Pinned*& out)
 
 void defer_reset(DeferCtx& D)
 {
-    D.q.clear(); D.d2h.clear(); D.h2d.clear(); D.h2d_index.clear(); D.wlevel.clear(); D.rlevel.clear();
+    D.q.clear(); D.d2h.clear(); D.h2d.clear(); D.h2d_index.clear(); D.d2h_index.clear(); D.wlevel.clear(); D.rlevel.clear();
     D.maxlvl = 0;
 }
 
@@ -166,13 +168,49 @@ int defer_flush_body(int device, HostJob* job, bool& handed_over)
         k_stage_copy<false><<<n < 4096 ? n : 4096, 128, 0, D.fs>>>(d_stage, d_items, n);
         LAUNCHED();
     }
-    // ---- the gates, level by level
+    // ---- results are snapshots: a copy-back queued after its producer (level L) is gathered into the
+    // staging area before level L + 1 runs, so a later in-place update of the same buffer does not
+    // leak into it (stream order of the reference); one transfer for all of them at the end
+    uint16_t* d_out_stage = nullptr;
+    CopyItem* d_out_items = nullptr;
+    std::vector<int> first_of_lvl;          // items sorted by lvl: [first_of_lvl[l], first_of_lvl[l+1])
+    size_t out_total = 0;
     int maxl = 0;
     for (const Pending& p : D.q) maxl = p.lvl > maxl ? p.lvl : maxl;
+    if (!D.d2h.empty()) {
+        std::vector<size_t> order(D.d2h.size());
+        for (size_t i = 0; i < order.size(); i++) order[i] = i;
+        std::stable_sort(order.begin(), order.end(), [&](size_t x, size_t y) { return D.d2h[x].lvl < D.d2h[y].lvl; });
+        items.clear();
+        items.reserve(order.size());
+        first_of_lvl.assign(maxl + 3, 0);
+        for (size_t i : order) {
+            const PendingCopy& pc = D.d2h[i];
+            const int l = pc.lvl > maxl + 1 ? maxl + 1 : pc.lvl;
+            first_of_lvl[l + 1]++;
+            items.push_back(CopyItem{const_cast<void*>(pc.dev), (uint32_t)(out_total / 2), (uint32_t)(pc.bytes / 2)});
+            job->outs.push_back(HostJob::Out{pc.host, out_total, pc.bytes});
+            out_total += (pc.bytes + 15) & ~size_t(15);
+        }
+        for (int l = 0; l <= maxl + 1; l++) first_of_lvl[l + 1] += first_of_lvl[l];
+        if (int r = acquire_pinned(D, out_total, job->stage_out)) return r;
+        if (int r = S.get((void**)&d_out_stage, out_total)) return r;
+        if (int r = upload(S, &d_out_items, items)) return r;
+    }
+    auto gather_results = [&](int l) -> int {
+        if (first_of_lvl.empty()) return 0;
+        const int lo = first_of_lvl[l], n = first_of_lvl[l + 1] - lo;
+        if (n <= 0) return 0;
+        k_stage_copy<true><<<n < 4096 ? n : 4096, 128, 0, D.fs>>>(d_out_stage, d_out_items + lo, n);
+        LAUNCHED();
+        return 0;
+    };
+    // ---- the gates, level by level
     std::vector<uint8_t> ops;
     std::vector<void*> out;
     std::vector<const void*> in[3];
-    for (int l = 0; l <= maxl; l++)
+    for (int l = 0; l <= maxl; l++) {
+        if (int r = gather_results(l)) return r;
         for (int level = 0; level < 2; level++) {
             ops.clear(); out.clear(); in[0].clear(); in[1].clear(); in[2].clear();
             for (const Pending& p : D.q)
@@ -186,32 +224,16 @@ int defer_flush_body(int device, HostJob* job, bool& handed_over)
                                      : gate_ptrs<uint32_t>(*c, D.fs, ops.data(), 1, out.data(), in[0].data(), in[1].data(), in[2].data(), n);
             if (r) return r;
         }
-    // ---- results: device buffers -> staging -> one transfer -> a host function hands them out
-    if (!D.d2h.empty()) {
-        size_t total = 0;
-        items.clear();
-        items.reserve(D.d2h.size());
-        for (const PendingCopy& pc : D.d2h) {
-            items.push_back(CopyItem{const_cast<void*>(pc.dev), (uint32_t)(total / 2), (uint32_t)(pc.bytes / 2)});
-            job->outs.push_back(HostJob::Out{pc.host, total, pc.bytes});
-            total += (pc.bytes + 15) & ~size_t(15);
-        }
-        if (int r = acquire_pinned(D, total, job->stage_out)) return r;
-        uint16_t* d_stage;
-        CopyItem* d_items;
-        if (int r = S.get((void**)&d_stage, total)) return r;
-        if (int r = upload(S, &d_items, items)) return r;
-        const int n = (int)items.size();
-        k_stage_copy<true><<<n < 4096 ? n : 4096, 128, 0, D.fs>>>(d_stage, d_items, n);
-        LAUNCHED();
-        CK(cudaMemcpyAsync(job->stage_out->p, d_stage, total, cudaMemcpyDeviceToHost, D.fs));
     }
+    if (int r = gather_results(maxl + 1)) return r;
+    if (out_total) CK(cudaMemcpyAsync(job->stage_out->p, d_out_stage, out_total, cudaMemcpyDeviceToHost, D.fs));
     CK(cudaLaunchHostFunc(D.fs, run_host_job, job));
     handed_over = true;
     CK(cudaEventRecord(D.done, D.fs));
     // later work on the user streams is ordered after this flush ("same stream = issue order")
     for (auto& kv : D.seen) {
-        CK(cudaStreamWaitEvent(kv.first, D.done, 0));
+        // a stream the caller has already destroyed (legal with work pending) has nothing left to order
+        if (cudaStreamWaitEvent(kv.first, D.done, 0) != cudaSuccess) (void)cudaGetLastError();
         D.pool.push_back(kv.second);
     }
     // the user may destroy its streams after Synchronize(): keep no handle past the flush
@@ -333,7 +355,14 @@ int b2fhe_defer_d2h(int device, void* host_dst, const void* dev_src, size_t byte
 {
     std::lock_guard<std::mutex> lk(g_defer_mu);
     REQUIRE(device >= 0 && device < kMaxDev && host_dst && dev_src && bytes % 2 == 0 && bytes < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    g_defer[device].d2h.push_back(PendingCopy{host_dst, dev_src, bytes});
+    DeferCtx& D = g_defer[device];
+    // a repeated host destination needs only the last copy
+    const auto w = D.wlevel.find(dev_src);
+    const int lvl = w == D.wlevel.end() ? 0 : w->second + 1;        // right after its queued producer
+    auto it = D.d2h_index.find(host_dst);
+    if (it != D.d2h_index.end()) { D.d2h[it->second] = PendingCopy{host_dst, dev_src, bytes, lvl}; return 0; }
+    D.d2h_index.emplace(host_dst, D.d2h.size());
+    D.d2h.push_back(PendingCopy{host_dst, dev_src, bytes, lvl});
     return 0;
 }
 

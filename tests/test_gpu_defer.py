@@ -210,3 +210,27 @@ def test_deferred_copy_variant_chain(engine, keys, level):
     cf._lib.check(L.b2fhe_defer_d2h(0, out_h.data_ptr(), dev["e"][0].data_ptr(), nbytes))
     cf.Synchronize()
     assert np.array_equal(_np(out_h, level), orc.gate_batch(keys, NAND, level, x[0][1:2], x[2][0:1])[0])
+
+
+def test_deferred_copy_back_is_a_snapshot(engine, keys):
+    """Nand(c, a, b, st) followed by gNot(c, c, st): the host copy queued with the NAND holds the
+    NAND (the reference copies it back before the NOT runs on that stream), a second copy-back
+    queued after the NOT holds the NOT."""
+    cf = engine
+    L = cf._lib.lib()
+    x0 = orc.encrypt(keys, [1, 1], 0, base_index=93000)
+    x1 = orc.encrypt(keys, [1, 0], 0, base_index=94000)
+    d0, d1 = _dev(x0), _dev(x1)
+    c = torch.zeros_like(d0)
+    h1 = [torch.zeros(637, dtype=torch.int16).pin_memory() for _ in range(2)]
+    h2 = [torch.zeros(637, dtype=torch.int16).pin_memory() for _ in range(2)]
+    torch.cuda.synchronize()
+    for i in range(2):
+        cf._lib.check(L.b2fhe_defer_gate(0, None, orc.OP["NAND"], 0, c[i].data_ptr(), d0[i].data_ptr(), d1[i].data_ptr(), None))
+        cf._lib.check(L.b2fhe_defer_d2h(0, h1[i].data_ptr(), c[i].data_ptr(), 1274))
+        cf._lib.check(L.b2fhe_defer_gate(0, None, orc.OP["NOT"], 0, c[i].data_ptr(), c[i].data_ptr(), None, None))
+        cf._lib.check(L.b2fhe_defer_d2h(0, h2[i].data_ptr(), c[i].data_ptr(), 1274))
+    cf.Synchronize()
+    nand = orc.gate_batch(keys, orc.OP["NAND"], 0, x0, x1)
+    assert np.array_equal(np.stack([_np(t, 0) for t in h1]), nand)
+    assert np.array_equal(np.stack([_np(t, 0) for t in h2]), orc.gate_batch(keys, orc.OP["NOT"], 0, nand))
