@@ -15,6 +15,7 @@
 #include "k_blindrotate_lat.cuh"
 #include "k_blindrotate_cl.cuh"
 #include "k_cmux.cuh"
+#include "k_polymul16.cuh"
 #include "k_keyswitch.cuh"
 #include "k_ntt.cuh"
 
@@ -116,6 +117,7 @@ int setup_device(int device)
     CK(cudaFuncSetAttribute(k_blind_rotate_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, kClSmemBytes));
     CK(cudaFuncSetAttribute(k_cmux16<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(1)));
     CK(cudaFuncSetAttribute(k_cmux16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(4)));
+    CK(cudaFuncSetAttribute(k_polymul16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, polymul16_smem_bytes(4)));
     if (int r = set_br16_attr<1>()) return r;
     if (int r = set_br16_attr<2>()) return r;
     if (int r = set_br16_attr<3>()) return r;

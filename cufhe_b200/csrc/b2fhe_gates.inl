@@ -501,7 +501,15 @@ int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, co
     if (int r = get_ctx(device, c)) return r;
     if (count == 0) return 0;
     REQUIRE(out && a && b && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    k_polymul<<<ntt_grid(*c, count), kNttThreads, kNttSmemBytes, (cudaStream_t)stream>>>(a, b, out, (int)count, c->tab);
+    if (g_br_variant == 32) {             // first design (A/B): one warp x 32 coefficients per (product, prime)
+        k_polymul<<<ntt_grid(*c, count), kNttThreads, kNttSmemBytes, (cudaStream_t)stream>>>(a, b, out, (int)count, c->tab);
+        LAUNCHED();
+        return 0;
+    }
+    constexpr int G = 4;
+    const int ctas = (int)((count + G - 1) / G);
+    k_polymul16<G><<<ctas < c->sm_count ? ctas : c->sm_count, 128 * G, polymul16_smem_bytes(G), (cudaStream_t)stream>>>(
+        a, b, out, (int)count, c->tab16);
     LAUNCHED();
     return 0;
 }
