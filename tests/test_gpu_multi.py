@@ -82,3 +82,44 @@ def test_initialize_from_archive_and_key_cache(engine, keys):
         cf.CleanUp()
         cf.SetGPUNum(1)
         cf.Initialize(keys.bk, keys.ksk)
+
+
+def test_deferred_queue_on_second_gpu(engine, keys):
+    """The per-gate queue is per device (test/test_gate_gpu_multi.cc issues gates on streams of
+    every GPU from one thread): queue a dependent pair on GPU 1 while GPU 0 also has work."""
+    import ctypes as C
+    n = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    cf = engine
+    L = cf._lib.lib()
+    cf.CleanUp()
+    cf.SetGPUNum(2)
+    cf.Initialize(keys.bk, keys.ksk)
+    try:
+        x0 = orc.encrypt(keys, [1, 0, 1], 0, base_index=9500)
+        x1 = orc.encrypt(keys, [1, 1, 0], 0, base_index=9600)
+        nand = orc.gate_batch(keys, orc.OP["NAND"], 0, x0, x1)
+        want = orc.gate_batch(keys, orc.OP["XOR"], 0, nand, x1)
+        hosts, outs = {}, {}
+        for d in (0, 1):
+            with torch.cuda.device(d):
+                a = torch.from_numpy(x0.view(np.int16)).cuda(d)
+                b = torch.from_numpy(x1.view(np.int16)).cuda(d)
+                m = torch.zeros_like(a)
+                o = torch.zeros_like(a)
+                h = torch.zeros(3, 637, dtype=torch.int16).pin_memory()
+                torch.cuda.synchronize(d)
+                for i in range(3):
+                    cf._lib.check(L.b2fhe_defer_gate(d, None, orc.OP["NAND"], 0, m[i].data_ptr(), a[i].data_ptr(), b[i].data_ptr(), None))
+                    cf._lib.check(L.b2fhe_defer_gate(d, None, orc.OP["XOR"], 0, o[i].data_ptr(), m[i].data_ptr(), b[i].data_ptr(), None))
+                    cf._lib.check(L.b2fhe_defer_d2h(d, h[i].data_ptr(), o[i].data_ptr(), 1274))
+                hosts[d], outs[d] = h, (a, b, m, o)
+        assert L.b2fhe_defer_pending(0) == 9 and L.b2fhe_defer_pending(1) == 9
+        cf.Synchronize()
+        for d in (0, 1):
+            assert np.array_equal(hosts[d].numpy().view(np.uint16), want), d
+    finally:
+        cf.CleanUp()
+        cf.SetGPUNum(1)
+        cf.Initialize(keys.bk, keys.ksk)
