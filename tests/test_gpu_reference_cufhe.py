@@ -72,8 +72,10 @@ def test_reference_gpu_throughput_recorded(ref):
     sms = torch.cuda.get_device_properties(0).multi_processor_count
     count = 8 * sms
     secs = ref.cufheref_bench_nand(count, 4 * sms)
+    lat = min(ref.cufheref_bench_nand(1, 1) for _ in range(5))      # one gate, one stream, copies included
     rec = {"reference_cufhe_gpu_nand_lvl0": {"gates": count, "streams": 4 * sms, "seconds": secs,
-                                             "gates_per_s": count / secs, "ms_per_gate_throughput": secs / count * 1e3}}
+                                             "gates_per_s": count / secs, "ms_per_gate_throughput": secs / count * 1e3,
+                                             "single_gate_latency_ms": lat * 1e3}}
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ROOT, "gpurun_out", "reference_gpu_bench.json"), "w") as f:
         json.dump(rec, f)
