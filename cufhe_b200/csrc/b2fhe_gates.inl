@@ -39,8 +39,15 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
         const int64_t prev = last_ns[dev].exchange(now, std::memory_order_relaxed);
         burst = g_br_burst_detect && prev != 0 && now - prev < kBurstGapNs;
     }
-    // a handful of gates: one gate per cluster of 8 CTAs on 8 SMs
-    if (variant == 2 || (g_br_variant == 0 && g == 0 && !burst && P.count <= g_br_cluster_max)) {
+    // up to 33 gates: one gate per cluster of 4 CTAs x 128 threads (33 clusters run concurrently)
+    if (variant == 4 || (g_br_variant == 0 && g == 0 && !burst && P.count <= g_br_cluster_max)) {
+        P.bk = c.bk_ntt16;
+        k_blind_rotate_cl4<<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, c.tab16);
+        LAUNCHED();
+        return 0;
+    }
+    // first cluster design (A/B): one gate per cluster of 8 CTAs x 64 threads
+    if (variant == 2) {
         P.bk = c.bk_ntt16;
         k_blind_rotate_cl<<<P.count * kClCtas, 64, kClSmemBytes, st>>>(P, c.tab16);
         LAUNCHED();
