@@ -249,7 +249,7 @@ def run_product(args):
                     "d2h_bytes_per_step": cnt * 1274 * world},
             "single_gate_latency_ms": {"device_resident": lat_dev, "host_buffers": lat_host,
                                        "note": "one NAND: k_blind_rotate_cl4 (one gate per 4-CTA cluster, DSMEM) + k_keyswitch_lat; L2 is flushed "
-                                               "before every call here (keys come from HBM) -- 1.9 ms with the keys L2-resident "
+                                               "before every call here (keys come from HBM) -- 1.74 ms with the keys L2-resident "
                                                "(tools/probe_small.py)"},
             "gpu_launches": int(launches),
             "clocks": summarize_clocks(samples),

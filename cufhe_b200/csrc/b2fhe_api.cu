@@ -40,7 +40,7 @@ std::mutex g_mu;
 int g_gates_per_cta = 0;
 int g_ks_variant = 0;            // 0 = by batch size, 1 = k_keyswitch_lat, 2 = k_keyswitch
 int g_ks_lat_max_per_sm = 32;    // k_keyswitch_lat up to this many gates per SM (measured faster up to there)
-int g_br_cluster_max = 33;       // k_blind_rotate_cl4 for batches up to this many gates (33 four-CTA clusters = 132 CTAs run concurrently on B200, 34 take two waves)
+int g_br_cluster_max = 66;       // k_blind_rotate_cl4 up to this many gates: 33 four-CTA clusters (132 CTAs) run concurrently on B200 (1.62 ms); two waves (3.2 ms) still beat k_blind_rotate_lat (3.5 ms)
 int g_br_burst_detect = 1;       // small calls arriving back to back use the throughput kernel
 constexpr int64_t kBurstGapNs = 300000;
 int g_br_variant = 0;            // 0 = default, 1 = k_blind_rotate_lat, 2 = k_blind_rotate_cl, 16 = k_blind_rotate16, 32 = k_blind_rotate
@@ -116,7 +116,8 @@ int setup_device(int device)
     if (int r = set_br_attr<8>()) return r;
     CK(cudaFuncSetAttribute(k_blind_rotate_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatSmemBytes));
     CK(cudaFuncSetAttribute(k_blind_rotate_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, kClSmemBytes));
-    CK(cudaFuncSetAttribute(k_blind_rotate_cl4, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
+    CK(cudaFuncSetAttribute(k_blind_rotate_cl4<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
+    CK(cudaFuncSetAttribute(k_blind_rotate_cl4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
     CK(cudaFuncSetAttribute(k_cmux16<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(1)));
     CK(cudaFuncSetAttribute(k_cmux16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(4)));
     CK(cudaFuncSetAttribute(k_polymul16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, polymul16_smem_bytes(4)));
@@ -230,7 +231,7 @@ int b2fhe_set_ks_variant(int variant)
 }
 int b2fhe_set_br_variant(int variant)
 {
-    REQUIRE(variant == 0 || variant == 1 || variant == 2 || variant == 4 || variant == 16 || variant == 32, B2FHE_E_BAD_ARGUMENT);
+    REQUIRE(variant == 0 || variant == 1 || variant == 2 || variant == 4 || variant == 5 || variant == 16 || variant == 32, B2FHE_E_BAD_ARGUMENT);
     g_br_variant = variant;
     return 0;
 }

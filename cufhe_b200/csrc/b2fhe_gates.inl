@@ -39,10 +39,12 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
         const int64_t prev = last_ns[dev].exchange(now, std::memory_order_relaxed);
         burst = g_br_burst_detect && prev != 0 && now - prev < kBurstGapNs;
     }
-    // up to 33 gates: one gate per cluster of 4 CTAs x 128 threads (33 clusters run concurrently)
-    if (variant == 4 || (g_br_variant == 0 && g == 0 && !burst && P.count <= g_br_cluster_max)) {
+    // up to 66 gates: one gate per cluster of 4 CTAs x 128 threads (33 clusters run concurrently; two waves still win)
+    if (variant == 4 || variant == 5 || (g_br_variant == 0 && g == 0 && !burst && P.count <= g_br_cluster_max)) {
         P.bk = c.bk_ntt16;
-        k_blind_rotate_cl4<<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, c.tab16);
+        // default: hand-overs by st.async + mbarrier (variant 5); variant 4 = cluster barriers (A/B)
+        if (variant == 4) k_blind_rotate_cl4<false><<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, c.tab16);
+        else k_blind_rotate_cl4<true><<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, c.tab16);
         LAUNCHED();
         return 0;
     }

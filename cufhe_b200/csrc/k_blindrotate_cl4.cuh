@@ -16,6 +16,12 @@
 //      keep identical copies of acc_j).
 // Same arithmetic (ntt16.cuh), key layout and tables as k_blind_rotate16: bit-identical results.
 //
+// ASYNC = true: the two hand-overs use st.async stores that complete on an mbarrier of the receiving
+// CTA (transaction bytes) instead of "remote stores, cluster-scope fence, cluster barrier": ncu shows
+// the barrier version spending 18 % of its warp time in the fence and 17 % at barriers.  Receive
+// buffers are double-buffered by step parity: a sender is never two steps ahead of its receiver
+// (its own progress needs data the receiver only sends after consuming the previous buffer).
+//
 // Replaces (for batches of a few gates) __BlindRotatePreAdd__ + Accumulate
 // (reference include/gatebootstrapping_gpu.cuh:115-345), SampleExtract src/bootstrap_gpu.cu:366-381.
 #pragma once
@@ -24,14 +30,50 @@
 
 namespace b2 {
 
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, int rank)
+{
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "MBAR_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra MBAR_DONE_%=;\n"
+        "bra MBAR_WAIT_%=;\n"
+        "MBAR_DONE_%=:\n"
+        "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+// 32-bit store into another CTA's shared memory that signals `bytes written` on that CTA's mbarrier
+__device__ __forceinline__ void st_async_u32(uint32_t remote_addr, uint32_t v, uint32_t remote_bar)
+{
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.u32 [%0], %1, [%2];" ::"r"(remote_addr), "r"(v),
+                 "r"(remote_bar) : "memory");
+}
+
 constexpr int kCl4Ctas = 4;
 constexpr int kCl4Threads = 128;
 // tables | acc_j | 2 teams x 2 exchange buffers | 2 team hand-over buffers | received partial |
 // my inverse result | the other prime's inverse result | abar
-constexpr int kCl4SmemWords = kLane16TableWords + kN + 4 * kXbufWords + 2 * kN + kN + kN + kN + 640 / 2;
+// (ASYNC: received partial and the other prime's result are double-buffered, + 4 mbarriers)
+constexpr int kCl4SmemWords = kLane16TableWords + kN + 4 * kXbufWords + 2 * kN + 2 * kN + kN + 2 * kN + 640 / 2 + 8;
 // more than half an SM's shared memory, so that no two CTAs of a cluster share an SM
 constexpr int kCl4SmemBytes = (kCl4SmemWords * 4 > 120 * 1024) ? kCl4SmemWords * 4 : 120 * 1024;
 
+template <bool ASYNC>
 __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 1)
     k_blind_rotate_cl4(const BrParams P, const Lane16Tables* __restrict__ tab16)
 {
@@ -42,10 +84,11 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
     uint32_t* acc = smem + kLane16TableWords;          // acc_j
     uint32_t* xbufs = acc + kN;
     uint32_t* tx = xbufs + 4 * kXbufWords;             // [team][k * 64 + T]: product for the OTHER team's output
-    uint32_t* recv = tx + 2 * kN;                      // partial sum of output j from CTA (q, 1-j)
-    uint32_t* zloc = recv + kN;                        // inverse result, my prime      [e]
-    uint32_t* zrecv = zloc + kN;                       // inverse result, other prime   [e]
-    uint16_t* s_abar = reinterpret_cast<uint16_t*>(zrecv + kN);
+    uint32_t* recv = tx + 2 * kN;                      // [parity] partial sum of output j from CTA (q, 1-j)
+    uint32_t* zloc = recv + 2 * kN;                    // inverse result, my prime      [e]
+    uint32_t* zrecv = zloc + kN;                       // [parity] inverse result, other prime   [e]
+    uint16_t* s_abar = reinterpret_cast<uint16_t*>(zrecv + 2 * kN);
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(zrecv + 2 * kN + 640 / 2);      // [0..1] recv, [2..3] zrecv
     stage_tables16(s_tab, tab16);
 
     const int d = threadIdx.x >> 6, T = threadIdx.x & 63;      // team = gadget digit
@@ -83,7 +126,15 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
     // remote destinations: the partial of output 1-j -> CTA (q, 1-j); my inverse result -> CTA (1-q, j)
     uint32_t* dst_part = cluster.map_shared_rank(recv, q * 2 + (1 - j)) + T;
     uint32_t* dst_z = cluster.map_shared_rank(zrecv, (1 - q) * 2 + j) + T;
-    cluster.sync();                                            // every CTA's shared memory is live
+    const uint32_t ra_part = mapa_u32(smem_u32(recv + T), q * 2 + (1 - j));
+    const uint32_t ra_z = mapa_u32(smem_u32(zrecv + T), (1 - q) * 2 + j);
+    const uint32_t rb_part = mapa_u32(smem_u32(mbar), q * 2 + (1 - j));           // + 8 * parity
+    const uint32_t rb_z = mapa_u32(smem_u32(mbar + 2), (1 - q) * 2 + j);
+    if (ASYNC && threadIdx.x == 0) {
+        for (int b = 0; b < 4; b++) mbar_init(smem_u32(mbar + b), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    cluster.sync();                                            // every CTA's shared memory (and mbarriers) are live
 
     for (int i = 0; i < kLwe; i++) {
         const uint32_t abar = s_abar[i];
@@ -97,6 +148,12 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
         for (int o = 0; o < 2; o++)
 #pragma unroll
             for (int v = 0; v < 4; v++) kb[4 * o + v] = __ldg(row + o * (kN / 4) + v * 64);
+        const int par = i & 1;
+        const uint32_t phase = (uint32_t)(i >> 1) & 1u;
+        if (ASYNC && threadIdx.x == 0) {                       // arm this step's two receive barriers: 4 KB each
+            mbar_arrive_expect_tx(smem_u32(mbar + par), kN * 4);
+            mbar_arrive_expect_tx(smem_u32(mbar + 2 + par), kN * 4);
+        }
         // ---- A: digits, forward transform, products -------------------------------------------
         uint32_t x[16];
 #pragma unroll
@@ -127,33 +184,48 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
 #pragma unroll
         for (int k = 0; k < 16; k++) y[k] += tx[(1 - d) * kN + k * 64 + T];            // both rows of acc_j: (0, 4p)
         if (d != j) {                                          // output 1-j is finished by CTA (q, 1-j)
+            if (ASYNC) {
 #pragma unroll
-            for (int k = 0; k < 16; k++) dst_part[k * 64] = y[k];
+                for (int k = 0; k < 16; k++) st_async_u32(ra_part + (par * kN + k * 64) * 4, y[k], rb_part + 8 * par);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 16; k++) dst_part[k * 64] = y[k];
+            }
         }
-        cluster.sync();
+        if (!ASYNC) cluster.sync();
         // ---- B: team j sums the two accumulator polynomials' contributions, inverse transform ----
+        const uint32_t* rcv = ASYNC ? recv + par * kN : recv;
+        const uint32_t* zrc = ASYNC ? zrecv + par * kN : zrecv;
         if (d == j) {
+            if (ASYNC) mbar_wait_cluster(smem_u32(mbar + par), phase);
 #pragma unroll
-            for (int k = 0; k < 16; k++) y[k] += recv[k * 64 + T];                     // (0, 8p)
+            for (int k = 0; k < 16; k++) y[k] += rcv[k * 64 + T];                      // (0, 8p)
             inv16(y, bufA, bufB, s_tab, xa, T, q, p, bar, 64);
 #pragma unroll
             for (int k = 0; k < 16; k++) {
                 zloc[T + 64 * k] = y[k];
-                dst_z[64 * k] = y[k];
+                if (ASYNC) st_async_u32(ra_z + (par * kN + 64 * k) * 4, y[k], rb_z + 8 * par);
+                else dst_z[64 * k] = y[k];
             }
         }
-        cluster.sync();
+        if (ASYNC) {
+            __syncthreads();                                   // zloc
+            mbar_wait_cluster(smem_u32(mbar + 2 + par), phase);
+        } else {
+            cluster.sync();
+        }
         // ---- C: CRT of output j, local accumulator update (8 coefficients per thread) ------------
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const int e = (int)threadIdx.x + kCl4Threads * k;
-            const uint32_t s0 = q ? zrecv[e] : zloc[e];
-            const uint32_t s1 = q ? zloc[e] : zrecv[e];
+            const uint32_t s0 = q ? zrc[e] : zloc[e];
+            const uint32_t s1 = q ? zloc[e] : zrc[e];
             acc[e] += crt_lift32(s0, s1, c_crt_p0inv.w, c_crt_p0inv.ws);
         }
         __syncthreads();                                       // rotated reads of the next step cross threads
     }
 
+    if (ASYNC) cluster.sync();                                 // no CTA leaves while a peer may still address it
     // ---- tail: CTA (0, 0) holds acc_a, CTA (0, 1) holds acc_b ----
     if (q != 0) return;
     if (P.trlwe) {

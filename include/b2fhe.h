@@ -184,9 +184,10 @@ int b2fhe_init_from_key_cache(int ngpu, const void* blob, size_t len);
 
 /* tuning / introspection */
 int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
-/* blind-rotation kernel: 0 = default (k_blind_rotate_cl4 up to 33 gates, k_blind_rotate_lat up
+/* blind-rotation kernel: 0 = default (k_blind_rotate_cl4 up to 66 gates, k_blind_rotate_lat up
  * to one gate per SM, else k_blind_rotate16), 1 = k_blind_rotate_lat (one gate per 512-thread
- * CTA), 4 = k_blind_rotate_cl4 (one gate per cluster of 4 CTAs x 128 threads), 2 =
+ * CTA), 5 / 4 = k_blind_rotate_cl4 (one gate per cluster of 4 CTAs x 128 threads; hand-overs by
+ * st.async + mbarrier / by cluster barriers), 2 =
  * k_blind_rotate_cl (first cluster design: 8 CTAs x 64 threads), 16 =
  * k_blind_rotate16 (128 threads x 16 coefficients per gate), 32 = k_blind_rotate (64 threads
  * x 32 coefficients per gate).  All produce identical bits. */

@@ -101,9 +101,9 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     d0 = torch.from_numpy(c0.view(np.int16)).cuda()
     d1 = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
     refs = [orc.blind_rotate_extract(keys, c0[i]) for i in range(cnt)]
-    # all blind-rotation kernels (4 = 4-CTA cluster kernel, 2 = 8-CTA cluster kernel, 1 = latency kernel, 16 = 128 threads/gate, 32 = 64 threads/gate),
+    # all blind-rotation kernels (5 / 4 = 4-CTA cluster kernel with st.async + mbarrier / with cluster barriers, 2 = 8-CTA cluster kernel, 1 = latency kernel, 16 = 128 threads/gate, 32 = 64 threads/gate),
     # every gates-per-CTA instantiation
-    for variant, gs in ((4, (0,)), (2, (0,)), (1, (0,)), (16, (0, 1, 2, 3, 4, 5, 6)), (32, (0, 1, 2, 4, 6, 8))):
+    for variant, gs in ((5, (0,)), (4, (0,)), (2, (0,)), (1, (0,)), (16, (0, 1, 2, 3, 4, 5, 6)), (32, (0, 1, 2, 4, 6, 8))):
         cf._lib.check(L.b2fhe_set_br_variant(variant))
         for g in gs:
             cf._lib.check(L.b2fhe_set_gates_per_cta(g))

@@ -35,7 +35,7 @@ e.random_()
 out = torch.empty_like(x0)
 for cnt in [int(a) for a in sys.argv[1:]] or [1, 8, 16, 24, 32, 37, 64, 148]:
     row = {"count": cnt}
-    for variant in (4, 2, 1, 16):
+    for variant in (5, 4, 2, 1, 16):
         cf._lib.check(L.b2fhe_set_br_variant(variant))
         row[f"br_v{variant}_ms"] = round(timed(lambda: cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, e.data_ptr(), x0.data_ptr(), 1 << 29, cnt))), 4)
     cf._lib.check(L.b2fhe_set_br_variant(0))
