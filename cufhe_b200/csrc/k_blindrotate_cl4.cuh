@@ -45,13 +45,15 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+// default (.acquire.cta) wait, as for TMA-written shared memory: the st.async data is in shared memory
+// when the transaction count completes; an .acquire.cluster wait would add an L1 invalidate (CCTL.IVALL)
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
 {
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
         "MBAR_WAIT_%=:\n"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
         "@p bra MBAR_DONE_%=;\n"
         "bra MBAR_WAIT_%=;\n"
         "MBAR_DONE_%=:\n"
@@ -136,18 +138,17 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
     }
     cluster.sync();                                            // every CTA's shared memory (and mbarriers) are live
 
+    uint4 kb[8];                                               // my key row, fetched ONE STEP AHEAD (L2 latency ~ 1/5 of a step)
+#pragma unroll
+    for (int o = 0; o < 2; o++)
+#pragma unroll
+        for (int v = 0; v < 4; v++) kb[4 * o + v] = __ldg(bk4 + o * (kN / 4) + v * 64);
     for (int i = 0; i < kLwe; i++) {
         const uint32_t abar = s_abar[i];
         const uint32_t am = abar & (kN - 1);
         const bool flip = (abar >> kNbit) != 0;
         const uint32_t rbase = ((uint32_t)T - abar) & (kN - 1);
         const int kth = ((int)am - T + 63) >> 6;
-        const uint4* row = bk4 + (size_t)i * kRows * (4 * (kN / 4));
-        uint4 kb[8];                                           // key row first: its latency hides behind the transform
-#pragma unroll
-        for (int o = 0; o < 2; o++)
-#pragma unroll
-            for (int v = 0; v < 4; v++) kb[4 * o + v] = __ldg(row + o * (kN / 4) + v * 64);
         const int par = i & 1;
         const uint32_t phase = (uint32_t)(i >> 1) & 1u;
         if (ASYNC && threadIdx.x == 0) {                       // arm this step's two receive barriers: 4 KB each
@@ -179,6 +180,13 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
             t[64] = (uint32_t)umontmul_p(x[4 * v + 1], bo.y, p, pinv) + p;
             t[128] = (uint32_t)umontmul_p(x[4 * v + 2], bo.z, p, pinv) + p;
             t[192] = (uint32_t)umontmul_p(x[4 * v + 3], bo.w, p, pinv) + p;
+        }
+        {   // the products above were the last use of this step's key row: fetch the next one now
+            const uint4* row = bk4 + (size_t)(i + 1 < kLwe ? i + 1 : i) * kRows * (4 * (kN / 4));
+#pragma unroll
+            for (int o = 0; o < 2; o++)
+#pragma unroll
+                for (int v = 0; v < 4; v++) kb[4 * o + v] = __ldg(row + o * (kN / 4) + v * 64);
         }
         __syncthreads();
 #pragma unroll
