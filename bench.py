@@ -173,7 +173,7 @@ def run_product(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, flush_l2=True):
         """device time of exactly `steps` steps (CUDA events on the launching stream; L2
         flushed between iterations, flush outside the timed intervals); max over ranks."""
         for _ in range(warmup):
@@ -181,7 +181,8 @@ def run_product(args):
         barrier()
         total = 0.0
         for _ in range(steps):
-            flush.fill_(1)
+            if flush_l2:
+                flush.fill_(1)
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(st)
             fn()
@@ -212,6 +213,7 @@ def run_product(args):
         cf._lib.check(L.b2fhe_gate_batch_host(local, sp, NAND, None, 0, hout.data_ptr(), h0.data_ptr(), h1.data_ptr(), None, 1))
 
     lat_dev = timed(one_dev, 10, 3) / 10
+    lat_dev_warm = timed(one_dev, 10, 3, flush_l2=False) / 10
     lat_host = timed(one_host, 10, 3) / 10
     stop.set()
     th.join()
@@ -248,9 +250,10 @@ def run_product(args):
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 2 * cnt * 1274 * world,
                     "d2h_bytes_per_step": cnt * 1274 * world},
             "single_gate_latency_ms": {"device_resident": lat_dev, "host_buffers": lat_host,
+                                       "device_resident_keys_in_l2": lat_dev_warm,
                                        "note": "one NAND: k_blind_rotate_cl4 (one gate per 4-CTA cluster, DSMEM) + k_keyswitch_lat; L2 is flushed "
-                                               "before every call here (keys come from HBM) -- 1.74 ms with the keys L2-resident "
-                                               "(tools/probe_small.py)"},
+                                               "before every call for the first two figures (keys come from HBM); the third "
+                                               "repeats the call without the flush"},
             "gpu_launches": int(launches),
             "clocks": summarize_clocks(samples),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
