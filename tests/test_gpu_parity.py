@@ -307,3 +307,28 @@ def test_full_batch_16384_nand(engine, keys):
     idx = np.arange(0, cnt, 431)
     ref = orc.gate_batch(keys, orc.OP["NAND"], 0, x0[idx], x1[idx])
     assert np.array_equal(got[idx], ref)
+
+
+def test_cluster_kernel_stress_against_throughput_kernel(engine):
+    """The cluster kernels hand data between CTAs with st.async / mbarrier (or cluster barriers) and
+    reuse double-buffered receive areas every other step: a protocol slip would show up as sporadic
+    corruption.  Full waves (33 concurrent clusters), two waves, and repeated launches on random
+    inputs must reproduce the throughput kernel's bits every time."""
+    cf = engine
+    L = cf._lib.lib()
+    rng = np.random.default_rng(77)
+    try:
+        for cnt in (33, 66, 7):
+            x = torch.from_numpy(rng.integers(0, 2**16, (cnt, 637), dtype=np.uint64).astype(np.uint16).view(np.int16)).cuda()
+            want = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
+            cf._lib.check(L.b2fhe_set_br_variant(16))
+            cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, want.data_ptr(), x.data_ptr(), 1 << 29, cnt))
+            for variant in (5, 4, 2):
+                cf._lib.check(L.b2fhe_set_br_variant(variant))
+                for rep in range(6 if variant == 5 else 2):
+                    got = torch.zeros_like(want)
+                    cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, got.data_ptr(), x.data_ptr(), 1 << 29, cnt))
+                    torch.cuda.synchronize()
+                    assert torch.equal(got, want), (cnt, variant, rep)
+    finally:
+        cf._lib.check(L.b2fhe_set_br_variant(0))
