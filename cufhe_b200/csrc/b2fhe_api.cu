@@ -40,7 +40,7 @@ std::mutex g_mu;
 int g_gates_per_cta = 0;
 int g_ks_variant = 0;            // 0 = by batch size, 1 = k_keyswitch_lat, 2 = k_keyswitch
 int g_ks_lat_max_per_sm = 32;    // k_keyswitch_lat up to this many gates per SM (measured faster up to there)
-int g_br_cluster_max = 66;       // k_blind_rotate_cl4 up to this many gates: 33 four-CTA clusters (132 CTAs) run concurrently on B200 (1.62 ms); two waves (3.2 ms) still beat k_blind_rotate_lat (3.5 ms)
+int g_br_cluster_max = 70;       // k_blind_rotate_cl4 up to this many gates: 33 four-CTA clusters run one CTA per SM (1.63 ms), up to 70 two per SM (2.2 ms); beyond that k_blind_rotate_lat (3.5 ms) wins
 int g_br_burst_detect = 1;       // small calls arriving back to back use the throughput kernel
 constexpr int64_t kBurstGapNs = 300000;
 int g_br_variant = 0;            // 0 = default, 1 = k_blind_rotate_lat, 2 = k_blind_rotate_cl, 16 = k_blind_rotate16, 32 = k_blind_rotate

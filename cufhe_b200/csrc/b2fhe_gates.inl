@@ -39,7 +39,7 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
         const int64_t prev = last_ns[dev].exchange(now, std::memory_order_relaxed);
         burst = g_br_burst_detect && prev != 0 && now - prev < kBurstGapNs;
     }
-    // up to 66 gates: one gate per cluster of 4 CTAs x 128 threads (33 clusters run concurrently; two waves still win)
+    // up to 70 gates: one gate per cluster of 4 CTAs x 128 threads (70 clusters are resident at once, two CTAs per SM)
     if (variant == 4 || variant == 5 || (g_br_variant == 0 && g == 0 && !burst && P.count <= g_br_cluster_max)) {
         P.bk = c.bk_ntt16;
         // default: hand-overs by st.async + mbarrier (variant 5); variant 4 = cluster barriers (A/B)

@@ -72,11 +72,11 @@ constexpr int kCl4Threads = 128;
 // my inverse result | the other prime's inverse result | abar
 // (ASYNC: received partial and the other prime's result are double-buffered, + 4 mbarriers)
 constexpr int kCl4SmemWords = kLane16TableWords + kN + 4 * kXbufWords + 2 * kN + 2 * kN + kN + 2 * kN + 640 / 2 + 8;
-// more than half an SM's shared memory, so that no two CTAs of a cluster share an SM
-constexpr int kCl4SmemBytes = (kCl4SmemWords * 4 > 120 * 1024) ? kCl4SmemWords * 4 : 120 * 1024;
+// 110 KB: two CTAs (of different gates, or of one gate when few are in flight) fit one SM
+constexpr int kCl4SmemBytes = kCl4SmemWords * 4;
 
 template <bool ASYNC>
-__global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 1)
+__global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 2)
     k_blind_rotate_cl4(const BrParams P, const Lane16Tables* __restrict__ tab16)
 {
     namespace cg = cooperative_groups;

@@ -184,7 +184,7 @@ int b2fhe_init_from_key_cache(int ngpu, const void* blob, size_t len);
 
 /* tuning / introspection */
 int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
-/* blind-rotation kernel: 0 = default (k_blind_rotate_cl4 up to 66 gates, k_blind_rotate_lat up
+/* blind-rotation kernel: 0 = default (k_blind_rotate_cl4 up to 70 gates, k_blind_rotate_lat up
  * to one gate per SM, else k_blind_rotate16), 1 = k_blind_rotate_lat (one gate per 512-thread
  * CTA), 5 / 4 = k_blind_rotate_cl4 (one gate per cluster of 4 CTAs x 128 threads; hand-overs by
  * st.async + mbarrier / by cluster barriers), 2 =

@@ -312,13 +312,13 @@ def test_full_batch_16384_nand(engine, keys):
 def test_cluster_kernel_stress_against_throughput_kernel(engine):
     """The cluster kernels hand data between CTAs with st.async / mbarrier (or cluster barriers) and
     reuse double-buffered receive areas every other step: a protocol slip would show up as sporadic
-    corruption.  Full waves (33 concurrent clusters), two waves, and repeated launches on random
+    corruption.  One CTA per SM (33 clusters), two per SM (70 clusters) and repeated launches on random
     inputs must reproduce the throughput kernel's bits every time."""
     cf = engine
     L = cf._lib.lib()
     rng = np.random.default_rng(77)
     try:
-        for cnt in (33, 66, 7):
+        for cnt in (33, 70, 7):
             x = torch.from_numpy(rng.integers(0, 2**16, (cnt, 637), dtype=np.uint64).astype(np.uint16).view(np.int16)).cuda()
             want = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
             cf._lib.check(L.b2fhe_set_br_variant(16))
