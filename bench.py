@@ -32,9 +32,9 @@ UNIT = "gates/s"
 # algorithmic figures per NAND bootstrap
 KEY_BYTES_PER_GATE = 41_680_896            # NTT-domain bootstrapping key touched per gate
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_blind_rotate16<4> launch over 16384 gates
-# (profiles/r1_ncu_traffic_k_blind_rotate16_16384.csv): keys once + ciphertext I/O, far below the
+# (profiles/r1_ncu_traffic_k_blind_rotate16_16384_v6.csv): keys once + ciphertext I/O, far below the
 # algorithmic key bytes because each key row is served to all gates from L2
-DRAM_TRAFFIC_PER_LAUNCH = 68_316_928 + 48_672_768
+DRAM_TRAFFIC_PER_LAUNCH = 67_865_344 + 48_037_888
 # integer multiply-pipe slots per gate of OUR formulation (DESIGN.md "integer roofline")
 IMAD_SLOTS_PER_GATE = 636 * 2 * (6 * 5120 * 4 + 2 * 1024 * 4 + 8192 * 5 + 1024 * 5)
 
