@@ -11,10 +11,10 @@ template <int G> int launch_br_g(const BrParams& P, cudaStream_t st)
     LAUNCHED();
     return 0;
 }
-template <int G> int launch_br16_g(const DevCtx& c, const BrParams& P, cudaStream_t st)
+template <int G, int PAIR = 0> int launch_br16_g(const DevCtx& c, const BrParams& P, cudaStream_t st)
 {
     const int grid = (P.count + G - 1) / G;
-    k_blind_rotate16<G><<<grid, 128 * G, br16_smem_bytes(G), st>>>(P, c.tab16);
+    k_blind_rotate16<G, PAIR><<<grid, 128 * G, br16_smem_bytes(G), st>>>(P, c.tab16);
     LAUNCHED();
     return 0;
 }
@@ -62,6 +62,24 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
         k_blind_rotate_lat<<<P.count, kLatThreads, kLatSmemBytes, st>>>(P, c.tab16);
         LAUNCHED();
         return 0;
+    }
+    if (variant == 17 || variant == 18) {      // row-pair key multiply (17), + paired digit transforms (18): A/B against 16
+        P.bk = c.bk_ntt16;
+        if (g == 0) g = per_sm >= 4 ? 4 : per_sm >= 1 ? per_sm : 1;
+        if (variant == 17) switch (g) {
+            case 1: return launch_br16_g<1, 1>(c, P, st);
+            case 2: return launch_br16_g<2, 1>(c, P, st);
+            case 3: return launch_br16_g<3, 1>(c, P, st);
+            case 4: return launch_br16_g<4, 1>(c, P, st);
+            default: return launch_br16_g<5, 1>(c, P, st);
+        }
+        switch (g) {
+            case 1: return launch_br16_g<1, 2>(c, P, st);
+            case 2: return launch_br16_g<2, 2>(c, P, st);
+            case 3: return launch_br16_g<3, 2>(c, P, st);
+            case 4: return launch_br16_g<4, 2>(c, P, st);
+            default: return launch_br16_g<5, 2>(c, P, st);
+        }
     }
     if (variant == 16) {
         P.bk = c.bk_ntt16;

@@ -94,6 +94,33 @@ __device__ __forceinline__ void fwd16_digits(uint32_t (&x)[16], uint32_t* bufA, 
     fwd16_tail(x, bufA, bufB, s_tab, a, T, q, p, bar, barn);
 }
 
+// two digit transforms at once (x0 through bufA, x1 through bufB): 16 independent butterflies per
+// stage.  Both buffers are in use at every exchange, so each exchange's stores wait (barrier) for
+// the previous exchange's loads -- four barriers, as for two single transforms.
+__device__ __forceinline__ void fwd16_digits2(uint32_t (&x0)[16], uint32_t (&x1)[16], uint32_t* bufA, uint32_t* bufB,
+                                              const uint32_t* s_tab, const X16& a, int T, int q, uint32_t p, int bar,
+                                              int barn = 128)
+{
+    pass16_fwd_digits(x0, t16_lut1(s_tab, q), t16_lut24(s_tab, q), t16_lut35(s_tab, q), c_fw1[q], p);
+    pass16_fwd_digits(x1, t16_lut1(s_tab, q), t16_lut24(s_tab, q), t16_lut35(s_tab, q), c_fw1[q], p);
+    named_bar_sync(bar, barn);
+#pragma unroll
+    for (int k = 0; k < 16; k++) { bufA[a.wA + 68 * k] = x0[k]; bufB[a.wA + 68 * k] = x1[k]; }
+    named_bar_sync(bar, barn);
+#pragma unroll
+    for (int k = 0; k < 16; k++) { x0[k] = bufA[a.rB + 4 * k]; x1[k] = bufB[a.rB + 4 * k]; }
+    pass16_fwd<4, 8>(x0, t16_fw2(s_tab, q, T >> 2), 16, p);
+    pass16_fwd<4, 8>(x1, t16_fw2(s_tab, q, T >> 2), 16, p);
+    named_bar_sync(bar, barn);
+#pragma unroll
+    for (int k = 0; k < 16; k++) { bufA[a.wB + 4 * k + (k >> 2)] = x0[k]; bufB[a.wB + 4 * k + (k >> 2)] = x1[k]; }
+    named_bar_sync(bar, barn);
+#pragma unroll
+    for (int k = 0; k < 16; k++) { x0[k] = bufA[a.rC + k]; x1[k] = bufB[a.rC + k]; }
+    pass16_fwd3(x0, t16_fw3(s_tab, q, T), 64, p);
+    pass16_fwd3(x1, t16_fw3(s_tab, q, T), 64, p);
+}
+
 // inverse transform incl. n^-1 psi^-e scaling: layout C in, layout A out, values in [0, 2p)
 __device__ __forceinline__ void inv16(uint32_t (&x)[16], uint32_t* bufA, uint32_t* bufB, const uint32_t* s_tab,
                                       const X16& a, int T, int q, uint32_t p, int bar, int barn = 128)
@@ -124,6 +151,8 @@ __host__ __device__ constexpr int br16_smem_bytes(int gates) { return (kLane16Ta
 
 // One code copy serves both primes (q is team-uniform).  sa = residues of output polynomial
 // q ("mine", finished by this team), sb = residues of output polynomial 1-q (handed over).
+// PAIR: 0 = one row at a time, 1 = row pairs share a Montgomery reduction, 2 = ... and are transformed together
+template <int PAIR>
 __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, uint32_t* acc, uint32_t* bufA,
                                                uint32_t* bufB, const uint32_t* bufA_other, const uint16_t* s_abar,
                                                const uint32_t* s_tab, const int T, const int q, const int bar)
@@ -139,13 +168,56 @@ __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, 
         const uint32_t abar = s_abar[i];
         uint32_t sa[16], sb[16];
 #pragma unroll
-        for (int k = 0; k < 16; k++) sa[k] = sb[k] = 4u * p;     // + four products in (-p, p) -> (0, 8p)
+        for (int k = 0; k < 16; k++) sa[k] = sb[k] = PAIR ? 2u * p : 4u * p;   // + four products in (-p, p) -> (0, 8p); PAIR: + two in (-p, 2p) -> (0, 6p)
 
         const uint32_t am = abar & (kN - 1);
         const bool flip = (abar >> kNbit) != 0;
         const uint32_t rbase = ((uint32_t)T - abar) & (kN - 1);
         // coefficient e = T + 64k is negated iff (e < am) xor flip;  e < am <=> k < kth
         const int kth = ((int)am - T + 63) >> 6;
+        if (PAIR) {
+            // Both digits of acc_j are transformed before the key multiply, so a row PAIR shares one
+            // Montgomery reduction: x0 b0 + x1 b1 < 2^33 p is accumulated in 64 bits (IMAD.WIDE with
+            // accumulate) and reduced once -- 7 multiply-pipe slots per pair instead of 10.
+#pragma unroll 1
+            for (int j = 0; j < 2; j++) {
+                uint32_t x0[16], x1[16];
+                const uint32_t* aj = acc + j * kN;
+#pragma unroll
+                for (int k = 0; k < 16; k++) {
+                    uint32_t rot = aj[(rbase + 64 * k) & (kN - 1)];
+                    const bool neg = (k < kth) != flip;
+                    rot = neg ? 0u - rot : rot;
+                    const uint32_t t = rot - aj[T + 64 * k] + kDecompAdd;
+                    x0[k] = t >> 24;
+                    x1[k] = (t >> 16) & 0xFFu;
+                }
+                if (PAIR == 2) {
+                    fwd16_digits2(x0, x1, bufA, bufB, s_tab, xa, T, q, p, bar);
+                } else {
+                    fwd16_digits(x0, bufA, bufB, s_tab, xa, T, q, p, bar);
+                    fwd16_digits(x1, bufA, bufB, s_tab, xa, T, q, p, bar);
+                }
+                const uint4* row0 = bk4 + (size_t)(i * kRows + 2 * j) * (4 * (kN / 4));
+                const uint4* row1 = row0 + 4 * (kN / 4);
+#pragma unroll
+                for (int v = 0; v < 4; v++) {
+                    const uint4 b0 = __ldg(row0 + off_a + v * 64), b1 = __ldg(row1 + off_a + v * 64);
+                    sa[4 * v + 0] += umontmul2_p(x0[4 * v + 0], b0.x, x1[4 * v + 0], b1.x, p, pinv);
+                    sa[4 * v + 1] += umontmul2_p(x0[4 * v + 1], b0.y, x1[4 * v + 1], b1.y, p, pinv);
+                    sa[4 * v + 2] += umontmul2_p(x0[4 * v + 2], b0.z, x1[4 * v + 2], b1.z, p, pinv);
+                    sa[4 * v + 3] += umontmul2_p(x0[4 * v + 3], b0.w, x1[4 * v + 3], b1.w, p, pinv);
+                }
+#pragma unroll
+                for (int v = 0; v < 4; v++) {
+                    const uint4 b0 = __ldg(row0 + off_b + v * 64), b1 = __ldg(row1 + off_b + v * 64);
+                    sb[4 * v + 0] += umontmul2_p(x0[4 * v + 0], b0.x, x1[4 * v + 0], b1.x, p, pinv);
+                    sb[4 * v + 1] += umontmul2_p(x0[4 * v + 1], b0.y, x1[4 * v + 1], b1.y, p, pinv);
+                    sb[4 * v + 2] += umontmul2_p(x0[4 * v + 2], b0.z, x1[4 * v + 2], b1.z, p, pinv);
+                    sb[4 * v + 3] += umontmul2_p(x0[4 * v + 3], b0.w, x1[4 * v + 3], b1.w, p, pinv);
+                }
+            }
+        } else {
         uint32_t dlo[4];
 #pragma unroll 1
         for (int r = 0; r < kRows; r++) {           // TRGSW row r = 2 j + d
@@ -185,7 +257,9 @@ __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, 
                 sb[4 * v + 3] += (uint32_t)umontmul_p(x[4 * v + 3], b.w, p, pinv);
             }
         }
+        }
         // two inverse transforms (two code copies: no register swap between them)
+        if (PAIR == 2) named_bar_sync(bar, 128);     // the paired transform's last loads were from both buffers
         inv16(sb, bufA, bufB, s_tab, xa, T, q, p, bar);
         inv16(sa, bufA, bufB, s_tab, xa, T, q, p, bar);
         // now sa = INTT(out q) (mine), sb = INTT(out 1-q): hand sb to the other team
@@ -203,7 +277,7 @@ __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, 
     }
 }
 
-template <int G>
+template <int G, int PAIR = 0>
 __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate16(const BrParams P, const Lane16Tables* __restrict__ tab16)
 {
     extern __shared__ __align__(16) uint32_t smem[];
@@ -244,7 +318,7 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate16(const BrParams P,
     }
     named_bar_sync(bar, 128);
 
-    br16_gate_loop(P.bk, acc, bufA, bufB, bufA_other, s_abar, s_tab, T, q, bar);
+    br16_gate_loop<PAIR>(P.bk, acc, bufA, bufB, bufA_other, s_abar, s_tab, T, q, bar);
 
     // ---- SampleExtract(0) (src/bootstrap_gpu.cu:366-381) ----
     if (P.trlwe) {          // BootstrapTLWE2TRLWE (src/bootstrap_gpu.cu:316-322): no extraction

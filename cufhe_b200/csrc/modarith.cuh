@@ -79,6 +79,19 @@ B2_HD int32_t umontmul_p(uint32_t a, uint32_t bt, uint32_t p, uint32_t pinv)
 #endif
     return (int32_t)((uint32_t)(prod >> 32) - t);
 }
+// a0 b0 + a1 b1 in one reduction: 0 <= a < 2^32, 0 <= b < p, so the 64-bit sum is < 2^33 p and the
+// result lies in (-p, 2p).  On sm_100a: two IMAD.WIDE (the second accumulates), IMAD, IMAD.HI.
+B2_HD uint32_t umontmul2_p(uint32_t a0, uint32_t b0, uint32_t a1, uint32_t b1, uint32_t p, uint32_t pinv)
+{
+    const uint64_t prod = (uint64_t)a0 * (uint64_t)b0 + (uint64_t)a1 * (uint64_t)b1;
+    const uint32_t m = (uint32_t)prod * pinv;
+#ifdef __CUDA_ARCH__
+    const uint32_t t = __umulhi(m, p);
+#else
+    const uint32_t t = (uint32_t)(((uint64_t)m * (uint64_t)p) >> 32);
+#endif
+    return (uint32_t)(prod >> 32) - t;
+}
 template <int Q>
 B2_HD int32_t umontmul(uint32_t a, uint32_t bt) { return umontmul_p(a, bt, Prime<Q>::p, Prime<Q>::pinv); }
 
