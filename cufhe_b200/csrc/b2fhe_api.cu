@@ -12,6 +12,7 @@
 #include "../../include/b2fhe.h"
 #include "k_blindrotate.cuh"
 #include "k_blindrotate16.cuh"
+#include "k_blindrotate16q.cuh"
 #include "k_blindrotate_lat.cuh"
 #include "k_blindrotate_cl.cuh"
 #include "k_blindrotate_cl4.cuh"
@@ -74,9 +75,12 @@ template <int G> int set_br_attr()
 template <int G> int set_br16_attr()
 {
     CK(cudaFuncSetAttribute(k_blind_rotate16<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
+    if (G <= 4) CK(cudaFuncSetAttribute(k_blind_rotate16q<(G <= 4 ? G : 4)>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16q_smem_bytes(G <= 4 ? G : 4)));
     if (G <= 5) {
         CK(cudaFuncSetAttribute(k_blind_rotate16<(G <= 5 ? G : 5), 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
         CK(cudaFuncSetAttribute(k_blind_rotate16<(G <= 5 ? G : 5), 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
+        CK(cudaFuncSetAttribute(k_blind_rotate16<(G <= 5 ? G : 5), 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
+        CK(cudaFuncSetAttribute(k_blind_rotate16<(G <= 5 ? G : 5), 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
     }
     return 0;
 }
@@ -235,7 +239,7 @@ int b2fhe_set_ks_variant(int variant)
 }
 int b2fhe_set_br_variant(int variant)
 {
-    REQUIRE(variant == 0 || variant == 1 || variant == 2 || variant == 4 || variant == 5 || variant == 16 || variant == 17 || variant == 18 || variant == 32, B2FHE_E_BAD_ARGUMENT);
+    REQUIRE(variant == 0 || variant == 1 || variant == 2 || variant == 4 || variant == 5 || variant == 16 || (variant >= 17 && variant <= 21) || variant == 32, B2FHE_E_BAD_ARGUMENT);
     g_br_variant = variant;
     return 0;
 }

@@ -18,10 +18,17 @@ template <int G, int PAIR = 0> int launch_br16_g(const DevCtx& c, const BrParams
     LAUNCHED();
     return 0;
 }
+template <int G> int launch_br16q_g(const DevCtx& c, const BrParams& P, cudaStream_t st)
+{
+    const int grid = (P.count + G - 1) / G;
+    k_blind_rotate16q<G><<<grid, 128 * G, br16q_smem_bytes(G), st>>>(P, c.tab16);
+    LAUNCHED();
+    return 0;
+}
 int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
 {
     if (P.count <= 0) return 0;
-    const int variant = g_br_variant ? g_br_variant : 16;
+    const int variant = g_br_variant ? g_br_variant : 19;
     int g = g_gates_per_cta;
     const int per_sm = (P.count + c.sm_count - 1) / c.sm_count;
     // The two latency kernels spend several SMs (or a whole SM) on one gate: right for an
@@ -63,7 +70,17 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
         LAUNCHED();
         return 0;
     }
-    if (variant == 17 || variant == 18) {      // row-pair key multiply (17), + paired digit transforms (18): A/B against 16
+    if (variant == 21) {      // paired transforms + four exchange buffers per team (8 barriers per step)
+        P.bk = c.bk_ntt16;
+        if (g == 0) g = per_sm >= 4 ? 4 : per_sm >= 1 ? per_sm : 1;
+        switch (g) {
+            case 1: return launch_br16q_g<1>(c, P, st);
+            case 2: return launch_br16q_g<2>(c, P, st);
+            case 3: return launch_br16q_g<3>(c, P, st);
+            default: return launch_br16q_g<4>(c, P, st);
+        }
+    }
+    if (variant >= 17 && variant <= 20) {      // row-pair key multiply (17), + paired digit transforms (18): A/B against 16
         P.bk = c.bk_ntt16;
         if (g == 0) g = per_sm >= 4 ? 4 : per_sm >= 1 ? per_sm : 1;
         if (variant == 17) switch (g) {
@@ -72,6 +89,20 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
             case 3: return launch_br16_g<3, 1>(c, P, st);
             case 4: return launch_br16_g<4, 1>(c, P, st);
             default: return launch_br16_g<5, 1>(c, P, st);
+        }
+        if (variant == 20) switch (g) {
+            case 1: return launch_br16_g<1, 4>(c, P, st);
+            case 2: return launch_br16_g<2, 4>(c, P, st);
+            case 3: return launch_br16_g<3, 4>(c, P, st);
+            case 4: return launch_br16_g<4, 4>(c, P, st);
+            default: return launch_br16_g<5, 4>(c, P, st);
+        }
+        if (variant == 19) switch (g) {
+            case 1: return launch_br16_g<1, 3>(c, P, st);
+            case 2: return launch_br16_g<2, 3>(c, P, st);
+            case 3: return launch_br16_g<3, 3>(c, P, st);
+            case 4: return launch_br16_g<4, 3>(c, P, st);
+            default: return launch_br16_g<5, 3>(c, P, st);
         }
         switch (g) {
             case 1: return launch_br16_g<1, 2>(c, P, st);

@@ -99,11 +99,11 @@ __device__ __forceinline__ void fwd16_digits(uint32_t (&x)[16], uint32_t* bufA, 
 // the previous exchange's loads -- four barriers, as for two single transforms.
 __device__ __forceinline__ void fwd16_digits2(uint32_t (&x0)[16], uint32_t (&x1)[16], uint32_t* bufA, uint32_t* bufB,
                                               const uint32_t* s_tab, const X16& a, int T, int q, uint32_t p, int bar,
-                                              int barn = 128)
+                                              bool lead = true, int barn = 128)
 {
     pass16_fwd_digits(x0, t16_lut1(s_tab, q), t16_lut24(s_tab, q), t16_lut35(s_tab, q), c_fw1[q], p);
     pass16_fwd_digits(x1, t16_lut1(s_tab, q), t16_lut24(s_tab, q), t16_lut35(s_tab, q), c_fw1[q], p);
-    named_bar_sync(bar, barn);
+    if (lead) named_bar_sync(bar, barn);        // not needed when a barrier already follows the buffers' last loads
 #pragma unroll
     for (int k = 0; k < 16; k++) { bufA[a.wA + 68 * k] = x0[k]; bufB[a.wA + 68 * k] = x1[k]; }
     named_bar_sync(bar, barn);
@@ -146,12 +146,44 @@ __device__ __forceinline__ void inv16(uint32_t (&x)[16], uint32_t* bufA, uint32_
     }
 }
 
+// two inverse transforms at once (x0 through bufA, x1 through bufB); the caller guarantees that
+// nobody still reads either buffer when this starts
+__device__ __forceinline__ void inv16_2(uint32_t (&x0)[16], uint32_t (&x1)[16], uint32_t* bufA, uint32_t* bufB,
+                                        const uint32_t* s_tab, const X16& a, int T, int q, uint32_t p, int bar, int barn = 128)
+{
+    pass16_inv<true>(x0, c_iv1[q], 1, p);
+    pass16_inv<true>(x1, c_iv1[q], 1, p);
+#pragma unroll
+    for (int k = 0; k < 16; k++) { bufA[a.rC + k] = x0[k]; bufB[a.rC + k] = x1[k]; }
+    named_bar_sync(bar, barn);
+#pragma unroll
+    for (int k = 0; k < 16; k++) { x0[k] = bufA[a.rD + 17 * k]; x1[k] = bufB[a.rD + 17 * k]; }
+    pass16_inv<false>(x0, t16_iv2(s_tab, q, T & 15), 16, p);
+    pass16_inv<false>(x1, t16_iv2(s_tab, q, T & 15), 16, p);
+    named_bar_sync(bar, barn);
+#pragma unroll
+    for (int k = 0; k < 16; k++) { bufA[a.wD + 16 * k] = x0[k]; bufB[a.wD + 16 * k] = x1[k]; }
+    named_bar_sync(bar, barn);
+#pragma unroll
+    for (int k = 0; k < 16; k++) { x0[k] = bufA[T + 64 * k + 16 * (k >> 2)]; x1[k] = bufB[T + 64 * k + 16 * (k >> 2)]; }
+    pass16_inv3(x0, t16_iv3(s_tab, q, T), 64, p);
+    pass16_inv3(x1, t16_iv3(s_tab, q, T), 64, p);
+    const Tw* sc = t16_scale(s_tab, q, T);
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        const Tw f = sc[k * 64];
+        x0[k] = shoup_mul_p(x0[k], f.w, f.ws, p);
+        x1[k] = shoup_mul_p(x1[k], f.w, f.ws, p);
+    }
+}
+
 constexpr int kBr16GateSmemWords = 2 * kN + 4 * kXbufWords + 640 / 2;   // acc + 2 teams x 2 buffers + abar(u16)
 __host__ __device__ constexpr int br16_smem_bytes(int gates) { return (kLane16TableWords + gates * kBr16GateSmemWords) * 4; }
 
 // One code copy serves both primes (q is team-uniform).  sa = residues of output polynomial
 // q ("mine", finished by this team), sb = residues of output polynomial 1-q (handed over).
-// PAIR: 0 = one row at a time, 1 = row pairs share a Montgomery reduction, 2 = ... and are transformed together
+// PAIR: 0 = one row at a time, 1 = row pairs share a Montgomery reduction, 2 = ... and are transformed together,
+// 3 = ... and so are the two inverse transforms, 4 = all four rows share one reduction
 template <int PAIR>
 __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, uint32_t* acc, uint32_t* bufA,
                                                uint32_t* bufB, const uint32_t* bufA_other, const uint16_t* s_abar,
@@ -167,6 +199,7 @@ __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, 
     for (int i = 0; i < kLwe; i++) {
         const uint32_t abar = s_abar[i];
         uint32_t sa[16], sb[16];
+        if (PAIR != 4)
 #pragma unroll
         for (int k = 0; k < 16; k++) sa[k] = sb[k] = PAIR ? 2u * p : 4u * p;   // + four products in (-p, p) -> (0, 8p); PAIR: + two in (-p, 2p) -> (0, 6p)
 
@@ -175,7 +208,47 @@ __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, 
         const uint32_t rbase = ((uint32_t)T - abar) & (kN - 1);
         // coefficient e = T + 64k is negated iff (e < am) xor flip;  e < am <=> k < kth
         const int kth = ((int)am - T + 63) >> 6;
-        if (PAIR) {
+        if (PAIR == 4) {
+            // All four digit polynomials are transformed (as two pairs) before the key multiply: the
+            // four row products of an output coefficient are summed in 64 bits (< 2^34 p) and reduced
+            // ONCE -- 11 multiply-pipe slots instead of 20 -- and no accumulator is live meanwhile.
+            uint32_t y0[16], y1[16], x0[16], x1[16];
+#pragma unroll 1
+            for (int j = 0; j < 2; j++) {
+                if (j == 1) {
+#pragma unroll
+                    for (int k = 0; k < 16; k++) { y0[k] = x0[k]; y1[k] = x1[k]; }
+                }
+                const uint32_t* aj = acc + j * kN;
+#pragma unroll
+                for (int k = 0; k < 16; k++) {
+                    uint32_t rot = aj[(rbase + 64 * k) & (kN - 1)];
+                    const bool neg = (k < kth) != flip;
+                    rot = neg ? 0u - rot : rot;
+                    const uint32_t t = rot - aj[T + 64 * k] + kDecompAdd;
+                    x0[k] = t >> 24;
+                    x1[k] = (t >> 16) & 0xFFu;
+                }
+                fwd16_digits2(x0, x1, bufA, bufB, s_tab, xa, T, q, p, bar, j != 0);
+            }
+            const uint4* row0 = bk4 + (size_t)(i * kRows) * (4 * (kN / 4));
+            const uint4 *row1 = row0 + 4 * (kN / 4), *row2 = row0 + 8 * (kN / 4), *row3 = row0 + 12 * (kN / 4);
+#pragma unroll
+            for (int v = 0; v < 4; v++) {
+                uint4 b0 = __ldg(row0 + off_a + v * 64), b1 = __ldg(row1 + off_a + v * 64);
+                uint4 b2 = __ldg(row2 + off_a + v * 64), b3 = __ldg(row3 + off_a + v * 64);
+                sa[4 * v + 0] = p + umontmul4_p(y0[4 * v + 0], b0.x, y1[4 * v + 0], b1.x, x0[4 * v + 0], b2.x, x1[4 * v + 0], b3.x, p, pinv);
+                sa[4 * v + 1] = p + umontmul4_p(y0[4 * v + 1], b0.y, y1[4 * v + 1], b1.y, x0[4 * v + 1], b2.y, x1[4 * v + 1], b3.y, p, pinv);
+                sa[4 * v + 2] = p + umontmul4_p(y0[4 * v + 2], b0.z, y1[4 * v + 2], b1.z, x0[4 * v + 2], b2.z, x1[4 * v + 2], b3.z, p, pinv);
+                sa[4 * v + 3] = p + umontmul4_p(y0[4 * v + 3], b0.w, y1[4 * v + 3], b1.w, x0[4 * v + 3], b2.w, x1[4 * v + 3], b3.w, p, pinv);
+                b0 = __ldg(row0 + off_b + v * 64), b1 = __ldg(row1 + off_b + v * 64);
+                b2 = __ldg(row2 + off_b + v * 64), b3 = __ldg(row3 + off_b + v * 64);
+                sb[4 * v + 0] = p + umontmul4_p(y0[4 * v + 0], b0.x, y1[4 * v + 0], b1.x, x0[4 * v + 0], b2.x, x1[4 * v + 0], b3.x, p, pinv);
+                sb[4 * v + 1] = p + umontmul4_p(y0[4 * v + 1], b0.y, y1[4 * v + 1], b1.y, x0[4 * v + 1], b2.y, x1[4 * v + 1], b3.y, p, pinv);
+                sb[4 * v + 2] = p + umontmul4_p(y0[4 * v + 2], b0.z, y1[4 * v + 2], b1.z, x0[4 * v + 2], b2.z, x1[4 * v + 2], b3.z, p, pinv);
+                sb[4 * v + 3] = p + umontmul4_p(y0[4 * v + 3], b0.w, y1[4 * v + 3], b1.w, x0[4 * v + 3], b2.w, x1[4 * v + 3], b3.w, p, pinv);
+            }
+        } else if (PAIR) {
             // Both digits of acc_j are transformed before the key multiply, so a row PAIR shares one
             // Montgomery reduction: x0 b0 + x1 b1 < 2^33 p is accumulated in 64 bits (IMAD.WIDE with
             // accumulate) and reduced once -- 7 multiply-pipe slots per pair instead of 10.
@@ -192,8 +265,8 @@ __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, 
                     x0[k] = t >> 24;
                     x1[k] = (t >> 16) & 0xFFu;
                 }
-                if (PAIR == 2) {
-                    fwd16_digits2(x0, x1, bufA, bufB, s_tab, xa, T, q, p, bar);
+                if (PAIR >= 2) {
+                    fwd16_digits2(x0, x1, bufA, bufB, s_tab, xa, T, q, p, bar, j != 0);   // j = 0 follows the step's closing barrier
                 } else {
                     fwd16_digits(x0, bufA, bufB, s_tab, xa, T, q, p, bar);
                     fwd16_digits(x1, bufA, bufB, s_tab, xa, T, q, p, bar);
@@ -259,9 +332,14 @@ __device__ __forceinline__ void br16_gate_loop(const uint32_t* __restrict__ bk, 
         }
         }
         // two inverse transforms (two code copies: no register swap between them)
-        if (PAIR == 2) named_bar_sync(bar, 128);     // the paired transform's last loads were from both buffers
-        inv16(sb, bufA, bufB, s_tab, xa, T, q, p, bar);
-        inv16(sa, bufA, bufB, s_tab, xa, T, q, p, bar);
+        if (PAIR >= 2) named_bar_sync(bar, 128);     // the paired transform's last loads were from both buffers
+        if (PAIR >= 3) {
+            inv16_2(sb, sa, bufA, bufB, s_tab, xa, T, q, p, bar);
+            named_bar_sync(bar, 128);                // ... and so were this one's, and the hand-over goes through bufA
+        } else {
+            inv16(sb, bufA, bufB, s_tab, xa, T, q, p, bar);
+            inv16(sa, bufA, bufB, s_tab, xa, T, q, p, bar);
+        }
         // now sa = INTT(out q) (mine), sb = INTT(out 1-q): hand sb to the other team
 #pragma unroll
         for (int k = 0; k < 16; k++) bufA[T + 64 * k] = sb[k];

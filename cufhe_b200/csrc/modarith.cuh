@@ -92,6 +92,20 @@ B2_HD uint32_t umontmul2_p(uint32_t a0, uint32_t b0, uint32_t a1, uint32_t b1, u
 #endif
     return (uint32_t)(prod >> 32) - t;
 }
+// four products in one reduction: the 64-bit sum is < 2^34 p < 2^61, result in (-p, 4p)
+B2_HD uint32_t umontmul4_p(uint32_t a0, uint32_t b0, uint32_t a1, uint32_t b1, uint32_t a2, uint32_t b2, uint32_t a3,
+                           uint32_t b3, uint32_t p, uint32_t pinv)
+{
+    const uint64_t prod = (uint64_t)a0 * (uint64_t)b0 + (uint64_t)a1 * (uint64_t)b1 + (uint64_t)a2 * (uint64_t)b2 +
+                          (uint64_t)a3 * (uint64_t)b3;
+    const uint32_t m = (uint32_t)prod * pinv;
+#ifdef __CUDA_ARCH__
+    const uint32_t t = __umulhi(m, p);
+#else
+    const uint32_t t = (uint32_t)(((uint64_t)m * (uint64_t)p) >> 32);
+#endif
+    return (uint32_t)(prod >> 32) - t;
+}
 template <int Q>
 B2_HD int32_t umontmul(uint32_t a, uint32_t bt) { return umontmul_p(a, bt, Prime<Q>::p, Prime<Q>::pinv); }
 

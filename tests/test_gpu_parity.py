@@ -103,7 +103,9 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     refs = [orc.blind_rotate_extract(keys, c0[i]) for i in range(cnt)]
     # all blind-rotation kernels (5 / 4 = 4-CTA cluster kernel with st.async + mbarrier / with cluster barriers, 2 = 8-CTA cluster kernel, 1 = latency kernel, 16 = 128 threads/gate, 32 = 64 threads/gate),
     # every gates-per-CTA instantiation
-    for variant, gs in ((5, (0,)), (4, (0,)), (2, (0,)), (1, (0,)), (16, (0, 1, 2, 3, 4, 5, 6)), (32, (0, 1, 2, 4, 6, 8))):
+    for variant, gs in ((5, (0,)), (4, (0,)), (2, (0,)), (1, (0,)), (16, (0, 1, 2, 3, 4, 5, 6)),
+                        (17, (0, 3, 5)), (18, (0, 3, 5)), (19, (0, 1, 2, 3, 4, 5)), (20, (0, 3)), (21, (0, 1, 2, 3, 4)),
+                        (32, (0, 1, 2, 4, 6, 8))):
         cf._lib.check(L.b2fhe_set_br_variant(variant))
         for g in gs:
             cf._lib.check(L.b2fhe_set_gates_per_cta(g))

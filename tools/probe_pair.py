@@ -48,8 +48,8 @@ nchk = min(cnt, 1200)
 ref = torch.zeros((nchk, 1025), dtype=torch.int32, device="cuda")
 run(16, 4, nchk, ref)
 torch.cuda.synchronize()
-for variant in (17, 18):
-    for g in (1, 2, 3, 4, 5):
+for variant in (19, 21):
+    for g in (1, 2, 3, 4):
         got = torch.zeros_like(ref)
         run(variant, g, nchk, got)
         torch.cuda.synchronize()
@@ -57,7 +57,7 @@ for variant in (17, 18):
                           "equal": bool(torch.equal(ref, got))}), flush=True)
 
 e = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
-for variant, gs in ((16, (4,)), (17, (3, 4, 5)), (18, (3, 4, 5)), (16, (4,))):
+for variant, gs in ((16, (4,)), (19, (4,)), (21, (3, 4)), (16, (4,))):
     for g in gs:
         best, med = timed(lambda: run(variant, g, cnt, e))
         print(json.dumps({"probe": "blind_rotate", "variant": variant, "gates_per_cta": g, "count": cnt, "ms_best": best,
