@@ -31,12 +31,15 @@ METRIC = "gate_bootstraps_per_sec_nand_batched"
 UNIT = "gates/s"
 # algorithmic figures per NAND bootstrap
 KEY_BYTES_PER_GATE = 41_680_896            # NTT-domain bootstrapping key touched per gate
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE k_blind_rotate16<4> launch over 16384 gates
-# (profiles/r1_ncu_traffic_k_blind_rotate16_16384_v6.csv): keys once + ciphertext I/O, far below the
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE k_blind_rotate16<4, 3> launch over 16384 gates
+# (profiles/r1_ncu_traffic_k_blind_rotate16_16384_v7.csv): keys once + ciphertext I/O, far below the
 # algorithmic key bytes because each key row is served to all gates from L2
 DRAM_TRAFFIC_PER_LAUNCH = 67_865_344 + 48_037_888
-# integer multiply-pipe slots per gate of OUR formulation (DESIGN.md "integer roofline")
-IMAD_SLOTS_PER_GATE = 636 * 2 * (6 * 5120 * 4 + 2 * 1024 * 4 + 8192 * 5 + 1024 * 5)
+# integer multiply-pipe slots per gate of OUR formulation (DESIGN.md "integer roofline"): per CMUX step
+# and prime 6 transforms x 5120 Shoup butterflies x 4 slots, 2 x 1024 scale factors x 4, 8192 key
+# products at 3.5 slots (a row pair shares one Montgomery reduction: 7 per pair; 5 each before the
+# paired kernel, when this figure was 225.3 M) and 1024 CRT lifts x 5
+IMAD_SLOTS_PER_GATE = 636 * 2 * (6 * 5120 * 4 + 2 * 1024 * 4 + 8192 * 7 // 2 + 1024 * 5)
 
 
 def clocks_sampler(stop, out):

@@ -97,12 +97,10 @@ __device__ __forceinline__ void fwd16_digits(uint32_t (&x)[16], uint32_t* bufA, 
 // two digit transforms at once (x0 through bufA, x1 through bufB): 16 independent butterflies per
 // stage.  Both buffers are in use at every exchange, so each exchange's stores wait (barrier) for
 // the previous exchange's loads -- four barriers, as for two single transforms.
-__device__ __forceinline__ void fwd16_digits2(uint32_t (&x0)[16], uint32_t (&x1)[16], uint32_t* bufA, uint32_t* bufB,
-                                              const uint32_t* s_tab, const X16& a, int T, int q, uint32_t p, int bar,
-                                              bool lead = true, int barn = 128)
+__device__ __forceinline__ void fwd16_tail2(uint32_t (&x0)[16], uint32_t (&x1)[16], uint32_t* bufA, uint32_t* bufB,
+                                            const uint32_t* s_tab, const X16& a, int T, int q, uint32_t p, int bar,
+                                            bool lead, int barn)
 {
-    pass16_fwd_digits(x0, t16_lut1(s_tab, q), t16_lut24(s_tab, q), t16_lut35(s_tab, q), c_fw1[q], p);
-    pass16_fwd_digits(x1, t16_lut1(s_tab, q), t16_lut24(s_tab, q), t16_lut35(s_tab, q), c_fw1[q], p);
     if (lead) named_bar_sync(bar, barn);        // not needed when a barrier already follows the buffers' last loads
 #pragma unroll
     for (int k = 0; k < 16; k++) { bufA[a.wA + 68 * k] = x0[k]; bufB[a.wA + 68 * k] = x1[k]; }
@@ -119,6 +117,23 @@ __device__ __forceinline__ void fwd16_digits2(uint32_t (&x0)[16], uint32_t (&x1)
     for (int k = 0; k < 16; k++) { x0[k] = bufA[a.rC + k]; x1[k] = bufB[a.rC + k]; }
     pass16_fwd3(x0, t16_fw3(s_tab, q, T), 64, p);
     pass16_fwd3(x1, t16_fw3(s_tab, q, T), 64, p);
+}
+__device__ __forceinline__ void fwd16_digits2(uint32_t (&x0)[16], uint32_t (&x1)[16], uint32_t* bufA, uint32_t* bufB,
+                                              const uint32_t* s_tab, const X16& a, int T, int q, uint32_t p, int bar,
+                                              bool lead = true, int barn = 128)
+{
+    pass16_fwd_digits(x0, t16_lut1(s_tab, q), t16_lut24(s_tab, q), t16_lut35(s_tab, q), c_fw1[q], p);
+    pass16_fwd_digits(x1, t16_lut1(s_tab, q), t16_lut24(s_tab, q), t16_lut35(s_tab, q), c_fw1[q], p);
+    fwd16_tail2(x0, x1, bufA, bufB, s_tab, a, T, q, p, bar, lead, barn);
+}
+// the same for two general inputs
+__device__ __forceinline__ void fwd16_2(uint32_t (&x0)[16], uint32_t (&x1)[16], uint32_t* bufA, uint32_t* bufB,
+                                        const uint32_t* s_tab, const X16& a, int T, int q, uint32_t p, int bar,
+                                        bool lead = true, int barn = 128)
+{
+    pass16_fwd<4, 8>(x0, c_fw1[q], 1, p);
+    pass16_fwd<4, 8>(x1, c_fw1[q], 1, p);
+    fwd16_tail2(x0, x1, bufA, bufB, s_tab, a, T, q, p, bar, lead, barn);
 }
 
 // inverse transform incl. n^-1 psi^-e scaling: layout C in, layout A out, values in [0, 2p)

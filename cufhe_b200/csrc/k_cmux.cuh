@@ -45,7 +45,6 @@ __global__ void __launch_bounds__(128 * G, 1) k_cmux16(const CmuxParams P, const
 
     const uint32_t p = q ? Prime<1>::p : Prime<0>::p;
     const uint32_t pinv = q ? Prime<1>::pinv : Prime<0>::pinv;
-    const uint32_t dig_off = p - 128u;
     const X16 xa = make_x16(T);
     const uint32_t* c1 = P.c1 + (size_t)item * 2 * kN;
     const uint32_t* c0 = P.c0 + (size_t)item * 2 * kN;
@@ -53,52 +52,45 @@ __global__ void __launch_bounds__(128 * G, 1) k_cmux16(const CmuxParams P, const
                        (size_t)q * 2 * (kN / 4);
     const int off_a = q * (kN / 4), off_b = (1 - q) * (kN / 4);
 
+    // same schedule as k_blind_rotate16's default: the two digits of c1_j - c0_j are transformed together,
+    // a row pair shares one Montgomery reduction, the two inverse transforms run together
     uint32_t sa[16], sb[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) sa[k] = sb[k] = 4u * p;
-    uint32_t dlo[4];
+    for (int k = 0; k < 16; k++) sa[k] = sb[k] = 2u * p;
 #pragma unroll 1
-    for (int r = 0; r < kRows; r++) {
-        uint32_t x[16];
-        if ((r & 1) == 0) {
-            const uint32_t* a1 = c1 + (r >> 1) * kN + T;
-            const uint32_t* a0 = c0 + (r >> 1) * kN + T;
+    for (int j = 0; j < 2; j++) {
+        uint32_t x0[16], x1[16];
+        const uint32_t* a1 = c1 + j * kN + T;
+        const uint32_t* a0 = c0 + j * kN + T;
 #pragma unroll
-            for (int k = 0; k < 16; k++) {
-                const uint32_t t = a1[64 * k] - a0[64 * k] + kDecompAdd;   // :162-194 (plain loads: out may alias)
-                x[k] = (t >> 24) + dig_off;
-                const uint32_t d1 = (t >> 16) & 0xFFu;
-                if ((k & 3) == 0) dlo[k >> 2] = d1; else dlo[k >> 2] |= d1 << (8 * (k & 3));
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < 16; k++) x[k] = ((dlo[k >> 2] >> (8 * (k & 3))) & 0xFFu) + dig_off;
+        for (int k = 0; k < 16; k++) {
+            const uint32_t t = a1[64 * k] - a0[64 * k] + kDecompAdd;   // :162-194 (plain loads: out may alias)
+            x0[k] = t >> 24;                                           // raw digits: stand for x - 128
+            x1[k] = (t >> 16) & 0xFFu;
         }
-        fwd16(x, bufA, bufB, s_tab, xa, T, q, p, bar);
-        const uint4* row = cs4 + (size_t)r * (4 * (kN / 4));
+        fwd16_digits2(x0, x1, bufA, bufB, s_tab, xa, T, q, p, bar, j != 0);
+        const uint4* row0 = cs4 + (size_t)(2 * j) * (4 * (kN / 4));
+        const uint4* row1 = row0 + 4 * (kN / 4);
 #pragma unroll
         for (int v = 0; v < 4; v++) {
-            const uint4 b = __ldg(row + off_a + v * 64);
-            sa[4 * v + 0] += (uint32_t)umontmul_p(x[4 * v + 0], b.x, p, pinv);
-            sa[4 * v + 1] += (uint32_t)umontmul_p(x[4 * v + 1], b.y, p, pinv);
-            sa[4 * v + 2] += (uint32_t)umontmul_p(x[4 * v + 2], b.z, p, pinv);
-            sa[4 * v + 3] += (uint32_t)umontmul_p(x[4 * v + 3], b.w, p, pinv);
+            const uint4 b0 = __ldg(row0 + off_a + v * 64), b1 = __ldg(row1 + off_a + v * 64);
+            sa[4 * v + 0] += umontmul2_p(x0[4 * v + 0], b0.x, x1[4 * v + 0], b1.x, p, pinv);
+            sa[4 * v + 1] += umontmul2_p(x0[4 * v + 1], b0.y, x1[4 * v + 1], b1.y, p, pinv);
+            sa[4 * v + 2] += umontmul2_p(x0[4 * v + 2], b0.z, x1[4 * v + 2], b1.z, p, pinv);
+            sa[4 * v + 3] += umontmul2_p(x0[4 * v + 3], b0.w, x1[4 * v + 3], b1.w, p, pinv);
         }
 #pragma unroll
         for (int v = 0; v < 4; v++) {
-            const uint4 b = __ldg(row + off_b + v * 64);
-            sb[4 * v + 0] += (uint32_t)umontmul_p(x[4 * v + 0], b.x, p, pinv);
-            sb[4 * v + 1] += (uint32_t)umontmul_p(x[4 * v + 1], b.y, p, pinv);
-            sb[4 * v + 2] += (uint32_t)umontmul_p(x[4 * v + 2], b.z, p, pinv);
-            sb[4 * v + 3] += (uint32_t)umontmul_p(x[4 * v + 3], b.w, p, pinv);
+            const uint4 b0 = __ldg(row0 + off_b + v * 64), b1 = __ldg(row1 + off_b + v * 64);
+            sb[4 * v + 0] += umontmul2_p(x0[4 * v + 0], b0.x, x1[4 * v + 0], b1.x, p, pinv);
+            sb[4 * v + 1] += umontmul2_p(x0[4 * v + 1], b0.y, x1[4 * v + 1], b1.y, p, pinv);
+            sb[4 * v + 2] += umontmul2_p(x0[4 * v + 2], b0.z, x1[4 * v + 2], b1.z, p, pinv);
+            sb[4 * v + 3] += umontmul2_p(x0[4 * v + 3], b0.w, x1[4 * v + 3], b1.w, p, pinv);
         }
     }
-#pragma unroll 1
-    for (int t = 0; t < 2; t++) {
-        inv16(sb, bufA, bufB, s_tab, xa, T, q, p, bar);
-#pragma unroll
-        for (int k = 0; k < 16; k++) { const uint32_t tmp = sa[k]; sa[k] = sb[k]; sb[k] = tmp; }
-    }
+    named_bar_sync(bar, 128);            // the paired transform's last loads were from both buffers
+    inv16_2(sb, sa, bufA, bufB, s_tab, xa, T, q, p, bar);
+    named_bar_sync(bar, 128);            // ... and so were this one's; the hand-over goes through bufA
     // sa = INTT(output q) (this team finishes it), sb = INTT(output 1-q) -> other team
 #pragma unroll
     for (int k = 0; k < 16; k++) bufA[T + 64 * k] = sb[k];

@@ -42,8 +42,8 @@ __global__ void __launch_bounds__(128 * G, 1)
             x[k] = __ldg(pa + 64 * k) % p;                  // arbitrary u32 -> [0, p)
             y[k] = __ldg(pb + 64 * k) + p;                  // small signed -> [0, 2p)
         }
-        fwd16(x, bufA, bufB, s_tab, xa, T, q, p, bar);
-        fwd16(y, bufA, bufB, s_tab, xa, T, q, p, bar);
+        fwd16_2(x, y, bufA, bufB, s_tab, xa, T, q, p, bar, false);        // both operands together: 16 butterflies in flight
+        named_bar_sync(bar, 128);                           // its last loads were from both buffers; inv16 stores to bufA
 #pragma unroll
         for (int k = 0; k < 16; k++) {
             const int32_t m = umontmul_p(x[k], r2, p, pinv);                    // x R in (-p, p)
