@@ -34,7 +34,7 @@ KEY_BYTES_PER_GATE = 41_680_896            # NTT-domain bootstrapping key touche
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_blind_rotate16<4, 3> launch over 16384 gates
 # (profiles/r1_ncu_traffic_k_blind_rotate16_16384_v7.csv): keys once + ciphertext I/O, far below the
 # algorithmic key bytes because each key row is served to all gates from L2
-DRAM_TRAFFIC_PER_LAUNCH = 67_865_344 + 48_037_888
+DRAM_TRAFFIC_PER_LAUNCH = 67_176_704 + 47_980_032
 # integer multiply-pipe slots per gate of OUR formulation (DESIGN.md "integer roofline"): per CMUX step
 # and prime 6 transforms x 5120 Shoup butterflies x 4 slots, 2 x 1024 scale factors x 4, 8192 key
 # products at 3.5 slots (a row pair shares one Montgomery reduction: 7 per pair; 5 each before the
