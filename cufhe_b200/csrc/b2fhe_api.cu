@@ -44,6 +44,7 @@ int g_ks_lat_max_per_sm = 32;    // k_keyswitch_lat up to this many gates per SM
 int g_br_cluster_max = 70;       // k_blind_rotate_cl4 up to this many gates: 33 four-CTA clusters run one CTA per SM (1.63 ms), up to 70 two per SM (2.2 ms); beyond that k_blind_rotate_lat (3.5 ms) wins
 int g_br_burst_detect = 1;       // small calls arriving back to back use the throughput kernel
 constexpr int64_t kBurstGapNs = 300000;
+bool g_br_tail_split = true;     // last partial wave of k_blind_rotate16 as its own launch (b2fhe_set_br_variant(-1) / (-2) = off / on)
 int g_br_variant = 0;            // 0 = default, 1 = k_blind_rotate_lat, 2 = k_blind_rotate_cl, 16 = k_blind_rotate16, 32 = k_blind_rotate
 std::atomic<uint64_t> g_launches{0};
 thread_local std::string t_err;
@@ -239,6 +240,7 @@ int b2fhe_set_ks_variant(int variant)
 }
 int b2fhe_set_br_variant(int variant)
 {
+    if (variant == -1 || variant == -2) { g_br_tail_split = variant == -2; return 0; }
     REQUIRE(variant == 0 || variant == 1 || variant == 2 || variant == 4 || variant == 5 || variant == 16 || (variant >= 17 && variant <= 21) || variant == 32, B2FHE_E_BAD_ARGUMENT);
     g_br_variant = variant;
     return 0;

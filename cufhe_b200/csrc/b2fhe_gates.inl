@@ -13,7 +13,7 @@ template <int G> int launch_br_g(const BrParams& P, cudaStream_t st)
 }
 template <int G, int PAIR = 0> int launch_br16_g(const DevCtx& c, const BrParams& P, cudaStream_t st)
 {
-    const int grid = (P.count + G - 1) / G;
+    const int grid = (P.count - P.first + G - 1) / G;
     k_blind_rotate16<G, PAIR><<<grid, 128 * G, br16_smem_bytes(G), st>>>(P, c.tab16);
     LAUNCHED();
     return 0;
@@ -80,8 +80,25 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
             default: return launch_br16q_g<4>(c, P, st);
         }
     }
-    if (variant >= 17 && variant <= 20) {      // row-pair key multiply (17), + paired digit transforms (18): A/B against 16
+    if (variant >= 17 && variant <= 20) {      // row-pair key multiply (17), + paired digit transforms (18), + paired inverse (19, default), 4-row reduction (20)
         P.bk = c.bk_ntt16;
+        if (g == 0 && variant == 19 && g_br_tail_split) {
+            // Waves of 4 gates per SM take ~9 ms each whether full or not; a last partial wave of at
+            // most 3 gates per SM runs as its own launch with fewer gates per CTA (3 per SM: ~7 ms).
+            const int wave = 4 * c.sm_count;
+            const int full = (P.count / wave) * wave, rest = P.count - full;
+            if (full > 0 && rest > 0 && rest <= 3 * c.sm_count) {
+                BrParams M = P;
+                M.count = full;
+                if (int r = launch_br16_g<4, 3>(c, M, st)) return r;
+                P.first = full;
+                switch ((rest + c.sm_count - 1) / c.sm_count) {
+                    case 1: return launch_br16_g<1, 3>(c, P, st);
+                    case 2: return launch_br16_g<2, 3>(c, P, st);
+                    default: return launch_br16_g<3, 3>(c, P, st);
+                }
+            }
+        }
         if (g == 0) g = per_sm >= 4 ? 4 : per_sm >= 1 ? per_sm : 1;
         if (variant == 17) switch (g) {
             case 1: return launch_br16_g<1, 1>(c, P, st);

@@ -380,7 +380,7 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate16(const BrParams P,
 
     const int gs = threadIdx.x >> 7, t128 = threadIdx.x & 127;
     const int q = t128 >> 6, T = t128 & 63;
-    const int item = blockIdx.x * G + gs;
+    const int item = P.first + blockIdx.x * G + gs;
     if (item >= P.count) return;
 
     uint32_t* gbase = smem + kLane16TableWords + gs * kBr16GateSmemWords;

@@ -189,8 +189,12 @@ int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
  * CTA), 5 / 4 = k_blind_rotate_cl4 (one gate per cluster of 4 CTAs x 128 threads; hand-overs by
  * st.async + mbarrier / by cluster barriers), 2 =
  * k_blind_rotate_cl (first cluster design: 8 CTAs x 64 threads), 16 =
- * k_blind_rotate16 (128 threads x 16 coefficients per gate), 32 = k_blind_rotate (64 threads
- * x 32 coefficients per gate).  All produce identical bits. */
+ * k_blind_rotate16 (128 threads x 16 coefficients per gate, one TRGSW row at a time), 19 = its
+ * paired schedule (digit pairs and inverse pairs transformed together, one Montgomery reduction
+ * per row pair; what 0 selects for large batches), 17 / 18 / 20 = steps towards / beyond it kept
+ * for A/B, 21 = k_blind_rotate16q (paired, four exchange buffers per team), 32 = k_blind_rotate
+ * (64 threads x 32 coefficients per gate).  All produce identical bits.  -1 / -2 switch off / on
+ * the separate launch of a last partial wave (on by default; does not change the variant). */
 int b2fhe_set_br_variant(int variant);
 /* key-switch kernel: 0 = by batch size, 1 = k_keyswitch_lat (16 warps per gate), 2 = k_keyswitch */
 int b2fhe_set_ks_variant(int variant);

@@ -48,7 +48,7 @@ nchk = min(cnt, 1200)
 ref = torch.zeros((nchk, 1025), dtype=torch.int32, device="cuda")
 run(16, 4, nchk, ref)
 torch.cuda.synchronize()
-for variant in (19, 21):
+for variant in (19,):
     for g in (1, 2, 3, 4):
         got = torch.zeros_like(ref)
         run(variant, g, nchk, got)
@@ -57,11 +57,26 @@ for variant in (19, 21):
                           "equal": bool(torch.equal(ref, got))}), flush=True)
 
 e = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
-for variant, gs in ((16, (4,)), (19, (4,)), (21, (3, 4)), (16, (4,))):
+for variant, gs in ((16, (4,)), (19, (1, 2, 3, 4)),):
     for g in gs:
         best, med = timed(lambda: run(variant, g, cnt, e))
         print(json.dumps({"probe": "blind_rotate", "variant": variant, "gates_per_cta": g, "count": cnt, "ms_best": best,
                           "ms_med": med, "gates_per_s": cnt / best * 1e3}), flush=True)
+# default path (variant 0, gates per CTA 0) with and without the separate launch of the last partial wave
+for tail in (-1, -2, -1, -2):
+    cf._lib.check(L.b2fhe_set_br_variant(tail))
+    for n in (cnt, 592 * 5 + 100, 592 + 300):
+        best, med = timed(lambda: run(0, 0, n, e))
+        print(json.dumps({"probe": "blind_rotate_default", "tail_split": tail == -2, "count": n, "ms_best": best, "ms_med": med,
+                          "gates_per_s": n / best * 1e3}), flush=True)
+ref = torch.zeros((cnt, 1025), dtype=torch.int32, device="cuda")
+got = torch.zeros_like(ref)
+cf._lib.check(L.b2fhe_set_br_variant(-1))
+run(0, 0, cnt, ref)
+cf._lib.check(L.b2fhe_set_br_variant(-2))
+run(0, 0, cnt, got)
+torch.cuda.synchronize()
+print(json.dumps({"probe": "tail_split_bit_exact", "count": cnt, "equal": bool(torch.equal(ref, got))}), flush=True)
 cf._lib.check(L.b2fhe_set_br_variant(0))
 cf._lib.check(L.b2fhe_set_gates_per_cta(0))
 cf.CleanUp()

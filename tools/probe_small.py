@@ -35,9 +35,14 @@ e.random_()
 out = torch.empty_like(x0)
 for cnt in [int(a) for a in sys.argv[1:]] or [1, 8, 16, 24, 32, 37, 64, 148]:
     row = {"count": cnt}
-    for variant in (5, 4, 2, 1, 16):
+    for variant in (5, 4, 2, 1, 16, 19):
         cf._lib.check(L.b2fhe_set_br_variant(variant))
         row[f"br_v{variant}_ms"] = round(timed(lambda: cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, e.data_ptr(), x0.data_ptr(), 1 << 29, cnt))), 4)
+    cf._lib.check(L.b2fhe_set_br_variant(19))
+    for g in (1, 2):
+        cf._lib.check(L.b2fhe_set_gates_per_cta(g))
+        row[f"br_v19_g{g}_ms"] = round(timed(lambda: cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, e.data_ptr(), x0.data_ptr(), 1 << 29, cnt))), 4)
+    cf._lib.check(L.b2fhe_set_gates_per_cta(0))
     cf._lib.check(L.b2fhe_set_br_variant(0))
     row["br_auto_ms"] = round(timed(lambda: cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, e.data_ptr(), x0.data_ptr(), 1 << 29, cnt))), 4)
     for kv in (1, 2):
