@@ -136,6 +136,11 @@ int setup_device(int device)
     if (int r = set_br16_attr<4>()) return r;
     if (int r = set_br16_attr<5>()) return r;
     if (int r = set_br16_attr<6>()) return r;
+    CK(cudaFuncSetAttribute(k_keyswitch_step<32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
+    CK(cudaFuncSetAttribute(k_keyswitch_step<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
+    CK(cudaFuncSetAttribute(k_keyswitch_step<32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
+    CK(cudaFuncSetAttribute(k_keyswitch_step<32, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
+    CK(cudaFuncSetAttribute(k_keyswitch_step<32, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
     CK(cudaFuncSetAttribute(k_ntt_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
     CK(cudaFuncSetAttribute(k_ntt_inv, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
     CK(cudaFuncSetAttribute(k_polymul, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
@@ -234,7 +239,7 @@ int b2fhe_set_gates_per_cta(int gates)
 }
 int b2fhe_set_ks_variant(int variant)
 {
-    REQUIRE(variant >= 0 && variant <= 2, B2FHE_E_BAD_ARGUMENT);
+    REQUIRE((variant >= 0 && variant <= 2) || (variant >= 10 && variant <= 21), B2FHE_E_BAD_ARGUMENT);
     g_ks_variant = variant;
     return 0;
 }

@@ -163,6 +163,30 @@ int launch_ks(const DevCtx& c, KsParams P, cudaStream_t st)
         LAUNCHED();
         return 0;
     }
+    // in-step variants (A/B): 10 + (warps per CTA: 0 = 8, 1 = 16, 2 = 32) * 3 + (barrier every 1 / 2 / 4 coefficients)
+    if (g_ks_variant == 0) {      // measured fastest (profiles/r1_probe_v14_keyswitch_in_step.log): 32 gates per CTA, barrier every 4 coefficients
+        k_keyswitch_step<32, 4><<<(P.count + 31) / 32, 32 * 32, 32 * kN * 2, st>>>(P);
+        LAUNCHED();
+        return 0;
+    }
+    if (g_ks_variant >= 10 && g_ks_variant < 22) {
+#define KS_STEP(Wn, Sj) do { k_keyswitch_step<Wn, Sj><<<(P.count + Wn - 1) / Wn, 32 * Wn, Wn * kN * 2, st>>>(P); LAUNCHED(); return 0; } while (0)
+        switch (g_ks_variant) {
+            case 10: KS_STEP(8, 1);
+            case 11: KS_STEP(8, 2);
+            case 12: KS_STEP(8, 4);
+            case 13: KS_STEP(16, 1);
+            case 14: KS_STEP(16, 2);
+            case 15: KS_STEP(16, 4);
+            case 16: KS_STEP(32, 1);
+            case 17: KS_STEP(32, 2);
+            case 18: KS_STEP(32, 4);
+            case 19: KS_STEP(32, 8);
+            case 20: KS_STEP(32, 16);
+            default: KS_STEP(16, 8);
+        }
+#undef KS_STEP
+    }
     k_keyswitch<<<(P.count + kKsGates - 1) / kKsGates, 32 * kKsGates, 0, st>>>(P);
     LAUNCHED();
     return 0;

@@ -116,6 +116,70 @@ __global__ void __launch_bounds__(32 * kKsGates) k_keyswitch(const KsParams P)
     }
 }
 
+// Large-batch variant: W gates (warps) per CTA walk the 1024 mask coefficients IN STEP (a CTA
+// barrier every SYNCJ coefficients), so the key rows of the current coefficients -- 21 candidate
+// rows, 26.9 KB per coefficient, each wanted by W/4 of the warps on average -- are served to most
+// of them by the SM's L1 instead of by L2.  Only bits 31..18 of the shifted coefficient select
+// digits, so its upper half is staged (2 KB per gate).  Same sums as k_keyswitch.
+template <int W, int SYNCJ>
+__global__ void __launch_bounds__(32 * W) k_keyswitch_step(const KsParams P)
+{
+    extern __shared__ __align__(16) uint16_t s_th[];          // [W][1024]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int item_raw = blockIdx.x * W + warp;
+    const bool active = item_raw < P.count;
+    const int item = active ? item_raw : P.count - 1;           // idle warps of the last CTA keep the barriers company
+    KsItem it;
+    if (P.items) it = P.items[item];
+    else { it.s0 = it.s1 = it.slot = (uint32_t)item; it.ca = (int8_t)P.ca; it.cb = (int8_t)P.cb; it.off = P.off; }
+    const uint32_t* x0 = P.A + (size_t)it.s0 * (P.trlwe ? 2 * kN : kLvl1Words);
+    const uint32_t* x1 = (it.cb != 0 && P.B) ? P.B + (size_t)it.s1 * kLvl1Words : nullptr;
+    const uint32_t ca = (uint32_t)(int32_t)it.ca, cb = x1 ? (uint32_t)(int32_t)it.cb : 0u;
+    uint16_t* th = s_th + warp * kN;
+    for (int j = lane; j < kN; j += 32)
+        th[j] = (uint16_t)((ca * ks_operand(x0, j, P.trlwe) + (x1 ? cb * x1[j] : 0u) + kIksAdd) >> 16);
+    const uint32_t eb = ca * ks_operand(x0, kN, P.trlwe) + (x1 ? cb * x1[kN] : 0u) + it.off;
+    __syncthreads();
+
+    uint32_t accF[10], accH[10];
+#pragma unroll
+    for (int w = 0; w < 10; w++) accF[w] = accH[w] = 0u;
+    const uint32_t* Tl = P.T + lane;
+    for (int j0 = 0; j0 < kN; j0 += SYNCJ) {
+        if (active) {
+#pragma unroll
+            for (int jj = 0; jj < SYNCJ; jj++) {
+                const int j = j0 + jj;
+                const uint32_t tj = (uint32_t)th[j] << 16;
+#pragma unroll
+                for (int d = 0; d < kIksT; d++) {
+                    const uint32_t dg = iks_digit(tj, d);
+                    if (dg != 2u) {
+                        const uint32_t* row = Tl + ((size_t)(j * kIksT + d) * 3 + min(dg, 2u)) * kKsRowWords;
+#pragma unroll
+                        for (int w = 0; w < 10; w++) {
+                            const uint32_t v = __ldg(row + 32 * w);
+                            accF[w] += v;
+                            accH[w] += v >> 16;
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+    if (!active) return;
+    uint16_t* out = P.out + (size_t)it.slot * kLvl0Words;
+#pragma unroll
+    for (int w = 0; w < 10; w++) {
+        const int c0 = 2 * (lane + 32 * w);
+        if (c0 < kLwe) out[c0] = (uint16_t)accF[w];
+        else if (c0 == kLwe) out[c0] = (uint16_t)(accF[w] + iks_round_b(eb));
+        if (c0 + 1 < kLwe) out[c0 + 1] = (uint16_t)accH[w];
+        else if (c0 + 1 == kLwe) out[c0 + 1] = (uint16_t)(accH[w] + iks_round_b(eb));
+    }
+}
+
 // Small-batch variant: one CTA of 16 warps per gate; warp w walks j in [64 w, 64 w + 64),
 // then the 16 partial sums are added through shared memory.  Same arithmetic (mod 2^16
 // per column), ~16x shorter critical path: 1.9 ms -> ~0.15 ms for a single gate.

@@ -124,7 +124,7 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     dx = dev_u32(x)
     dks = torch.empty((cnt, 637), dtype=torch.int16, device="cuda")
     want = [orc.keyswitch(keys, x[i]) for i in range(cnt)]
-    for ks_variant in (1, 2, 0):        # 16 warps per gate / one warp per gate / by batch size
+    for ks_variant in (1, 2, 10, 11, 12, 13, 14, 15, 16, 17, 18, 0):   # 16 warps per gate / one warp per gate / in-step CTAs (W x SYNCJ) / by batch size
         cf._lib.check(L.b2fhe_set_ks_variant(ks_variant))
         dks.zero_()
         cf._lib.check(L.b2fhe_keyswitch_batch(0, None, dks.data_ptr(), dx.data_ptr(), cnt))
