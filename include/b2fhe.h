@@ -197,10 +197,10 @@ int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
  * the separate launch of a last partial wave (on by default; does not change the variant). */
 int b2fhe_set_br_variant(int variant);
 /* key-switch kernel: 0 = by batch size (k_keyswitch_lat up to 32 gates per SM, else
- * k_keyswitch_step<32, 4>), 1 = k_keyswitch_lat (16 warps per gate), 2 = k_keyswitch (one
+ * k_keyswitch_step<16, 8>), 1 = k_keyswitch_lat (16 warps per gate), 2 = k_keyswitch (one
  * free-running warp per gate), 10..18 = k_keyswitch_step<W, SYNCJ> with W = 8 / 16 / 32 gates per
- * CTA walking the mask in step, a barrier every SYNCJ = 1 / 2 / 4 coefficients (10 + 3 iW + iS).
- * All produce identical bits. */
+ * CTA walking the mask in step, a barrier every SYNCJ = 1 / 2 / 4 coefficients (10 + 3 iW + iS),
+ * 19 / 20 / 21 = <32, 8> / <32, 16> / <16, 8>.  All produce identical bits. */
 int b2fhe_set_ks_variant(int variant);
 uint64_t b2fhe_kernel_launches(void);             /* kernels launched by this library so far */
 /* measured integer-pipe ceiling of `device` (register-only probe kernel): mode 0 = 1e9

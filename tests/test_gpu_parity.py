@@ -334,3 +334,41 @@ def test_cluster_kernel_stress_against_throughput_kernel(engine):
                     assert torch.equal(got, want), (cnt, variant, rep)
     finally:
         cf._lib.check(L.b2fhe_set_br_variant(0))
+
+
+@pytest.mark.gpu
+def test_default_large_batch_paths_against_single_row_kernel(engine):
+    """The default large-batch path = paired k_blind_rotate16<4, 3> in full waves + a separate launch
+    (fewer gates per CTA) for a last partial wave, then k_keyswitch_step<32, 4>.  Batch sizes around
+    the wave boundaries (one gate over, one SM over, just below the no-split threshold, idle warps in
+    the last key-switch CTA) must reproduce the bits of the first-generation kernels
+    (k_blind_rotate16<4, 0>, k_keyswitch), with and without the split."""
+    cf = engine
+    L = cf._lib.lib()
+    rng = np.random.default_rng(99)
+    sm = torch.cuda.get_device_properties(0).multi_processor_count
+    wave = 4 * sm
+    try:
+        for cnt in (wave + 1, wave + sm + 1, wave + 3 * sm, wave + 3 * sm + 1, 2 * wave, 2 * wave - 5):
+            x = torch.from_numpy(rng.integers(0, 2**16, (cnt, 637), dtype=np.uint64).astype(np.uint16).view(np.int16)).cuda()
+            want = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
+            wks = torch.empty((cnt, 637), dtype=torch.int16, device="cuda")
+            cf._lib.check(L.b2fhe_set_br_variant(16))
+            cf._lib.check(L.b2fhe_set_ks_variant(2))
+            cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, want.data_ptr(), x.data_ptr(), 1 << 29, cnt))
+            cf._lib.check(L.b2fhe_keyswitch_batch(0, None, wks.data_ptr(), want.data_ptr(), cnt))
+            cf._lib.check(L.b2fhe_set_br_variant(0))
+            cf._lib.check(L.b2fhe_set_ks_variant(0))
+            for split in (-2, -1):
+                cf._lib.check(L.b2fhe_set_br_variant(split))
+                got = torch.zeros_like(want)
+                gks = torch.zeros_like(wks)
+                cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, got.data_ptr(), x.data_ptr(), 1 << 29, cnt))
+                cf._lib.check(L.b2fhe_keyswitch_batch(0, None, gks.data_ptr(), got.data_ptr(), cnt))
+                torch.cuda.synchronize()
+                assert torch.equal(got, want), (cnt, split)
+                assert torch.equal(gks, wks), (cnt, split)
+    finally:
+        cf._lib.check(L.b2fhe_set_br_variant(-2))
+        cf._lib.check(L.b2fhe_set_br_variant(0))
+        cf._lib.check(L.b2fhe_set_ks_variant(0))
