@@ -92,14 +92,12 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
                 M.count = full;
                 if (int r = launch_br16_g<4, 3>(c, M, st)) return r;
                 P.first = full;
-                switch ((rest + c.sm_count - 1) / c.sm_count) {
-                    case 1: return launch_br16_g<1, 3>(c, P, st);
-                    case 2: return launch_br16_g<2, 3>(c, P, st);
-                    default: return launch_br16_g<3, 3>(c, P, st);
-                }
+                // 1 or 2 gates per SM: one-gate CTAs (two fit an SM; 5.2 ms vs 5.4 ms for a two-gate CTA)
+                if (rest <= 2 * c.sm_count) return launch_br16_g<1, 3>(c, P, st);
+                return launch_br16_g<3, 3>(c, P, st);
             }
         }
-        if (g == 0) g = per_sm >= 4 ? 4 : per_sm >= 1 ? per_sm : 1;
+        if (g == 0) g = per_sm >= 4 ? 4 : per_sm == 3 ? 3 : 1;      // two one-gate CTAs share an SM faster than one two-gate CTA
         if (variant == 17) switch (g) {
             case 1: return launch_br16_g<1, 1>(c, P, st);
             case 2: return launch_br16_g<2, 1>(c, P, st);

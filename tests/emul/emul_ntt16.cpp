@@ -202,6 +202,32 @@ static int check_digit_pass(std::mt19937_64& rng)
     return bad;
 }
 
+// row-pair / four-row key multiply (umontmul2_p, umontmul4_p: one Montgomery reduction for the
+// 64-bit sum) == the sum of the single products, as residues, and inside the stated bounds
+static int check_pair_mac(std::mt19937_64& rng)
+{
+    int bad = 0;
+    for (int it = 0; it < 200000; it++) {
+        const int q = it & 1;
+        const uint32_t p = kP[q], pinv = q ? Prime<1>::pinv : Prime<0>::pinv;
+        uint32_t a[4], b[4];
+        for (int i = 0; i < 4; i++) {
+            a[i] = it < 16 ? 0xFFFFFFFFu : (uint32_t)rng();              // any lazy 32-bit residue
+            b[i] = it < 16 ? p - 1 : (uint32_t)(rng() % p);             // key word in Montgomery form
+        }
+        int64_t one = 0, two = 0;
+        for (int i = 0; i < 4; i++) {
+            one += umontmul_p(a[i], b[i], p, pinv);
+            if (i < 2) two += umontmul_p(a[i], b[i], p, pinv);
+        }
+        const int32_t r2 = (int32_t)umontmul2_p(a[0], b[0], a[1], b[1], p, pinv);
+        const int32_t r4 = (int32_t)umontmul4_p(a[0], b[0], a[1], b[1], a[2], b[2], a[3], b[3], p, pinv);
+        if (((int64_t)r2 - two) % (int64_t)p != 0 || r2 <= -(int32_t)p || r2 >= 2 * (int32_t)p) bad++;
+        if (((int64_t)r4 - one) % (int64_t)p != 0 || r4 <= -(int32_t)p || r4 >= 4 * (int32_t)p) bad++;
+    }
+    return bad;
+}
+
 int main(int argc, char** argv)
 {
     make_tables(T);
@@ -217,6 +243,8 @@ int main(int argc, char** argv)
     printf("polymul mismatches: %d / %d\n", bad, trials);
     for (int i = 0; i < trials; i++) bad2 += check_cmux(rng);
     printf("cmux mismatches: %d / %d\n", bad2, trials);
+    const int bad4 = check_pair_mac(rng);
+    printf("pair / four-row multiply mismatches: %d\n", bad4);
     printf("bank conflicts: %d\n", g_conflicts);
-    return (bad0 || bad || bad2 || bad3 || g_conflicts) ? 1 : 0;
+    return (bad0 || bad || bad2 || bad3 || bad4 || g_conflicts) ? 1 : 0;
 }

@@ -137,6 +137,7 @@ def test_team_emulation_of_16_coefficient_ntt_and_cmux(tmp_path):
     assert "position mismatches vs 32-coefficient transform: 0" in out
     assert "digit look-up pass mismatches: 0" in out
     assert "polymul mismatches: 0 / 6" in out and "cmux mismatches: 0 / 6" in out
+    assert "pair / four-row multiply mismatches: 0" in out        # umontmul2_p / umontmul4_p of the paired kernels
     assert "bank conflicts: 0" in out
 
 
