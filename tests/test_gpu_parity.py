@@ -247,6 +247,33 @@ def test_mixed_batch(engine, keys, level):
     assert list(dec) == [orc.truth(ops[i], b[0][i], b[1][i], b[2][i]) for i in range(cnt)]
 
 
+@pytest.mark.parametrize("level,cnt", [(0, 14 * 45), (1, 14 * 64)])
+def test_mixed_batch_across_waves(engine, keys, level, cnt):
+    """A mixed batch whose blind-rotation work items (cnt of them: Mux/NMux count twice, Not/Copy not
+    at all) fill one wave of 4 gates per SM on a B200 plus a partial one, so the per-item lists go
+    through the separate launch of the last partial wave (one-gate CTAs for 630, three-gate CTAs
+    for 896) and the in-step key switch: every gate decrypts right, a strided sample matches the
+    oracle's bytes."""
+    cf = engine
+    rng = np.random.default_rng(17 + level)
+    ops = (np.arange(cnt) % 14).astype(np.uint8)
+    b = [rng.integers(0, 2, cnt) for _ in range(3)]
+    x = [orc.encrypt(keys, b[k], level, base_index=70000 + 2000 * k) for k in range(3)]
+    st = cf.Stream(0).Create()
+    cts = [cf.Ctxt(cnt, level).set(v) for v in x]
+    out = cf.Ctxt(cnt, level)
+    for c in cts:
+        cf.CtxtCopyH2D(c, st)
+    cf.gGateMixed(ops, out, cts[0], cts[1], cts[2], st)
+    cf.CtxtCopyD2H(out, st)
+    cf.Synchronize()
+    dec = orc.decrypt(keys, out.tlwehost, level)
+    assert list(dec) == [orc.truth(ops[i], b[0][i], b[1][i], b[2][i]) for i in range(cnt)]
+    idx = np.concatenate([np.arange(0, cnt, 23), np.arange(cnt - 14, cnt)])
+    ref = orc.gate_batch(keys, 0, level, x[0][idx], x[1][idx], x[2][idx], ops=ops[idx])
+    assert np.array_equal(out.tlwehost[idx], ref)
+
+
 def test_aliasing_and_stream_chain(engine, keys):
     """out may alias an input; gates on one stream run in issue order
     (test/test_intensive.cc:21-54: 20 back-to-back NANDs per stream)."""
