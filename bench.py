@@ -261,7 +261,7 @@ def run_product(args):
             "clocks": summarize_clocks(samples),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved / hbm_peak, "traffic": DRAM_TRAFFIC_PER_LAUNCH if cnt == GATES_PER_GPU else None,
-                         "kernel": "k_blind_rotate16<4, 3>", "kernel_ms": br_s * 1e3,
+                         "kernel": "k_blind_rotate16<4, 3> (+ its <3, 3> launch for the last partial wave)", "kernel_ms": br_s * 1e3,
                          "note": "algorithmic key bytes (41.68 MB x gates per launch) / kernel time, against the "
                                  "MEASURED HBM copy peak; the batch-major kernel serves each key row to all gates of "
                                  "a CTA from L1/L2, so this exceeds 1 by design -- the binding resource is the "
