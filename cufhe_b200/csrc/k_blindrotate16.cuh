@@ -18,6 +18,15 @@
 // then the teams swap one residue polynomial, each finishes the centred CRT of one output
 // polynomial and updates the accumulator.  All synchronisation is the gate's own
 // 128-thread named barrier (14 per step); gates of a CTA never wait for each other.
+//
+// Template parameter PAIR selects the schedule of those four phases (identical bits):
+//   0  one TRGSW row at a time, as listed above (first version; b2fhe_set_br_variant(16));
+//   3  the DEFAULT: the two digits of an accumulator polynomial are transformed together
+//      (fwd16_digits2: one through exchange buffer A, one through B -- 16 independent butterflies
+//      per stage per thread, twiddles fetched once), their two key rows share ONE Montgomery
+//      reduction (umontmul2_p), and the two inverse transforms run together (inv16_2);
+//   1, 2 intermediate steps, 4 = all four rows in one reduction (four transformed polynomials
+//      live at once: spills at 128 registers) -- kept for A/B, see DESIGN.md 4.1.
 #pragma once
 #include "k_blindrotate.cuh"
 #include "ntt16.cuh"
