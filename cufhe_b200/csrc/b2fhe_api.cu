@@ -13,6 +13,7 @@
 #include "k_blindrotate.cuh"
 #include "k_blindrotate16.cuh"
 #include "k_blindrotate16q.cuh"
+#include "k_blindrotate_s.cuh"
 #include "k_blindrotate_lat.cuh"
 #include "k_blindrotate_cl.cuh"
 #include "k_blindrotate_cl4.cuh"
@@ -34,6 +35,7 @@ struct DevCtx {
     LaneTables* tab = nullptr;
     uint32_t* bk_ntt16 = nullptr;   // same key in bk16_slot order (k_blind_rotate16), built lazily
     Lane16Tables* tab16 = nullptr;
+    TeamSTables* tabs = nullptr;    // second-generation tables (k_blind_rotate_s)
     int sm_count = 0;
 };
 DevCtx g_ctx[kMaxDev];
@@ -86,6 +88,20 @@ template <int G> int set_br16_attr()
     return 0;
 }
 
+// Solinas masks of the k_blind_rotate_s variants 40 + m (A/B of which passes put q*p on the ALU pipe)
+template <int G, int M> int set_brs_attr1()
+{
+    CK(cudaFuncSetAttribute(k_blind_rotate_s<G, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(G)));
+    return 0;
+}
+template <int M> int set_brs_attr()
+{
+    if (int r = set_brs_attr1<1, M>()) return r;
+    if (int r = set_brs_attr1<2, M>()) return r;
+    if (int r = set_brs_attr1<3, M>()) return r;
+    return set_brs_attr1<4, M>();
+}
+
 // twiddle tables + kernel attributes on `device` (InitializeNTThandlers, src/bootstrap_gpu.cu:97-109)
 int setup_device(int device)
 {
@@ -112,6 +128,12 @@ int setup_device(int device)
     make_tables16(L16);
     CK(cudaMalloc(&c.tab16, sizeof(Lane16Tables)));
     CK(cudaMemcpy(c.tab16, &L16, sizeof L16, cudaMemcpyHostToDevice));
+    static TeamSTables LS;
+    static TeamSConst CS;
+    make_tables16s(LS, CS);
+    CK(cudaMemcpyToSymbol(c_s, &CS, sizeof CS));
+    CK(cudaMalloc(&c.tabs, sizeof(TeamSTables)));
+    CK(cudaMemcpy(c.tabs, &LS, sizeof LS, cudaMemcpyHostToDevice));
     CK(cudaDeviceGetAttribute(&c.sm_count, cudaDevAttrMultiProcessorCount, device));
     // keep stream-ordered scratch cached between calls
     cudaMemPool_t pool;
@@ -130,6 +152,15 @@ int setup_device(int device)
     CK(cudaFuncSetAttribute(k_cmux16<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(1)));
     CK(cudaFuncSetAttribute(k_cmux16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(4)));
     CK(cudaFuncSetAttribute(k_polymul16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, polymul16_smem_bytes(4)));
+    if (int r = set_brs_attr<0>()) return r;
+    if (int r = set_brs_attr<1>()) return r;
+    if (int r = set_brs_attr<2>()) return r;
+    if (int r = set_brs_attr<3>()) return r;
+    if (int r = set_brs_attr<24>()) return r;
+    if (int r = set_brs_attr<27>()) return r;
+    if (int r = set_brs_attr<59>()) return r;
+    if (int r = set_brs_attr<63>()) return r;
+    CK(cudaFuncSetAttribute(k_blind_rotate_s<4, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(4)));
     if (int r = set_br16_attr<1>()) return r;
     if (int r = set_br16_attr<2>()) return r;
     if (int r = set_br16_attr<3>()) return r;
@@ -246,7 +277,7 @@ int b2fhe_set_ks_variant(int variant)
 int b2fhe_set_br_variant(int variant)
 {
     if (variant == -1 || variant == -2) { g_br_tail_split = variant == -2; return 0; }
-    REQUIRE(variant == 0 || variant == 1 || variant == 2 || variant == 4 || variant == 5 || variant == 16 || (variant >= 17 && variant <= 21) || variant == 32, B2FHE_E_BAD_ARGUMENT);
+    REQUIRE(variant == 0 || variant == 1 || variant == 2 || variant == 4 || variant == 5 || variant == 16 || (variant >= 17 && variant <= 21) || variant == 32 || (variant >= 40 && variant <= 48), B2FHE_E_BAD_ARGUMENT);
     g_br_variant = variant;
     return 0;
 }
@@ -315,6 +346,7 @@ int b2fhe_cleanup(void)
         if (c.owns_keys) { CK(cudaFree(c.bk_ntt)); CK(cudaFree(c.ksk)); }
         if (c.tab) CK(cudaFree(c.tab));
         if (c.tab16) CK(cudaFree(c.tab16));
+        if (c.tabs) CK(cudaFree(c.tabs));
         if (c.bk_ntt16) CK(cudaFree(c.bk_ntt16));
         c = DevCtx();
     }

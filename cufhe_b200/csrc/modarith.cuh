@@ -41,12 +41,12 @@ constexpr uint32_t inv32(uint32_t p)
 
 template <int Q> struct Prime;
 template <> struct Prime<0> {
-    static constexpr uint32_t p = 134215681u;           // 65535 * 2048 + 1
+    static constexpr uint32_t p = 134215681u;           // 65535 * 2048 + 1 = 2^27 - 2^11 + 1
     static constexpr uint32_t pinv = inv32(134215681u);
 };
 template <> struct Prime<1> {
-    static constexpr uint32_t p = 134203393u;           // 65529 * 2048 + 1
-    static constexpr uint32_t pinv = inv32(134203393u);
+    static constexpr uint32_t p = 132120577u;           // 63 * 2^21 + 1 = 2^27 - 2^21 + 1
+    static constexpr uint32_t pinv = inv32(132120577u);
 };
 constexpr uint32_t kP[2] = {Prime<0>::p, Prime<1>::p};
 

@@ -161,7 +161,7 @@ B2_HD void pass16_fwd3(uint32_t (&x)[16], const Tw* tw, const int stride, const 
     for (int k = 0; k < 16; k += 2) butterfly_p(x[k], x[k + 1], tw[(4 + (k >> 1)) * stride], p, p2);
 }
 
-// reduction of any 32-bit lazy residue into [0, 2p): v - (v >> 27) p  (p > 2^27 - 2^14)
+// reduction of any 32-bit lazy residue into [0, 2p): v - (v >> 27) p  (needs 31 (2^27 - p) < 2p - 2^27; both primes are 2^27 - 2^k + 1, k <= 21)
 B2_HD uint32_t lazy_reduce(uint32_t v, uint32_t p) { return v - (v >> 27) * p; }
 
 // inverse sub-strides 1, 2, 4, 8; twiddle index (2^u - 1) + (k mod tp).  UNIT: twiddle
