@@ -44,7 +44,8 @@ struct BrParams {
     int ca, cb, off;        // uniform coefficients
     uint32_t mu;            // test-vector constant (lvl1param::mu)
     int trlwe;              // 0: out[slot] = SampleExtract(0) (1025 words); 1: out[slot] = the TRLWE (2 x 1024 words)
-    int first;              // k_blind_rotate16 only: this launch covers items first .. count-1
+    int first;              // k_blind_rotate16 / _s only: this launch covers items first .. count-1
+    uint32_t dbg;           // always 0 in the product; tools/ablate_brs.cu uses it as an opaque zero
 };
 
 constexpr int kBrGateSmemWords = 2 * kN + 2 * kN + 640 / 2;   // acc + 2 exchange buffers + abar(u16)

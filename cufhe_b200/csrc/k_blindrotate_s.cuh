@@ -29,6 +29,15 @@ constexpr int kBrsGateSmemWords = 2 * kN + 4 * kXsWords + 640 / 2;      // acc +
 __host__ __device__ constexpr int brs_smem_bytes(int gates) { return (kTeamSTableWords + gates * kBrsGateSmemWords) * 4; }
 
 enum : int { SOL_F2 = 1, SOL_F3 = 2, SOL_I1 = 4, SOL_I2 = 8, SOL_I3 = 16, SOL_SC = 32 };
+// timing ablations (tools/ablate_brs.cu only; results are WRONG with any of them set): what does each
+// component of a CMUX step cost on the real machine?
+enum : int { ABL_LUT = 1,      // table look-ups at conflict-free (lane) indices
+             ABL_DIG = 2,      // no rotation / decomposition (one accumulator load per coefficient remains)
+             ABL_KEY = 4,      // no key loads (register constants)
+             ABL_BAR = 8,      // no named barriers / __syncwarp
+             ABL_XCH = 16,     // no shared-memory exchanges
+             ABL_FMA = 32,     // butterflies and key products without multiplies
+             ABL_TWD = 64 };   // twiddles from registers (no table loads)
 
 // smem image of TeamSTables: per-T vectors f3 | i3 | sc are addressed from ONE pointer
 // (vector v of pass X at tbT[64 (off_X + v)]) -- they are NOT adjacent in the struct, so the kernel
@@ -63,98 +72,168 @@ __device__ __forceinline__ void ld_own(int32_t (&x)[16], const int32_t* own)
     }
 }
 
-// two digit polynomials (raw digits, layout A) -> NTT domain (layout C)
-template <int SOLM>
-__device__ __forceinline__ void sfwd2_dev(int32_t (&x0)[16], int32_t (&x1)[16], const SPtr& a, const int32_t p, const int sk,
-                                          const int tbar, const bool lead)
+template <int ABL> __device__ __forceinline__ void tbar_sync(int id, int n) { if (!(ABL & ABL_BAR)) named_bar_sync(id, n); }
+template <int ABL> __device__ __forceinline__ void warp_sync() { if (!(ABL & ABL_BAR)) __syncwarp(); }
+// ablation stand-ins: same data flow, no multiplies
+__device__ __forceinline__ void abfly(int32_t& u, int32_t& v, const Tws t)
 {
+    const int32_t r = v ^ t.w, a = u;
+    u = a + r;
+    v = a - (r ^ t.ws);
+}
+template <int N>
+__device__ __forceinline__ void load_tw(V4 (&tv)[N], const V4* src, const int stride, const bool fake, const int32_t p, const int T)
+{
+#pragma unroll
+    for (int v = 0; v < N; v++) tv[v] = fake ? V4{p ^ v, T + v, p - v, T ^ v} : src[stride * v];
+}
+
+// two digit polynomials (raw digits, layout A) -> NTT domain (layout C)
+template <int SOLM, int ABL>
+__device__ __forceinline__ void sfwd2_dev(int32_t (&x0)[16], int32_t (&x1)[16], const SPtr& a, const int32_t p, const int sk,
+                                          const int tbar, const bool lead, const int T, const uint32_t dbg)
+{
+    if (ABL & ABL_LUT) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            x0[k] = (x0[k] & (int32_t)dbg) | (T & 31) | ((k & 7) << 5);
+            x1[k] = (x1[k] & (int32_t)dbg) | (T & 31) | (((k + 3) & 7) << 5);
+        }
+    }
     spass_digits(x0, a.lut, a.lut24, a.lut35);
     spass_digits(x1, a.lut, a.lut24, a.lut35);
-    if (lead) named_bar_sync(tbar, 64);          // owners have read their chunks (previous D->C)
+    if (lead) tbar_sync<ABL>(tbar, 64);          // owners have read their chunks (previous D->C)
+    if (!(ABL & ABL_XCH)) {
 #pragma unroll
-    for (int kh = 0; kh < 4; kh++) {
-        *reinterpret_cast<V4*>(a.vw + 336 * kh) = V4{x0[4 * kh], x0[4 * kh + 1], x0[4 * kh + 2], x0[4 * kh + 3]};
-        *reinterpret_cast<V4*>(a.vw + kXsWords + 336 * kh) = V4{x1[4 * kh], x1[4 * kh + 1], x1[4 * kh + 2], x1[4 * kh + 3]};
+        for (int kh = 0; kh < 4; kh++) {
+            *reinterpret_cast<V4*>(a.vw + 336 * kh) = V4{x0[4 * kh], x0[4 * kh + 1], x0[4 * kh + 2], x0[4 * kh + 3]};
+            *reinterpret_cast<V4*>(a.vw + kXsWords + 336 * kh) = V4{x1[4 * kh], x1[4 * kh + 1], x1[4 * kh + 2], x1[4 * kh + 3]};
+        }
     }
-    named_bar_sync(tbar, 64);
+    tbar_sync<ABL>(tbar, 64);
+    if (!(ABL & ABL_XCH)) {
 #pragma unroll
-    for (int th = 0; th < 4; th++) {
-        const V4 r0 = *reinterpret_cast<const V4*>(a.own + 4 * th);
-        const V4 r1 = *reinterpret_cast<const V4*>(a.own + kXsWords + 4 * th);
-        x0[th] = r0.x; x0[th + 4] = r0.y; x0[th + 8] = r0.z; x0[th + 12] = r0.w;
-        x1[th] = r1.x; x1[th + 4] = r1.y; x1[th + 8] = r1.z; x1[th + 12] = r1.w;
+        for (int th = 0; th < 4; th++) {
+            const V4 r0 = *reinterpret_cast<const V4*>(a.own + 4 * th);
+            const V4 r1 = *reinterpret_cast<const V4*>(a.own + kXsWords + 4 * th);
+            x0[th] = r0.x; x0[th + 4] = r0.y; x0[th + 8] = r0.z; x0[th + 12] = r0.w;
+            x1[th] = r1.x; x1[th + 4] = r1.y; x1[th + 8] = r1.z; x1[th + 12] = r1.w;
+        }
     }
     {
         V4 tv[8];
+        load_tw(tv, a.f2, 1, (ABL & ABL_TWD) != 0, p, T);
+        if (ABL & ABL_FMA) {
 #pragma unroll
-        for (int v = 0; v < 8; v++) tv[v] = a.f2[v];
-        spass_fwd2<(SOLM & SOL_F2) != 0>(x0, x1, tv, p, sk);
+            for (int s = 0; s < 4; s++)
+#pragma unroll
+                for (int k = 0; k < 16; k++)
+                    if ((k & (8 >> s)) == 0) { const Tws t = tws_of(tv, (1 << s) - 1 + k / (16 >> s)); abfly(x0[k], x0[k + (8 >> s)], t); abfly(x1[k], x1[k + (8 >> s)], t); }
+        } else spass_fwd2<(SOLM & SOL_F2) != 0>(x0, x1, tv, p, sk);
     }
-    __syncwarp();                                // group mates have read their chunks
+    warp_sync<ABL>();                            // group mates have read their chunks
+    if (!(ABL & ABL_XCH)) {
 #pragma unroll
-    for (int k = 0; k < 16; k++) { a.sw[20 * k] = x0[k]; a.sw[kXsWords + 20 * k] = x1[k]; }
-    __syncwarp();
-    ld_own(x0, a.own);
-    ld_own(x1, a.own + kXsWords);
+        for (int k = 0; k < 16; k++) { a.sw[20 * k] = x0[k]; a.sw[kXsWords + 20 * k] = x1[k]; }
+    }
+    warp_sync<ABL>();
+    if (!(ABL & ABL_XCH)) {
+        ld_own(x0, a.own);
+        ld_own(x1, a.own + kXsWords);
+    }
     {
         V4 tv[8];
+        load_tw(tv, a.f3, 64, (ABL & ABL_TWD) != 0, p, T);
+        if (ABL & ABL_FMA) {
 #pragma unroll
-        for (int v = 0; v < 8; v++) tv[v] = a.f3[64 * v];
-        spass_fwd2<(SOLM & SOL_F3) != 0>(x0, x1, tv, p, sk);
+            for (int s = 0; s < 4; s++)
+#pragma unroll
+                for (int k = 0; k < 16; k++)
+                    if ((k & (8 >> s)) == 0) { const Tws t = tws_of(tv, (1 << s) - 1 + k / (16 >> s)); abfly(x0[k], x0[k + (8 >> s)], t); abfly(x1[k], x1[k + (8 >> s)], t); }
+        } else spass_fwd2<(SOLM & SOL_F3) != 0>(x0, x1, tv, p, sk);
     }
 }
 
 // two inverse transforms incl. n^-1 psi^-e: layout C in, layout A out, values in [-p/4, 5p/4)
-template <int SOLM>
+template <int SOLM, int ABL>
 __device__ __forceinline__ void sinv2_dev(int32_t (&x0)[16], int32_t (&x1)[16], const SPtr& a, const int q, const int32_t p,
-                                          const int sk, const int tbar)
+                                          const int sk, const int tbar, const int T)
 {
-    {
+    if (ABL & ABL_FMA) {
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+#pragma unroll
+            for (int k = 0; k < 16; k++)
+                if ((k & (1 << u)) == 0) { const Tws t = Tws{p + u, k}; abfly(x0[k], x0[k + (1 << u)], t); abfly(x1[k], x1[k + (1 << u)], t); }
+    } else {
         const Tws* c1 = c_s.iv1[q];
         auto tw = [&](int i) { return c1[i]; };
         spass_inv<(SOLM & SOL_I1) != 0, true>(x0, tw, p, sk);
         spass_inv<(SOLM & SOL_I1) != 0, true>(x1, tw, p, sk);
     }
-    __syncwarp();                                // group mates' last loads of their chunks (forward D->C)
+    warp_sync<ABL>();                            // group mates' last loads of their chunks (forward D->C)
+    if (!(ABL & ABL_XCH)) {
 #pragma unroll
-    for (int k = 0; k < 16; k++) { a.sw[20 * k] = x0[k]; a.sw[kXsWords + 20 * k] = x1[k]; }
-    __syncwarp();
-    ld_own(x0, a.own);
-    ld_own(x1, a.own + kXsWords);
+        for (int k = 0; k < 16; k++) { a.sw[20 * k] = x0[k]; a.sw[kXsWords + 20 * k] = x1[k]; }
+    }
+    warp_sync<ABL>();
+    if (!(ABL & ABL_XCH)) {
+        ld_own(x0, a.own);
+        ld_own(x1, a.own + kXsWords);
+    }
     {
         V4 tv[8];
+        load_tw(tv, a.i2, 16, (ABL & ABL_TWD) != 0, p, T);
+        if (ABL & ABL_FMA) {
 #pragma unroll
-        for (int v = 0; v < 8; v++) tv[v] = a.i2[16 * v];
-        auto tw = [&](int i) { return tws_of(tv, i); };
-        spass_inv<(SOLM & SOL_I2) != 0, false>(x0, tw, p, sk);
-        spass_inv<(SOLM & SOL_I2) != 0, false>(x1, tw, p, sk);
-    }
-    named_bar_sync(tbar, 64);                    // every owner has read its chunk
+            for (int u = 0; u < 4; u++)
 #pragma unroll
-    for (int kl = 0; kl < 4; kl++) {
-        *reinterpret_cast<V4*>(a.vw + 336 * kl) = V4{x0[kl], x0[kl + 4], x0[kl + 8], x0[kl + 12]};
-        *reinterpret_cast<V4*>(a.vw + kXsWords + 336 * kl) = V4{x1[kl], x1[kl + 4], x1[kl + 8], x1[kl + 12]};
+                for (int k = 0; k < 16; k++)
+                    if ((k & (1 << u)) == 0) { const Tws t = tws_of(tv, (1 << u) - 1 + (k & ((1 << u) - 1))); abfly(x0[k], x0[k + (1 << u)], t); abfly(x1[k], x1[k + (1 << u)], t); }
+        } else {
+            auto tw = [&](int i) { return tws_of(tv, i); };
+            spass_inv<(SOLM & SOL_I2) != 0, false>(x0, tw, p, sk);
+            spass_inv<(SOLM & SOL_I2) != 0, false>(x1, tw, p, sk);
+        }
     }
-    named_bar_sync(tbar, 64);
-    ld_own(x0, a.own);
-    ld_own(x1, a.own + kXsWords);
+    tbar_sync<ABL>(tbar, 64);                    // every owner has read its chunk
+    if (!(ABL & ABL_XCH)) {
+#pragma unroll
+        for (int kl = 0; kl < 4; kl++) {
+            *reinterpret_cast<V4*>(a.vw + 336 * kl) = V4{x0[kl], x0[kl + 4], x0[kl + 8], x0[kl + 12]};
+            *reinterpret_cast<V4*>(a.vw + kXsWords + 336 * kl) = V4{x1[kl], x1[kl + 4], x1[kl + 8], x1[kl + 12]};
+        }
+    }
+    tbar_sync<ABL>(tbar, 64);
+    if (!(ABL & ABL_XCH)) {
+        ld_own(x0, a.own);
+        ld_own(x1, a.own + kXsWords);
+    }
     {
         V4 tv[6], sv[8];
+        load_tw(tv, a.i3, 64, (ABL & ABL_TWD) != 0, p, T);
+        load_tw(sv, a.sc, 64, (ABL & ABL_TWD) != 0, p, T);
+        if (ABL & ABL_FMA) {
 #pragma unroll
-        for (int v = 0; v < 6; v++) tv[v] = a.i3[64 * v];
+            for (int k = 0; k < 16; k++)
+                if ((k & 4) == 0) { abfly(x0[k], x0[k + 4], Tws{tv[k & 3].x, tv[k & 3].y}); abfly(x1[k], x1[k + 4], Tws{tv[k & 3].x, tv[k & 3].y}); }
 #pragma unroll
-        for (int v = 0; v < 8; v++) sv[v] = a.sc[64 * v];
-        spass_inv3<(SOLM & SOL_I3) != 0, (SOLM & SOL_SC) != 0>(x0, tv, sv, p, sk);
-        spass_inv3<(SOLM & SOL_I3) != 0, (SOLM & SOL_SC) != 0>(x1, tv, sv, p, sk);
+            for (int k = 0; k < 8; k++) { abfly(x0[k], x0[k + 8], tws_of(sv, k)); abfly(x1[k], x1[k + 8], tws_of(sv, k)); }
+#pragma unroll
+            for (int k = 0; k < 16; k++) { x0[k] ^= tws_of(sv, k).w; x1[k] ^= tws_of(sv, k).ws; }
+        } else {
+            spass_inv3<(SOLM & SOL_I3) != 0, (SOLM & SOL_SC) != 0>(x0, tv, sv, p, sk);
+            spass_inv3<(SOLM & SOL_I3) != 0, (SOLM & SOL_SC) != 0>(x1, tv, sv, p, sk);
+        }
     }
 }
 
 // One code copy serves both primes (q is team-uniform).  sa = residues of output polynomial q
 // ("mine", finished by this team), sb = residues of output polynomial 1-q (handed over).
-template <int SOLM, bool ROW0>
+template <int SOLM, bool ROW0, int ABL>
 __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, uint32_t* acc, const SPtr& a,
                                               const int32_t* other_own, const uint16_t* s_abar, const int T, const int q,
-                                              const int tbar, const int gbar)
+                                              const int tbar, const int gbar, const uint32_t dbg)
 {
     const int32_t p = (int32_t)(q ? Prime<1>::p : Prime<0>::p);
     const uint32_t pinv = q ? Prime<1>::pinv : Prime<0>::pinv;
@@ -177,6 +256,14 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, u
             int32_t x0[16], x1[16];
             const uint32_t* aj = acc + j * kN + T;
             const uint32_t* lin = aj - am;             // element e - am
+            if (ABL & ABL_DIG) {
+#pragma unroll
+                for (int k = 0; k < 16; k++) {
+                    const uint32_t t = (aj[64 * k] & dbg) + (uint32_t)(T + 5 * k);
+                    x0[k] = (int32_t)(t & 0xFFu);
+                    x1[k] = (int32_t)((t + 7u) & 0xFFu);
+                }
+            } else {
 #pragma unroll
             for (int k = 0; k < 16; k++) {
                 const bool wrap = k < kth;
@@ -187,31 +274,50 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, u
                 x0[k] = (int32_t)(t >> 24);
                 x1[k] = (int32_t)((t >> 16) & 0xFFu);
             }
-            sfwd2_dev<SOLM>(x0, x1, a, p, sk, tbar, j != 0);       // j = 0 follows the step's closing barrier
+            }
+            sfwd2_dev<SOLM, ABL>(x0, x1, a, p, sk, tbar, j != 0, T, dbg);       // j = 0 follows the step's closing barrier
             const uint4* row0 = bk4 + (size_t)((ROW0 ? 0 : i) * kRows + 2 * j) * (4 * (kN / 4));
             const uint4* row1 = row0 + 4 * (kN / 4);
 #pragma unroll
             for (int v = 0; v < 4; v++) {
-                const uint4 b0 = __ldg(row0 + off_a + v * 64), b1 = __ldg(row1 + off_a + v * 64);
+                uint4 b0, b1;
+                if (ABL & ABL_KEY) { b0 = make_uint4(i + v, j + 5, T, p - v); b1 = make_uint4(T + v, i, 9 + j, p - 2 * v); }
+                else { b0 = __ldg(row0 + off_a + v * 64); b1 = __ldg(row1 + off_a + v * 64); }
+                if (ABL & ABL_FMA) {
+                    sa[4 * v + 0] += (x0[4 * v + 0] ^ (int32_t)b0.x) + (x1[4 * v + 0] ^ (int32_t)b1.x);
+                    sa[4 * v + 1] += (x0[4 * v + 1] ^ (int32_t)b0.y) + (x1[4 * v + 1] ^ (int32_t)b1.y);
+                    sa[4 * v + 2] += (x0[4 * v + 2] ^ (int32_t)b0.z) + (x1[4 * v + 2] ^ (int32_t)b1.z);
+                    sa[4 * v + 3] += (x0[4 * v + 3] ^ (int32_t)b0.w) + (x1[4 * v + 3] ^ (int32_t)b1.w);
+                } else {
                 sa[4 * v + 0] += smontmul2(x0[4 * v + 0], b0.x, x1[4 * v + 0], b1.x, p, pinv);
                 sa[4 * v + 1] += smontmul2(x0[4 * v + 1], b0.y, x1[4 * v + 1], b1.y, p, pinv);
                 sa[4 * v + 2] += smontmul2(x0[4 * v + 2], b0.z, x1[4 * v + 2], b1.z, p, pinv);
                 sa[4 * v + 3] += smontmul2(x0[4 * v + 3], b0.w, x1[4 * v + 3], b1.w, p, pinv);
+                }
             }
 #pragma unroll
             for (int v = 0; v < 4; v++) {
-                const uint4 b0 = __ldg(row0 + off_b + v * 64), b1 = __ldg(row1 + off_b + v * 64);
+                uint4 b0, b1;
+                if (ABL & ABL_KEY) { b0 = make_uint4(i + v, j + 5, T, p - v); b1 = make_uint4(T + v, i, 9 + j, p - 2 * v); }
+                else { b0 = __ldg(row0 + off_b + v * 64); b1 = __ldg(row1 + off_b + v * 64); }
+                if (ABL & ABL_FMA) {
+                    sb[4 * v + 0] += (x0[4 * v + 0] ^ (int32_t)b0.x) + (x1[4 * v + 0] ^ (int32_t)b1.x);
+                    sb[4 * v + 1] += (x0[4 * v + 1] ^ (int32_t)b0.y) + (x1[4 * v + 1] ^ (int32_t)b1.y);
+                    sb[4 * v + 2] += (x0[4 * v + 2] ^ (int32_t)b0.z) + (x1[4 * v + 2] ^ (int32_t)b1.z);
+                    sb[4 * v + 3] += (x0[4 * v + 3] ^ (int32_t)b0.w) + (x1[4 * v + 3] ^ (int32_t)b1.w);
+                } else {
                 sb[4 * v + 0] += smontmul2(x0[4 * v + 0], b0.x, x1[4 * v + 0], b1.x, p, pinv);
                 sb[4 * v + 1] += smontmul2(x0[4 * v + 1], b0.y, x1[4 * v + 1], b1.y, p, pinv);
                 sb[4 * v + 2] += smontmul2(x0[4 * v + 2], b0.z, x1[4 * v + 2], b1.z, p, pinv);
                 sb[4 * v + 3] += smontmul2(x0[4 * v + 3], b0.w, x1[4 * v + 3], b1.w, p, pinv);
+                }
             }
         }
-        sinv2_dev<SOLM>(sb, sa, a, q, p, sk, tbar);
+        sinv2_dev<SOLM, ABL>(sb, sa, a, q, p, sk, tbar, T);
         // sa = INTT(out q) (mine), sb = INTT(out 1-q): hand sb to the other team through my own chunk
 #pragma unroll
         for (int v = 0; v < 4; v++) *reinterpret_cast<V4*>(a.own + 4 * v) = V4{sb[4 * v], sb[4 * v + 1], sb[4 * v + 2], sb[4 * v + 3]};
-        named_bar_sync(gbar, 128);
+        tbar_sync<ABL>(gbar, 128);
         int32_t t[16];
         ld_own(t, other_own);                            // other team's residue of out q
         const int32_t cw = c_s.crt.w, cws = c_s.crt.ws;
@@ -222,11 +328,11 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, u
 #pragma unroll
             for (int k = 0; k < 16; k++) acc_mine[64 * k] += scrt_lift32(sa[k], t[k], cw, cws);
         }
-        named_bar_sync(gbar, 128);
+        tbar_sync<ABL>(gbar, 128);
     }
 }
 
-template <int G, int SOLM, bool ROW0 = false>
+template <int G, int SOLM, bool ROW0 = false, int ABL = 0>
 __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P, const TeamSTables* __restrict__ tabs)
 {
     extern __shared__ __align__(16) uint32_t smem[];
@@ -279,7 +385,7 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P,
     }
     named_bar_sync(gbar, 128);
 
-    brs_gate_loop<SOLM, ROW0>(P.bk, acc, a, xs_other + chunk_of(T), s_abar, T, q, tbar, gbar);
+    brs_gate_loop<SOLM, ROW0, ABL>(P.bk, acc, a, xs_other + chunk_of(T), s_abar, T, q, tbar, gbar, P.dbg);
 
     // ---- SampleExtract(0) (src/bootstrap_gpu.cu:366-381) ----
     if (P.trlwe) {          // BootstrapTLWE2TRLWE (src/bootstrap_gpu.cu:316-322): no extraction

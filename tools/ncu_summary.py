@@ -6,7 +6,7 @@ steps = int(sys.argv[4]) if len(sys.argv) > 4 else 636
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, vals = rows[0], rows[1], rows[2]
-want = r"^(gpu__time_duration.sum|sm__cycles_elapsed.max|launch__registers_per_thread|launch__occupancy_limit.*|sm__warps_active.avg.pct_of_peak_sustained_active|smsp__issue_active.avg.per_cycle_active|sm__inst_executed_pipe_(alu|fma|lsu|adu|uniform).avg.pct_of_peak_sustained_active|sm__pipe_(alu|fma|fmaheavy|fmalite)_cycles_active.avg.pct_of_peak_sustained_active|smsp__average_warps_issue_stalled_.*_per_issue_active.ratio|dram__bytes_(read|write).sum|l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed|l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum|l1tex__data_pipe_lsu_wavefronts_mem_shared.sum|smsp__inst_executed.sum|lts__t_sector_hit_rate.pct|l1tex__t_sector_hit_rate.pct|sm__throughput.avg.pct_of_peak_sustained_elapsed|smsp__sass_inst_executed_op_local_(ld|st).sum|l1tex__lsu_writeback_active.*pct.*|l1tex__data_pipe.*pct.*)$"
+want = r"^(gpu__time_duration.sum|sm__cycles_elapsed.max|launch__registers_per_thread|launch__occupancy_limit.*|sm__warps_active.avg.pct_of_peak_sustained_active|smsp__issue_active.avg.per_cycle_active|sm__inst_executed_pipe_(alu|fma|lsu|adu|uniform).avg.pct_of_peak_sustained_active|sm__pipe_(alu|fma|fmaheavy|fmalite|fp64|shared)_cycles_active.avg.pct_of_peak_sustained_active|sm__inst_executed_pipe_(fmaheavy|fmalite|fp64|xu|cbu|tex).*pct_of_peak_sustained_active|smsp__inst_executed_pipe_(fmaheavy|fmalite|alu|fma).*|sm__inst_executed.avg.per_cycle_elapsed|smsp__warps_eligible.avg.per_cycle_active|smsp__issue_inst0.avg.pct_of_peak_sustained_active|smsp__average_warps_issue_stalled_.*_per_issue_active.ratio|dram__bytes_(read|write).sum|l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed|l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum|l1tex__data_pipe_lsu_wavefronts_mem_shared.sum|smsp__inst_executed.sum|lts__t_sector_hit_rate.pct|l1tex__t_sector_hit_rate.pct|sm__throughput.avg.pct_of_peak_sustained_elapsed|smsp__sass_inst_executed_op_local_(ld|st).sum|l1tex__lsu_writeback_active.*pct.*|l1tex__data_pipe.*pct.*)$"
 for h, u, v in zip(hdr, units, vals):
     if re.match(want, h):
         print(f"{h:95s} {u:12s} {v}")
