@@ -88,18 +88,10 @@ template <int G> int set_br16_attr()
     return 0;
 }
 
-// Solinas masks of the k_blind_rotate_s variants 40 + m (A/B of which passes put q*p on the ALU pipe)
-template <int G, int M> int set_brs_attr1()
+template <int G> int set_brs_attr()
 {
-    CK(cudaFuncSetAttribute(k_blind_rotate_s<G, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(G)));
+    CK(cudaFuncSetAttribute(k_blind_rotate_s<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(G)));
     return 0;
-}
-template <int M> int set_brs_attr()
-{
-    if (int r = set_brs_attr1<1, M>()) return r;
-    if (int r = set_brs_attr1<2, M>()) return r;
-    if (int r = set_brs_attr1<3, M>()) return r;
-    return set_brs_attr1<4, M>();
 }
 
 // twiddle tables + kernel attributes on `device` (InitializeNTThandlers, src/bootstrap_gpu.cu:97-109)
@@ -152,15 +144,11 @@ int setup_device(int device)
     CK(cudaFuncSetAttribute(k_cmux16<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(1)));
     CK(cudaFuncSetAttribute(k_cmux16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(4)));
     CK(cudaFuncSetAttribute(k_polymul16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, polymul16_smem_bytes(4)));
-    if (int r = set_brs_attr<0>()) return r;
     if (int r = set_brs_attr<1>()) return r;
     if (int r = set_brs_attr<2>()) return r;
     if (int r = set_brs_attr<3>()) return r;
-    if (int r = set_brs_attr<24>()) return r;
-    if (int r = set_brs_attr<27>()) return r;
-    if (int r = set_brs_attr<59>()) return r;
-    if (int r = set_brs_attr<63>()) return r;
-    CK(cudaFuncSetAttribute(k_blind_rotate_s<4, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(4)));
+    if (int r = set_brs_attr<4>()) return r;
+    CK(cudaFuncSetAttribute(k_blind_rotate_s<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(4)));
     if (int r = set_br16_attr<1>()) return r;
     if (int r = set_br16_attr<2>()) return r;
     if (int r = set_br16_attr<3>()) return r;
@@ -277,7 +265,7 @@ int b2fhe_set_ks_variant(int variant)
 int b2fhe_set_br_variant(int variant)
 {
     if (variant == -1 || variant == -2) { g_br_tail_split = variant == -2; return 0; }
-    REQUIRE(variant == 0 || variant == 1 || variant == 2 || variant == 4 || variant == 5 || variant == 16 || (variant >= 17 && variant <= 21) || variant == 32 || (variant >= 40 && variant <= 48), B2FHE_E_BAD_ARGUMENT);
+    REQUIRE(variant == 0 || variant == 1 || variant == 2 || variant == 4 || variant == 5 || variant == 16 || (variant >= 17 && variant <= 21) || variant == 32 || variant == 40 || variant == 48, B2FHE_E_BAD_ARGUMENT);
     g_br_variant = variant;
     return 0;
 }

@@ -25,21 +25,12 @@ template <int G> int launch_br16q_g(const DevCtx& c, const BrParams& P, cudaStre
     LAUNCHED();
     return 0;
 }
-template <int G, int M> int launch_brs_g(const DevCtx& c, const BrParams& P, cudaStream_t st)
+template <int G> int launch_brs_g(const DevCtx& c, const BrParams& P, cudaStream_t st)
 {
     const int grid = (P.count - P.first + G - 1) / G;
-    k_blind_rotate_s<G, M><<<grid, 128 * G, brs_smem_bytes(G), st>>>(P, c.tabs);
+    k_blind_rotate_s<G><<<grid, 128 * G, brs_smem_bytes(G), st>>>(P, c.tabs);
     LAUNCHED();
     return 0;
-}
-template <int M> int launch_brs(const DevCtx& c, const BrParams& P, cudaStream_t st, int g)
-{
-    switch (g) {
-        case 1: return launch_brs_g<1, M>(c, P, st);
-        case 2: return launch_brs_g<2, M>(c, P, st);
-        case 3: return launch_brs_g<3, M>(c, P, st);
-        default: return launch_brs_g<4, M>(c, P, st);
-    }
 }
 int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
 {
@@ -86,24 +77,20 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
         LAUNCHED();
         return 0;
     }
-    if (variant >= 40 && variant <= 48) {      // second generation (signed residues, Solinas primes, vector exchanges); 40 + m = Solinas mask A/B
+    if (variant == 40 || variant == 48) {      // second generation (signed residues, vector exchanges, doubled accumulator)
         P.bk = c.bk_ntt16;
+        if (variant == 48) {      // key row 0 at every step (timing experiment: key traffic vs arithmetic; wrong results)
+            const int grid = (P.count - P.first + 3) / 4;
+            k_blind_rotate_s<4, true><<<grid, 512, brs_smem_bytes(4), st>>>(P, c.tabs);
+            LAUNCHED();
+            return 0;
+        }
         if (g == 0) g = per_sm >= 4 ? 4 : per_sm == 3 ? 3 : 1;
-        switch (variant) {
-            case 40: return launch_brs<0>(c, P, st, g);
-            case 41: return launch_brs<1>(c, P, st, g);
-            case 42: return launch_brs<2>(c, P, st, g);
-            case 43: return launch_brs<3>(c, P, st, g);
-            case 44: return launch_brs<24>(c, P, st, g);
-            case 45: return launch_brs<27>(c, P, st, g);
-            case 46: return launch_brs<59>(c, P, st, g);
-            case 47: return launch_brs<63>(c, P, st, g);
-            default: {      // 48: key row 0 at every step (timing experiment: key traffic vs arithmetic; wrong results)
-                const int grid = (P.count - P.first + 3) / 4;
-                k_blind_rotate_s<4, 0, true><<<grid, 512, brs_smem_bytes(4), st>>>(P, c.tabs);
-                LAUNCHED();
-                return 0;
-            }
+        switch (g) {
+            case 1: return launch_brs_g<1>(c, P, st);
+            case 2: return launch_brs_g<2>(c, P, st);
+            case 3: return launch_brs_g<3>(c, P, st);
+            default: return launch_brs_g<4>(c, P, st);
         }
     }
     if (variant == 21) {      // paired transforms + four exchange buffers per team (8 barriers per step)

@@ -87,6 +87,9 @@ __device__ __forceinline__ void inv_dev_rt(uint32_t (&x)[32], uint32_t* xbuf, co
     }
 }
 
+// 32-bit shared-window address of a shared-memory pointer
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads)
 {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");

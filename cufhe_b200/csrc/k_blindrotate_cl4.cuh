@@ -30,7 +30,6 @@
 
 namespace b2 {
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, int rank)
 {
     uint32_t r;

@@ -8,15 +8,23 @@
 // gadget digits of an accumulator polynomial are transformed together, their two key rows share
 // one Montgomery reduction, the two inverse transforms run together.
 //
-// What is new (ntt16s.cuh has the arithmetic): signed lazy residues (4-instruction butterflies),
-// Solinas primes (SOLM selects the passes whose q*p product runs on the ALU pipe), forward
-// passes A -> D -> C so that every exchange is 128-bit on at least one side, and
-// synchronisation that matches who actually shares data:
-//   * D <-> C exchanges stay inside a half-warp            -> __syncwarp
-//   * A -> D and D -> A cross the team's two warps         -> 64-thread named barrier (5 per step)
-//   * residue hand-over + accumulator update cross teams   -> 128-thread named barrier (2 per step)
-// (the first generation used fourteen 128-thread barriers per step).  Per thread and step the
-// exchanges cost 96 LDS/STS instead of 384.
+// What is new (ntt16s.cuh has the arithmetic and the measured cost model: a step costs about
+// 4 N(IMAD.HI, IMAD.WIDE) + N(other instructions) issue cycles per warp, so the work is cutting
+// instructions):
+//   * signed lazy residues: 4-instruction butterflies, no offsets;
+//   * forward passes A -> D -> C so that every exchange is 128-bit on at least one side; per thread
+//     and step the exchanges cost 96 LDS/STS instead of 384;
+//   * synchronisation that matches who actually shares data: D <-> C exchanges stay inside a
+//     half-warp (__syncwarp), A -> D and D -> A cross the team's two warps (64-thread named
+//     barrier, 5 per step), only the residue hand-over and the accumulator update cross teams
+//     (128-thread named barrier, 2 per step) -- the first generation used fourteen 128-thread
+//     barriers per step;
+//   * the accumulator is kept as [-acc | +acc] (2 x 1024 words per polynomial): coefficient e of
+//     X^a acc is word 1024 + e - a, sign included, for every e -- no wrap test, no select, no
+//     negation per coefficient; a >= 1024 (all signs flipped) takes a warp-uniform branch;
+//   * table look-ups take shared-memory ADDRESSES built straight from the digit byte (SHF/PRMT + LEA);
+//   * all shared-memory traffic goes through explicit 32-bit addresses with immediate offsets, so
+//     ptxas keeps eight address registers instead of re-deriving pointers inside the loop.
 #pragma once
 #include "k_blindrotate.cuh"
 #include "ntt16s.cuh"
@@ -25,10 +33,10 @@ namespace b2 {
 
 __constant__ TeamSConst c_s;
 
-constexpr int kBrsGateSmemWords = 2 * kN + 4 * kXsWords + 640 / 2;      // acc + 2 teams x 2 arrays + abar(u16)
+constexpr int kBrsAccWords = 2 * 2 * kN;                               // two polynomials x [-acc | +acc]
+constexpr int kBrsGateSmemWords = kBrsAccWords + 4 * kXsWords + 640 / 2;      // acc + 2 teams x 2 arrays + abar(u16)
 __host__ __device__ constexpr int brs_smem_bytes(int gates) { return (kTeamSTableWords + gates * kBrsGateSmemWords) * 4; }
 
-enum : int { SOL_F2 = 1, SOL_F3 = 2, SOL_I1 = 4, SOL_I2 = 8, SOL_I3 = 16, SOL_SC = 32 };
 // timing ablations (tools/ablate_brs.cu only; results are WRONG with any of them set): what does each
 // component of a CMUX step cost on the real machine?
 enum : int { ABL_LUT = 1,      // table look-ups at conflict-free (lane) indices
@@ -36,25 +44,47 @@ enum : int { ABL_LUT = 1,      // table look-ups at conflict-free (lane) indices
              ABL_KEY = 4,      // no key loads (register constants)
              ABL_BAR = 8,      // no named barriers / __syncwarp
              ABL_XCH = 16,     // no shared-memory exchanges
-             ABL_FMA = 32,     // butterflies and key products without multiplies
              ABL_TWD = 64 };   // twiddles from registers (no table loads)
 
-// smem image of TeamSTables: per-T vectors f3 | i3 | sc are addressed from ONE pointer
-// (vector v of pass X at tbT[64 (off_X + v)]) -- they are NOT adjacent in the struct, so the kernel
-// uses three immediates relative to &f3[q][0][T]
-struct SPtr {
-    int32_t* own;           // chunk_of(T) in array 0 of my team; array 1 = + kXsWords
-    int32_t* vw;            // vector scatter base 20 (T&15) + 4 (T>>4)   (+ 336 kh)    A->D, D->A
-    int32_t* sw;            // word scatter base 336 (T>>4) + (T&15)      (+ 20 k)      D<->C
-    const V4* f2;           // &tab.f2[q][T>>4][0]
-    const V4* f3;           // &tab.f3[q][0][T]   (vector stride 64)
-    const V4* i2;           // &tab.i2[q][0][T&15] (vector stride 16)
-    const V4* i3;           // &tab.i3[q][0][T]
-    const V4* sc;           // &tab.sc[q][0][T]
-    const int32_t* lut;     // &tab.lut1[q][0]; lut24 / lut35 of prime q follow via tab offsets
-    const I2* lut24;
-    const I2* lut35;
+// ---- shared memory through explicit 32-bit window addresses ------------------------------------
+template <int OFF> __device__ __forceinline__ int32_t lds32(uint32_t a)
+{
+    int32_t r;
+    asm volatile("ld.shared.s32 %0, [%1 + %2];" : "=r"(r) : "r"(a), "n"(OFF));
+    return r;
+}
+template <int OFF> __device__ __forceinline__ I2 lds64(uint32_t a)
+{
+    I2 r;
+    asm volatile("ld.shared.v2.s32 {%0, %1}, [%2 + %3];" : "=r"(r.x), "=r"(r.y) : "r"(a), "n"(OFF));
+    return r;
+}
+template <int OFF> __device__ __forceinline__ V4 lds128(uint32_t a)
+{
+    V4 r;
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4 + %5];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a), "n"(OFF));
+    return r;
+}
+template <int OFF> __device__ __forceinline__ void sts32(uint32_t a, int32_t v)
+{
+    asm volatile("st.shared.s32 [%0 + %1], %2;" ::"r"(a), "n"(OFF), "r"(v) : "memory");
+}
+template <int OFF> __device__ __forceinline__ void sts128(uint32_t a, int32_t x, int32_t y, int32_t z, int32_t w)
+{
+    asm volatile("st.shared.v4.s32 [%0 + %1], {%2, %3, %4, %5};" ::"r"(a), "n"(OFF), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+
+struct SAddr {              // per-thread shared-window byte addresses
+    uint32_t own;           // chunk_of(T) in array 0 of my team; array 1 = + 4 kXsWords
+    uint32_t vw;            // vector scatter base 20 (T&15) + 4 (T>>4) words  (+ 336 words per kh)   A->D, D->A
+    uint32_t sw;            // word scatter base 336 (T>>4) + (T&15) words     (+ 20 words per k)     D<->C
+    uint32_t oth;           // the other team's chunk_of(T) in its array 0 (residue hand-over)
+    uint32_t tT;            // &tab.perT[q][0][T]    (+ 1024 bytes per vector)
+    uint32_t tLo;           // &tab.i2[q][0][T&15]   (+ 256 bytes per vector)
+    uint32_t tHi;           // &tab.f2[q][T>>4][0]   (+ 16 bytes per vector)
+    uint32_t lut;           // &tab.lut[q][0][0]     (+ 2048 bytes per table, 8 bytes per entry)
 };
+constexpr int kXsBytes = kXsWords * 4;
 
 __device__ __forceinline__ void stage_tables_s(uint32_t* s_tab, const TeamSTables* g_tab)
 {
@@ -63,276 +93,234 @@ __device__ __forceinline__ void stage_tables_s(uint32_t* s_tab, const TeamSTable
     for (int i = threadIdx.x; i < kTeamSTableWords / 4; i += blockDim.x) dst[i] = __ldg(src + i);
 }
 
-__device__ __forceinline__ void ld_own(int32_t (&x)[16], const int32_t* own)
-{
-#pragma unroll
-    for (int v = 0; v < 4; v++) {
-        const V4 r = *reinterpret_cast<const V4*>(own + 4 * v);
-        x[4 * v] = r.x; x[4 * v + 1] = r.y; x[4 * v + 2] = r.z; x[4 * v + 3] = r.w;
-    }
-}
-
 template <int ABL> __device__ __forceinline__ void tbar_sync(int id, int n) { if (!(ABL & ABL_BAR)) named_bar_sync(id, n); }
 template <int ABL> __device__ __forceinline__ void warp_sync() { if (!(ABL & ABL_BAR)) __syncwarp(); }
-// ablation stand-ins: same data flow, no multiplies
-__device__ __forceinline__ void abfly(int32_t& u, int32_t& v, const Tws t)
-{
-    const int32_t r = v ^ t.w, a = u;
-    u = a + r;
-    v = a - (r ^ t.ws);
-}
-template <int N>
-__device__ __forceinline__ void load_tw(V4 (&tv)[N], const V4* src, const int stride, const bool fake, const int32_t p, const int T)
-{
-#pragma unroll
-    for (int v = 0; v < N; v++) tv[v] = fake ? V4{p ^ v, T + v, p - v, T ^ v} : src[stride * v];
-}
 
-// two digit polynomials (raw digits, layout A) -> NTT domain (layout C)
-template <int SOLM, int ABL>
-__device__ __forceinline__ void sfwd2_dev(int32_t (&x0)[16], int32_t (&x1)[16], const SPtr& a, const int32_t p, const int sk,
-                                          const int tbar, const bool lead, const int T, const uint32_t dbg)
+// owner's four LDS.128 of its chunk in array ARR: vector v -> x[4 v .. 4 v + 3]
+template <int ARR> __device__ __forceinline__ void ld_own(int32_t (&x)[16], const uint32_t own)
 {
-    if (ABL & ABL_LUT) {
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-            x0[k] = (x0[k] & (int32_t)dbg) | (T & 31) | ((k & 7) << 5);
-            x1[k] = (x1[k] & (int32_t)dbg) | (T & 31) | (((k + 3) & 7) << 5);
+    const V4 r0 = lds128<ARR * kXsBytes + 0>(own), r1 = lds128<ARR * kXsBytes + 16>(own);
+    const V4 r2 = lds128<ARR * kXsBytes + 32>(own), r3 = lds128<ARR * kXsBytes + 48>(own);
+    x[0] = r0.x; x[1] = r0.y; x[2] = r0.z; x[3] = r0.w;
+    x[4] = r1.x; x[5] = r1.y; x[6] = r1.z; x[7] = r1.w;
+    x[8] = r2.x; x[9] = r2.y; x[10] = r2.z; x[11] = r2.w;
+    x[12] = r3.x; x[13] = r3.y; x[14] = r3.z; x[15] = r3.w;
+}
+// ... the same after A -> D: vector th -> x[th], x[th + 4], x[th + 8], x[th + 12]
+template <int ARR> __device__ __forceinline__ void ld_own_strided(int32_t (&x)[16], const uint32_t own)
+{
+    const V4 r0 = lds128<ARR * kXsBytes + 0>(own), r1 = lds128<ARR * kXsBytes + 16>(own);
+    const V4 r2 = lds128<ARR * kXsBytes + 32>(own), r3 = lds128<ARR * kXsBytes + 48>(own);
+    x[0] = r0.x; x[4] = r0.y; x[8] = r0.z; x[12] = r0.w;
+    x[1] = r1.x; x[5] = r1.y; x[9] = r1.z; x[13] = r1.w;
+    x[2] = r2.x; x[6] = r2.y; x[10] = r2.z; x[14] = r2.w;
+    x[3] = r3.x; x[7] = r3.y; x[11] = r3.z; x[15] = r3.w;
+}
+// word scatter (D <-> C): word k to sw + 80 k bytes
+template <int ARR, int K = 0> __device__ __forceinline__ void st_words(const int32_t (&x)[16], const uint32_t sw)
+{
+    if constexpr (K < 16) {
+        sts32<ARR * kXsBytes + 80 * K>(sw, x[K]);
+        st_words<ARR, K + 1>(x, sw);
+    }
+}
+// vector scatter, contiguous registers (A -> D): vector kh = x[4 kh .. 4 kh + 3] to vw + 1344 kh bytes
+template <int ARR> __device__ __forceinline__ void st_vec_contig(const int32_t (&x)[16], const uint32_t vw)
+{
+    sts128<ARR * kXsBytes + 0>(vw, x[0], x[1], x[2], x[3]);
+    sts128<ARR * kXsBytes + 1344>(vw, x[4], x[5], x[6], x[7]);
+    sts128<ARR * kXsBytes + 2688>(vw, x[8], x[9], x[10], x[11]);
+    sts128<ARR * kXsBytes + 4032>(vw, x[12], x[13], x[14], x[15]);
+}
+// vector scatter, strided registers (D -> A): vector kl = x[kl], x[kl + 4], x[kl + 8], x[kl + 12]
+template <int ARR> __device__ __forceinline__ void st_vec_strided(const int32_t (&x)[16], const uint32_t vw)
+{
+    sts128<ARR * kXsBytes + 0>(vw, x[0], x[4], x[8], x[12]);
+    sts128<ARR * kXsBytes + 1344>(vw, x[1], x[5], x[9], x[13]);
+    sts128<ARR * kXsBytes + 2688>(vw, x[2], x[6], x[10], x[14]);
+    sts128<ARR * kXsBytes + 4032>(vw, x[3], x[7], x[11], x[15]);
+}
+// twiddle vector loader (vector stride STRIDE bytes from BASE), or register stand-ins for the TWD ablation
+template <int STRIDE, int BASE, bool FAKE>
+struct TwLd {
+    uint32_t a; int32_t p; int T;
+    __device__ __forceinline__ V4 operator()(int v) const
+    {
+        if (FAKE) return V4{p ^ v, T + v, p - v, T ^ v};
+        // v is a compile-time constant after unrolling: one LDS.128 with an immediate offset
+        switch (v) {
+            case 0: return lds128<BASE + 0 * STRIDE>(a);
+            case 1: return lds128<BASE + 1 * STRIDE>(a);
+            case 2: return lds128<BASE + 2 * STRIDE>(a);
+            case 3: return lds128<BASE + 3 * STRIDE>(a);
+            case 4: return lds128<BASE + 4 * STRIDE>(a);
+            case 5: return lds128<BASE + 5 * STRIDE>(a);
+            case 6: return lds128<BASE + 6 * STRIDE>(a);
+            default: return lds128<BASE + 7 * STRIDE>(a);
         }
     }
-    spass_digits(x0, a.lut, a.lut24, a.lut35);
-    spass_digits(x1, a.lut, a.lut24, a.lut35);
+};
+
+// two digit polynomials (slots k < 4: signed digits, k >= 4: table addresses; layout A) -> NTT domain (layout C)
+template <int ABL>
+__device__ __forceinline__ void sfwd2_dev(int32_t (&x0)[16], int32_t (&x1)[16], const SAddr& a, const int32_t p, const int tbar,
+                                          const bool lead, const int T)
+{
+    {
+        auto l0 = [](int32_t h) { return lds32<0>((uint32_t)h); };
+        auto l1 = [](int32_t h) { return lds64<2048>((uint32_t)h); };
+        auto l2 = [](int32_t h) { return lds64<4096>((uint32_t)h); };
+        spass_digits(x0, l0, l1, l2);
+        spass_digits(x1, l0, l1, l2);
+    }
     if (lead) tbar_sync<ABL>(tbar, 64);          // owners have read their chunks (previous D->C)
-    if (!(ABL & ABL_XCH)) {
-#pragma unroll
-        for (int kh = 0; kh < 4; kh++) {
-            *reinterpret_cast<V4*>(a.vw + 336 * kh) = V4{x0[4 * kh], x0[4 * kh + 1], x0[4 * kh + 2], x0[4 * kh + 3]};
-            *reinterpret_cast<V4*>(a.vw + kXsWords + 336 * kh) = V4{x1[4 * kh], x1[4 * kh + 1], x1[4 * kh + 2], x1[4 * kh + 3]};
-        }
-    }
+    if (!(ABL & ABL_XCH)) { st_vec_contig<0>(x0, a.vw); st_vec_contig<1>(x1, a.vw); }
     tbar_sync<ABL>(tbar, 64);
-    if (!(ABL & ABL_XCH)) {
-#pragma unroll
-        for (int th = 0; th < 4; th++) {
-            const V4 r0 = *reinterpret_cast<const V4*>(a.own + 4 * th);
-            const V4 r1 = *reinterpret_cast<const V4*>(a.own + kXsWords + 4 * th);
-            x0[th] = r0.x; x0[th + 4] = r0.y; x0[th + 8] = r0.z; x0[th + 12] = r0.w;
-            x1[th] = r1.x; x1[th + 4] = r1.y; x1[th + 8] = r1.z; x1[th + 12] = r1.w;
-        }
-    }
-    {
-        V4 tv[8];
-        load_tw(tv, a.f2, 1, (ABL & ABL_TWD) != 0, p, T);
-        if (ABL & ABL_FMA) {
-#pragma unroll
-            for (int s = 0; s < 4; s++)
-#pragma unroll
-                for (int k = 0; k < 16; k++)
-                    if ((k & (8 >> s)) == 0) { const Tws t = tws_of(tv, (1 << s) - 1 + k / (16 >> s)); abfly(x0[k], x0[k + (8 >> s)], t); abfly(x1[k], x1[k + (8 >> s)], t); }
-        } else spass_fwd2<(SOLM & SOL_F2) != 0>(x0, x1, tv, p, sk);
-    }
+    if (!(ABL & ABL_XCH)) { ld_own_strided<0>(x0, a.own); ld_own_strided<1>(x1, a.own); }
+    spass_fwd<2>(x0, x1, TwLd<16, 0, (ABL & ABL_TWD) != 0>{a.tHi, p, T}, p);
     warp_sync<ABL>();                            // group mates have read their chunks
-    if (!(ABL & ABL_XCH)) {
-#pragma unroll
-        for (int k = 0; k < 16; k++) { a.sw[20 * k] = x0[k]; a.sw[kXsWords + 20 * k] = x1[k]; }
-    }
+    if (!(ABL & ABL_XCH)) { st_words<0>(x0, a.sw); st_words<1>(x1, a.sw); }
     warp_sync<ABL>();
-    if (!(ABL & ABL_XCH)) {
-        ld_own(x0, a.own);
-        ld_own(x1, a.own + kXsWords);
-    }
-    {
-        V4 tv[8];
-        load_tw(tv, a.f3, 64, (ABL & ABL_TWD) != 0, p, T);
-        if (ABL & ABL_FMA) {
-#pragma unroll
-            for (int s = 0; s < 4; s++)
-#pragma unroll
-                for (int k = 0; k < 16; k++)
-                    if ((k & (8 >> s)) == 0) { const Tws t = tws_of(tv, (1 << s) - 1 + k / (16 >> s)); abfly(x0[k], x0[k + (8 >> s)], t); abfly(x1[k], x1[k + (8 >> s)], t); }
-        } else spass_fwd2<(SOLM & SOL_F3) != 0>(x0, x1, tv, p, sk);
-    }
+    if (!(ABL & ABL_XCH)) { ld_own<0>(x0, a.own); ld_own<1>(x1, a.own); }
+    spass_fwd<2>(x0, x1, TwLd<1024, 1024 * kVecF3, (ABL & ABL_TWD) != 0>{a.tT, p, T}, p);
 }
 
 // two inverse transforms incl. n^-1 psi^-e: layout C in, layout A out, values in [-p/4, 5p/4)
-template <int SOLM, int ABL>
-__device__ __forceinline__ void sinv2_dev(int32_t (&x0)[16], int32_t (&x1)[16], const SPtr& a, const int q, const int32_t p,
-                                          const int sk, const int tbar, const int T)
+template <int ABL>
+__device__ __forceinline__ void sinv2_dev(int32_t (&x0)[16], int32_t (&x1)[16], const SAddr& a, const int q, const int32_t p,
+                                          const int tbar, const int T)
 {
-    if (ABL & ABL_FMA) {
-#pragma unroll
-        for (int u = 0; u < 4; u++)
-#pragma unroll
-            for (int k = 0; k < 16; k++)
-                if ((k & (1 << u)) == 0) { const Tws t = Tws{p + u, k}; abfly(x0[k], x0[k + (1 << u)], t); abfly(x1[k], x1[k + (1 << u)], t); }
-    } else {
+    {
         const Tws* c1 = c_s.iv1[q];
-        auto tw = [&](int i) { return c1[i]; };
-        spass_inv<(SOLM & SOL_I1) != 0, true>(x0, tw, p, sk);
-        spass_inv<(SOLM & SOL_I1) != 0, true>(x1, tw, p, sk);
+        spass_inv1<2>(x0, x1, [&](int i) { return c1[i]; }, p);
     }
     warp_sync<ABL>();                            // group mates' last loads of their chunks (forward D->C)
-    if (!(ABL & ABL_XCH)) {
-#pragma unroll
-        for (int k = 0; k < 16; k++) { a.sw[20 * k] = x0[k]; a.sw[kXsWords + 20 * k] = x1[k]; }
-    }
+    if (!(ABL & ABL_XCH)) { st_words<0>(x0, a.sw); st_words<1>(x1, a.sw); }
     warp_sync<ABL>();
-    if (!(ABL & ABL_XCH)) {
-        ld_own(x0, a.own);
-        ld_own(x1, a.own + kXsWords);
-    }
-    {
-        V4 tv[8];
-        load_tw(tv, a.i2, 16, (ABL & ABL_TWD) != 0, p, T);
-        if (ABL & ABL_FMA) {
-#pragma unroll
-            for (int u = 0; u < 4; u++)
-#pragma unroll
-                for (int k = 0; k < 16; k++)
-                    if ((k & (1 << u)) == 0) { const Tws t = tws_of(tv, (1 << u) - 1 + (k & ((1 << u) - 1))); abfly(x0[k], x0[k + (1 << u)], t); abfly(x1[k], x1[k + (1 << u)], t); }
-        } else {
-            auto tw = [&](int i) { return tws_of(tv, i); };
-            spass_inv<(SOLM & SOL_I2) != 0, false>(x0, tw, p, sk);
-            spass_inv<(SOLM & SOL_I2) != 0, false>(x1, tw, p, sk);
-        }
-    }
+    if (!(ABL & ABL_XCH)) { ld_own<0>(x0, a.own); ld_own<1>(x1, a.own); }
+    spass_inv2<2>(x0, x1, TwLd<256, 0, (ABL & ABL_TWD) != 0>{a.tLo, p, T}, p);
     tbar_sync<ABL>(tbar, 64);                    // every owner has read its chunk
-    if (!(ABL & ABL_XCH)) {
-#pragma unroll
-        for (int kl = 0; kl < 4; kl++) {
-            *reinterpret_cast<V4*>(a.vw + 336 * kl) = V4{x0[kl], x0[kl + 4], x0[kl + 8], x0[kl + 12]};
-            *reinterpret_cast<V4*>(a.vw + kXsWords + 336 * kl) = V4{x1[kl], x1[kl + 4], x1[kl + 8], x1[kl + 12]};
-        }
-    }
+    if (!(ABL & ABL_XCH)) { st_vec_strided<0>(x0, a.vw); st_vec_strided<1>(x1, a.vw); }
     tbar_sync<ABL>(tbar, 64);
-    if (!(ABL & ABL_XCH)) {
-        ld_own(x0, a.own);
-        ld_own(x1, a.own + kXsWords);
-    }
-    {
-        V4 tv[6], sv[8];
-        load_tw(tv, a.i3, 64, (ABL & ABL_TWD) != 0, p, T);
-        load_tw(sv, a.sc, 64, (ABL & ABL_TWD) != 0, p, T);
-        if (ABL & ABL_FMA) {
-#pragma unroll
-            for (int k = 0; k < 16; k++)
-                if ((k & 4) == 0) { abfly(x0[k], x0[k + 4], Tws{tv[k & 3].x, tv[k & 3].y}); abfly(x1[k], x1[k + 4], Tws{tv[k & 3].x, tv[k & 3].y}); }
-#pragma unroll
-            for (int k = 0; k < 8; k++) { abfly(x0[k], x0[k + 8], tws_of(sv, k)); abfly(x1[k], x1[k + 8], tws_of(sv, k)); }
-#pragma unroll
-            for (int k = 0; k < 16; k++) { x0[k] ^= tws_of(sv, k).w; x1[k] ^= tws_of(sv, k).ws; }
+    if (!(ABL & ABL_XCH)) { ld_own<0>(x0, a.own); ld_own<1>(x1, a.own); }
+    spass_inv3<2>(x0, x1, TwLd<1024, 1024 * kVecI3, (ABL & ABL_TWD) != 0>{a.tT, p, T},
+                  TwLd<1024, 1024 * kVecSc, (ABL & ABL_TWD) != 0>{a.tT, p, T}, p);
+}
+
+// digit extraction of accumulator polynomial j: slots k < 4 get the signed digits, slots k >= 4 the
+// address of their table entry.  own = &D_j[1024 + T] (my coefficients), rot = &D_j[1024 + T - am]
+// (coefficient e - am of the rotated polynomial, sign included), both + 256 bytes per k.
+template <bool FLIP, int K = 0>
+__device__ __forceinline__ void digits_dev(int32_t (&x0)[16], int32_t (&x1)[16], const uint32_t own, const uint32_t rot, const uint32_t lut)
+{
+    if constexpr (K < 16) {
+        const uint32_t r = (uint32_t)lds32<256 * K>(rot), o = (uint32_t)lds32<256 * K>(own);
+        const uint32_t t = FLIP ? kDecompAdd - o - r : kDecompAdd - o + r;
+        if (K < 4) {
+            x0[K] = (int32_t)(t >> 24) - 128;
+            x1[K] = (int32_t)((t >> 16) & 0xFFu) - 128;
         } else {
-            spass_inv3<(SOLM & SOL_I3) != 0, (SOLM & SOL_SC) != 0>(x0, tv, sv, p, sk);
-            spass_inv3<(SOLM & SOL_I3) != 0, (SOLM & SOL_SC) != 0>(x1, tv, sv, p, sk);
+            x0[K] = (int32_t)(lut + ((t >> 24) << 3));
+            x1[K] = (int32_t)(lut + (__byte_perm(t, 0, 0x4442) << 3));
         }
+        digits_dev<FLIP, K + 1>(x0, x1, own, rot, lut);
+    }
+}
+// accumulator update of my sixteen coefficients: acc += S, both copies
+template <int K = 0>
+__device__ __forceinline__ void acc_update(const uint32_t mine, const int32_t (&s0)[16], const int32_t (&s1)[16], const int32_t cw, const int32_t cws)
+{
+    if constexpr (K < 16) {
+        const uint32_t nv = (uint32_t)lds32<256 * K>(mine) + scrt_lift32(s0[K], s1[K], cw, cws);
+        sts32<256 * K>(mine, (int32_t)nv);
+        sts32<256 * K - 4096>(mine, (int32_t)(0u - nv));
+        acc_update<K + 1>(mine, s0, s1, cw, cws);
     }
 }
 
 // One code copy serves both primes (q is team-uniform).  sa = residues of output polynomial q
 // ("mine", finished by this team), sb = residues of output polynomial 1-q (handed over).
-template <int SOLM, bool ROW0, int ABL>
-__device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, uint32_t* acc, const SPtr& a,
-                                              const int32_t* other_own, const uint16_t* s_abar, const int T, const int q,
-                                              const int tbar, const int gbar, const uint32_t dbg)
+template <bool ROW0, int ABL>
+__device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, const uint32_t accb, const SAddr& a,
+                                              const uint16_t* s_abar, const int T, const int q, const int tbar, const int gbar,
+                                              const uint32_t dbg)
 {
     const int32_t p = (int32_t)(q ? Prime<1>::p : Prime<0>::p);
     const uint32_t pinv = q ? Prime<1>::pinv : Prime<0>::pinv;
-    const int sk = q ? 21 : 11;                  // kSolK
     // key row layout [row][prime][out][256 uint4] in bk16_slot order; out = q first, then 1-q
     const uint4* bk4 = reinterpret_cast<const uint4*>(bk) + T + (size_t)q * 2 * (kN / 4);
     const int off_a = q * (kN / 4), off_b = (1 - q) * (kN / 4);
-    uint32_t* acc_mine = acc + q * kN + T;
+    const uint32_t own0 = accb + 4 * (kN + T);                     // &D_0[1024 + T]; D_1 = + 8192 bytes
+    const uint32_t mine = own0 + q * 8192;                         // my output polynomial's +acc copy
+    const uint4* row0 = bk4;                                       // rows 2j, 2j + 1 of step i: advances by two rows per j
     for (int i = 0; i < kLwe; i++) {
         const uint32_t abar = s_abar[i];
-        const int am = (int)(abar & (kN - 1));
+        const uint32_t rot0 = own0 - 4 * (abar & (kN - 1));
         const bool flip = (abar >> kNbit) != 0;
-        // coefficient e = T + 64k of X^abar * acc is -/+ acc[e - am (+ 1024)]: wrapped (and negated) iff e < am <=> k < kth
-        const int kth = (am - T + 63) >> 6;
         int32_t sa[16], sb[16];
 #pragma unroll
         for (int k = 0; k < 16; k++) sa[k] = sb[k] = 0;
 #pragma unroll 1
         for (int j = 0; j < 2; j++) {
             int32_t x0[16], x1[16];
-            const uint32_t* aj = acc + j * kN + T;
-            const uint32_t* lin = aj - am;             // element e - am
             if (ABL & ABL_DIG) {
 #pragma unroll
                 for (int k = 0; k < 16; k++) {
-                    const uint32_t t = (aj[64 * k] & dbg) + (uint32_t)(T + 5 * k);
-                    x0[k] = (int32_t)(t & 0xFFu);
-                    x1[k] = (int32_t)((t + 7u) & 0xFFu);
+                    const uint32_t t = ((uint32_t)lds32<0>(own0 + j * 8192 + 256 * k) & dbg) + (uint32_t)(T + 5 * k);
+                    x0[k] = k < 4 ? (int32_t)(t & 0xFFu) - 128 : (int32_t)(a.lut + ((t & 0xFFu) << 3));
+                    x1[k] = k < 4 ? (int32_t)((t + 7u) & 0xFFu) - 128 : (int32_t)(a.lut + (((t + 7u) & 0xFFu) << 3));
                 }
-            } else {
+            } else if (flip) digits_dev<true>(x0, x1, own0 + j * 8192, rot0 + j * 8192, a.lut);
+            else digits_dev<false>(x0, x1, own0 + j * 8192, rot0 + j * 8192, a.lut);
+            if (ABL & ABL_LUT) {
 #pragma unroll
-            for (int k = 0; k < 16; k++) {
-                const bool wrap = k < kth;
-                const uint32_t* src = wrap ? lin + kN : lin;
-                uint32_t rot = src[64 * k];
-                rot = (wrap != flip) ? 0u - rot : rot;
-                const uint32_t t = rot - aj[64 * k] + kDecompAdd;
-                x0[k] = (int32_t)(t >> 24);
-                x1[k] = (int32_t)((t >> 16) & 0xFFu);
+                for (int k = 4; k < 16; k++) {
+                    x0[k] = (int32_t)((((uint32_t)x0[k] - a.lut) & dbg) + a.lut + 8 * ((T & 31) | ((k & 7) << 5)));
+                    x1[k] = (int32_t)((((uint32_t)x1[k] - a.lut) & dbg) + a.lut + 8 * ((T & 31) | (((k + 3) & 7) << 5)));
+                }
             }
-            }
-            sfwd2_dev<SOLM, ABL>(x0, x1, a, p, sk, tbar, j != 0, T, dbg);       // j = 0 follows the step's closing barrier
-            const uint4* row0 = bk4 + (size_t)((ROW0 ? 0 : i) * kRows + 2 * j) * (4 * (kN / 4));
+            sfwd2_dev<ABL>(x0, x1, a, p, tbar, j != 0, T);       // j = 0 follows the step's closing barrier
             const uint4* row1 = row0 + 4 * (kN / 4);
 #pragma unroll
             for (int v = 0; v < 4; v++) {
                 uint4 b0, b1;
                 if (ABL & ABL_KEY) { b0 = make_uint4(i + v, j + 5, T, p - v); b1 = make_uint4(T + v, i, 9 + j, p - 2 * v); }
                 else { b0 = __ldg(row0 + off_a + v * 64); b1 = __ldg(row1 + off_a + v * 64); }
-                if (ABL & ABL_FMA) {
-                    sa[4 * v + 0] += (x0[4 * v + 0] ^ (int32_t)b0.x) + (x1[4 * v + 0] ^ (int32_t)b1.x);
-                    sa[4 * v + 1] += (x0[4 * v + 1] ^ (int32_t)b0.y) + (x1[4 * v + 1] ^ (int32_t)b1.y);
-                    sa[4 * v + 2] += (x0[4 * v + 2] ^ (int32_t)b0.z) + (x1[4 * v + 2] ^ (int32_t)b1.z);
-                    sa[4 * v + 3] += (x0[4 * v + 3] ^ (int32_t)b0.w) + (x1[4 * v + 3] ^ (int32_t)b1.w);
-                } else {
                 sa[4 * v + 0] += smontmul2(x0[4 * v + 0], b0.x, x1[4 * v + 0], b1.x, p, pinv);
                 sa[4 * v + 1] += smontmul2(x0[4 * v + 1], b0.y, x1[4 * v + 1], b1.y, p, pinv);
                 sa[4 * v + 2] += smontmul2(x0[4 * v + 2], b0.z, x1[4 * v + 2], b1.z, p, pinv);
                 sa[4 * v + 3] += smontmul2(x0[4 * v + 3], b0.w, x1[4 * v + 3], b1.w, p, pinv);
-                }
             }
 #pragma unroll
             for (int v = 0; v < 4; v++) {
                 uint4 b0, b1;
                 if (ABL & ABL_KEY) { b0 = make_uint4(i + v, j + 5, T, p - v); b1 = make_uint4(T + v, i, 9 + j, p - 2 * v); }
                 else { b0 = __ldg(row0 + off_b + v * 64); b1 = __ldg(row1 + off_b + v * 64); }
-                if (ABL & ABL_FMA) {
-                    sb[4 * v + 0] += (x0[4 * v + 0] ^ (int32_t)b0.x) + (x1[4 * v + 0] ^ (int32_t)b1.x);
-                    sb[4 * v + 1] += (x0[4 * v + 1] ^ (int32_t)b0.y) + (x1[4 * v + 1] ^ (int32_t)b1.y);
-                    sb[4 * v + 2] += (x0[4 * v + 2] ^ (int32_t)b0.z) + (x1[4 * v + 2] ^ (int32_t)b1.z);
-                    sb[4 * v + 3] += (x0[4 * v + 3] ^ (int32_t)b0.w) + (x1[4 * v + 3] ^ (int32_t)b1.w);
-                } else {
                 sb[4 * v + 0] += smontmul2(x0[4 * v + 0], b0.x, x1[4 * v + 0], b1.x, p, pinv);
                 sb[4 * v + 1] += smontmul2(x0[4 * v + 1], b0.y, x1[4 * v + 1], b1.y, p, pinv);
                 sb[4 * v + 2] += smontmul2(x0[4 * v + 2], b0.z, x1[4 * v + 2], b1.z, p, pinv);
                 sb[4 * v + 3] += smontmul2(x0[4 * v + 3], b0.w, x1[4 * v + 3], b1.w, p, pinv);
-                }
             }
+            row0 += 2 * 4 * (kN / 4);
         }
-        sinv2_dev<SOLM, ABL>(sb, sa, a, q, p, sk, tbar, T);
+        if (ROW0) row0 = bk4;                            // timing experiment: key row 0 at every step
+        sinv2_dev<ABL>(sb, sa, a, q, p, tbar, T);
         // sa = INTT(out q) (mine), sb = INTT(out 1-q): hand sb to the other team through my own chunk
-#pragma unroll
-        for (int v = 0; v < 4; v++) *reinterpret_cast<V4*>(a.own + 4 * v) = V4{sb[4 * v], sb[4 * v + 1], sb[4 * v + 2], sb[4 * v + 3]};
+        sts128<0>(a.own, sb[0], sb[1], sb[2], sb[3]);
+        sts128<16>(a.own, sb[4], sb[5], sb[6], sb[7]);
+        sts128<32>(a.own, sb[8], sb[9], sb[10], sb[11]);
+        sts128<48>(a.own, sb[12], sb[13], sb[14], sb[15]);
         tbar_sync<ABL>(gbar, 128);
         int32_t t[16];
-        ld_own(t, other_own);                            // other team's residue of out q
+        ld_own<0>(t, a.oth);                             // other team's residue of out q
         const int32_t cw = c_s.crt.w, cws = c_s.crt.ws;
-        if (q) {
-#pragma unroll
-            for (int k = 0; k < 16; k++) acc_mine[64 * k] += scrt_lift32(t[k], sa[k], cw, cws);
-        } else {
-#pragma unroll
-            for (int k = 0; k < 16; k++) acc_mine[64 * k] += scrt_lift32(sa[k], t[k], cw, cws);
-        }
+        if (q) acc_update(mine, t, sa, cw, cws);
+        else acc_update(mine, sa, t, cw, cws);
         tbar_sync<ABL>(gbar, 128);
     }
 }
 
-template <int G, int SOLM, bool ROW0 = false, int ABL = 0>
+template <int G, bool ROW0 = false, int ABL = 0>
 __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P, const TeamSTables* __restrict__ tabs)
 {
     extern __shared__ __align__(16) uint32_t smem[];
@@ -346,24 +334,21 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P,
 
     const TeamSTables* tab = reinterpret_cast<const TeamSTables*>(smem);
     uint32_t* gbase = smem + kTeamSTableWords + gs * kBrsGateSmemWords;
-    uint32_t* acc = gbase;
-    int32_t* xs = reinterpret_cast<int32_t*>(gbase + 2 * kN) + q * 2 * kXsWords;           // my team's two arrays
-    const int32_t* xs_other = reinterpret_cast<const int32_t*>(gbase + 2 * kN) + (q ^ 1) * 2 * kXsWords;
-    uint16_t* s_abar = reinterpret_cast<uint16_t*>(gbase + 2 * kN + 4 * kXsWords);
-    const int gbar = 1 + gs, tbar = 1 + G + 2 * gs + q;                                    // named barriers (0 = __syncthreads)
+    uint32_t* acc = gbase;                                   // D_0 = [-acc_0 | +acc_0], D_1 = [-acc_1 | +acc_1]
+    uint32_t* xs = gbase + kBrsAccWords + q * 2 * kXsWords;  // my team's two arrays
+    uint32_t* xs_other = gbase + kBrsAccWords + (q ^ 1) * 2 * kXsWords;
+    uint16_t* s_abar = reinterpret_cast<uint16_t*>(gbase + kBrsAccWords + 4 * kXsWords);
+    const int gbar = 1 + gs, tbar = 1 + G + 2 * gs + q;      // named barriers (0 = __syncthreads)
 
-    SPtr a;
-    a.own = xs + chunk_of(T);
-    a.vw = xs + 20 * (T & 15) + 4 * (T >> 4);
-    a.sw = xs + 336 * (T >> 4) + (T & 15);
-    a.f2 = &tab->f2[q][T >> 4][0];
-    a.f3 = &tab->f3[q][0][T];
-    a.i2 = &tab->i2[q][0][T & 15];
-    a.i3 = &tab->i3[q][0][T];
-    a.sc = &tab->sc[q][0][T];
-    a.lut = &tab->lut1[q][0];
-    a.lut24 = &tab->lut24[q][0];
-    a.lut35 = &tab->lut35[q][0];
+    SAddr a;
+    a.own = smem_u32(xs + chunk_of(T));
+    a.vw = smem_u32(xs + 20 * (T & 15) + 4 * (T >> 4));
+    a.sw = smem_u32(xs + 336 * (T >> 4) + (T & 15));
+    a.oth = smem_u32(xs_other + chunk_of(T));
+    a.tT = smem_u32(&tab->perT[q][0][T]);
+    a.tLo = smem_u32(&tab->i2[q][0][T & 15]);
+    a.tHi = smem_u32(&tab->f2[q][T >> 4][0]);
+    a.lut = smem_u32(&tab->lut[q][0][0]);
 
     // ---- pre-add + modulus switch (gatebootstrapping_gpu.cuh:316-345) ----
     BrItem it;
@@ -380,22 +365,27 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P,
     const int cbody = it.off + ca * (int)a0[kLwe] + (a1 ? cb * (int)a1[kLwe] : 0);
     const uint32_t bbar = modswitch_b((uint32_t)cbody & 0xFFFFu);
     for (int c = t128; c < kN; c += 128) {
+        const uint32_t tv = testvec_b((uint32_t)c, bbar, P.mu);
         acc[c] = 0u;
-        acc[kN + c] = testvec_b((uint32_t)c, bbar, P.mu);
+        acc[kN + c] = 0u;
+        acc[2 * kN + c] = 0u - tv;
+        acc[3 * kN + c] = tv;
     }
     named_bar_sync(gbar, 128);
 
-    brs_gate_loop<SOLM, ROW0, ABL>(P.bk, acc, a, xs_other + chunk_of(T), s_abar, T, q, tbar, gbar, P.dbg);
+    brs_gate_loop<ROW0, ABL>(P.bk, smem_u32(acc), a, s_abar, T, q, tbar, gbar, P.dbg);
 
     // ---- SampleExtract(0) (src/bootstrap_gpu.cu:366-381) ----
+    const uint32_t* acc0 = acc + kN;                         // +acc_0
+    const uint32_t* acc1 = acc + 3 * kN;                     // +acc_1
     if (P.trlwe) {          // BootstrapTLWE2TRLWE (src/bootstrap_gpu.cu:316-322): no extraction
         uint32_t* out = P.out + (size_t)it.slot * 2 * kN;
-        for (int m = t128; m < 2 * kN; m += 128) out[m] = acc[m];
+        for (int m = t128; m < kN; m += 128) { out[m] = acc0[m]; out[kN + m] = acc1[m]; }
         return;
     }
     uint32_t* out = P.out + (size_t)it.slot * kLvl1Words;
-    for (int m = t128; m < kN; m += 128) out[m] = m == 0 ? acc[0] : 0u - acc[kN - m];
-    if (t128 == 0) out[kN] = acc[kN];
+    for (int m = t128; m < kN; m += 128) out[m] = m == 0 ? acc0[0] : 0u - acc0[kN - m];
+    if (t128 == 0) out[kN] = acc1[0];
 }
 
 }  // namespace b2

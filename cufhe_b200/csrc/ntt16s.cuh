@@ -1,12 +1,16 @@
 // ntt16s.cuh -- second-generation 1024-point negacyclic NTT for a TEAM of 64 threads x 16
-// coefficients: SIGNED lazy residues, Solinas primes, vectorised exchanges.
+// coefficients: SIGNED lazy residues, 128-bit exchanges, just-in-time twiddle vectors.
 //
 // Same transform as ntt16.cuh / ntt_core.cuh (merged-psi Cooley-Tukey forward, natural ->
 // bit-reversed; cyclic DIT inverse with w^-1 followed by n^-1 psi^-e), same NTT-domain
 // positions, so the bootstrapping key (bk16_slot order, Montgomery form in [0, p)) is shared.
 // Replaces SmallForwardNTT_1024 / SmallInverseNTT_1024 (reference
-// include/ntt_gpu/ntt_gpuntt.cuh:232-276,342-392).  What changed and why (VERDICT r1, weak 5:
-// the multiply pipe was 71 % busy at 1.74 issued instructions per multiply slot):
+// include/ntt_gpu/ntt_gpuntt.cuh:232-276,342-392).
+//
+// Cost model this file is written against (measured on B200, profiles/r2_ubench_mix_issue_port.log):
+// IMAD.HI / IMAD.WIDE take 4 cycles of a sub-partition during which NO ALU instruction overlaps
+// (IMAD.HI + k IADD3 = 4 + 2k cycles), IMAD (2 cycles) overlaps ALU work perfectly.  So a step costs
+// about 4 N(HI, WIDE) + N(everything else) issue cycles per warp, and the job is fewer instructions:
 //
 //  * residues are int32 in (-2^31, 2^31).  Shoup multiplication with a CENTRED twiddle w and the
 //    ROUNDED companion ws = round(w 2^32 / p):  q = mulhi.s32(v, ws), r = v w - q p lies in
@@ -14,21 +18,24 @@
 //         q = IMAD.HI(v, ws);  t = IMAD(v, w, u);  u' = IMAD(q, -p, t);  v' = IADD3(u, u, -u')
 //    -- 4 instructions instead of 5, and no "+2p" offsets.  Bounds: every stage widens a value by at
 //    most 5p/4; forward: table stages leave |x| < 3p/2 + 128, + 8 stages -> < 11.6 p; inverse: key
-//    products |s| < 2.45 p, first stage reduced, + 9 stages -> < 14.5 p; 2^31 > 16 p.
-//  * both primes are Solinas numbers p = 2^27 - 2^k + 1 (k = 11, 21), so q p = (q << 27) - (q << k) + q:
-//    the SOL form of the butterfly trades the third multiply for SHF + LEA + IADD3 on the ALU pipe
-//    (3 multiply-pipe slots instead of 4); which passes use it is a template mask, chosen by
-//    measurement so that the two pipes balance.
+//    products |s| < 2.45 p, first stage reduced, + 9 stages -> < 14.5 p; 2^31 > 16 p
+//    (tests/emul/emul_ntt16s.cpp propagates the intervals over the real butterfly structure).
+//  * both primes are Solinas numbers p = 2^27 - 2^k + 1 (k = 11, 21).  Computing q p as
+//    (q << 27) - (q << k) + q on the ALU pipe (3 multiply slots instead of 4) was built and MEASURED
+//    SLOWER in every mix (profiles/r2_probe_s_v1_first_signed_kernel.log, r2_ablate_v1.log) -- it
+//    trades one IMAD for three ALU instructions, the wrong direction under the cost model above.
 //  * forward passes: [table stages 0,1 in layout A] -> [strides 128..16 in layout D] -> [8..1 in
-//    layout C]; inverse: C -> D -> A as before.  Every exchange moves 128-bit vectors on at least
-//    one side, and the D<->C exchanges stay inside a half-warp (no barrier, __syncwarp only).
+//    layout C]; inverse: C -> D -> A.  Every exchange moves 128-bit vectors on at least one side,
+//    and the D<->C exchanges stay inside a half-warp (no barrier, __syncwarp only).
+//  * twiddles come as 128-bit vectors {w, ws, w', ws'} fetched stage by stage (at most 18 twiddle
+//    registers live instead of 32).
 //
 // Thread T (0..63), register k (0..15); e = coefficient / position index:
 //   layout A: e = T + 64 k                        layout C: e = 16 T + k
 //   layout D: e = 256 (T>>4) + (T&15) + 16 k
 // An exchange array is 64 chunks of 20 words (16 used), each 16-thread group skewed by 16 more
-// words (half the banks): chunk(T) = 20 T + 16 (T>>4).  A chunk is only ever READ by its owner T with four
-// LDS.128; writers scatter vectors or words into other threads' chunks.  All accesses are
+// words (half the banks): chunk(T) = 20 T + 16 (T>>4).  A chunk is only ever READ by its owner T
+// with four LDS.128; writers scatter vectors or words into other threads' chunks.  All accesses are
 // bank-conflict free (checked in tests/emul/emul_ntt16s.cpp).
 #pragma once
 #include "ntt16.cuh"
@@ -56,24 +63,27 @@ B2_HD int32_t smulhi(int32_t a, int32_t b)
 }
 
 // v * w mod p in [-p/4, 5p/4) for any int32 v
-template <bool SOL>
-B2_HD int32_t sshoup(int32_t v, int32_t w, int32_t ws, int32_t p, int k)
+B2_HD int32_t sshoup(int32_t v, int32_t w, int32_t ws, int32_t p)
 {
     const uint32_t q = (uint32_t)smulhi(v, ws);
-    const uint32_t t = (uint32_t)v * (uint32_t)w;
-    return (int32_t)(SOL ? t + (q << k) - ((q << 27) + q) : t - q * (uint32_t)p);
+    return (int32_t)((uint32_t)v * (uint32_t)w - q * (uint32_t)p);
 }
 // (u, v) -> (u + w v, u - w v)
-template <bool SOL>
-B2_HD void sbfly(int32_t& u, int32_t& v, const Tws t, const int32_t p, const int k)
+B2_HD void sbfly(int32_t& u, int32_t& v, const Tws t, const int32_t p)
 {
     const uint32_t q = (uint32_t)smulhi(v, t.ws);
     const uint32_t s = (uint32_t)v * (uint32_t)t.w + (uint32_t)u;
-    const uint32_t un = SOL ? s + (q << k) - ((q << 27) + q) : s - q * (uint32_t)p;
+    const uint32_t un = s - q * (uint32_t)p;
     v = (int32_t)((uint32_t)u + (uint32_t)u - un);
     u = (int32_t)un;
 }
-// v - round(v / 2^27) p: |result| <= 2^26 + 16 (2^k - 1)  (< 0.51 p for k = 11, < 0.76 p for k = 21)
+// the Solinas form of the same product (kept for the emulator's equality check and the record)
+B2_HD int32_t sshoup_solinas(int32_t v, int32_t w, int32_t ws, int k)
+{
+    const uint32_t q = (uint32_t)smulhi(v, ws);
+    return (int32_t)((uint32_t)v * (uint32_t)w + (q << k) - ((q << 27) + q));
+}
+// v - round(v / 2^27) p for |v| < 2^31 - 2^26: |result| <= 2^26 + 16 (2^k - 1)  (< 0.51 p for k = 11, < 0.76 p for k = 21)
 B2_HD int32_t sreduce(int32_t v, int32_t p)
 {
     const int32_t h = (int32_t)((uint32_t)v + (1u << 26)) >> 27;
@@ -108,26 +118,26 @@ B2_HD int32_t smontmul1(int32_t a0, uint32_t b0, int32_t p, uint32_t pinv)
 B2_HD uint32_t scrt_lift32(int32_t s0, int32_t s1, int32_t c, int32_t cs)
 {
     constexpr int32_t p1 = (int32_t)Prime<1>::p;
-    int32_t u = sshoup<false>(s1 - s0, c, cs, p1, 0);        // (s1 - s0) / p0 mod p1 in [-p1/4, 5 p1/4)
+    int32_t u = sshoup(s1 - s0, c, cs, p1);                  // (s1 - s0) / p0 mod p1 in [-p1/4, 5 p1/4)
     u = u > (p1 - 1) / 2 ? u - p1 : u;
     return (uint32_t)s0 + (uint32_t)u * Prime<0>::p;
 }
 
 // ---- tables ---------------------------------------------------------------------------------
 // Sixteen Tws per pass and thread = eight V4 vectors {w, ws, w', ws'}; index (2^s - 1) + g as in
-// ntt16.cuh.  [vec][T] order: a warp's LDS.128 is 512 contiguous bytes.
+// ntt16.cuh.  [vec][T] order: a warp's LDS.128 is 512 contiguous bytes.  The three per-thread
+// sets share one base pointer.
+constexpr int kVecF3 = 0, kVecI3 = 8, kVecSc = 14, kVecPerT = 22;
 struct TeamSTables {
-    V4 f2[2][4][8];         // [q][hi][vec]      forward strides 128..16 (layout D); half-warp broadcast
-    V4 f3[2][8][64];        // [q][vec][T]       forward strides 8..1    (layout C)
-    V4 i2[2][8][16];        // [q][vec][lo]      inverse t = 16..128     (layout D)
-    V4 i3[2][6][64];        // [q][vec][T]       inverse t = 256 (slots 0..3), 512 (slots 4..11)
-    V4 sc[2][8][64];        // [q][vec][T]       n^-1 psi^-(T + 64 k), k = 2 vec, 2 vec + 1
-    int32_t lut1[2][256];   // gadget-digit tables (entry d stands for d - 128), centred residues:
-    I2 lut24[2][256];       //   W1 (d-128);  { W2a (d-128), W2b (d-128) };  { W2a W1 (d-128), W2b W1 (d-128) }
-    I2 lut35[2][256];
+    V4 perT[2][kVecPerT][64];   // [q][vec][T]: forward strides 8..1 (layout C) | inverse t = 256 (slots 0..3), 512 (4..11) | n^-1 psi^-(T + 64 k)
+    V4 i2[2][8][16];            // [q][vec][lo]      inverse t = 16..128     (layout D)
+    V4 f2[2][4][8];             // [q][hi][vec]      forward strides 128..16 (layout D); half-warp broadcast
+    // gadget-digit tables, 8-byte entries indexed by the RAW digit byte d (standing for d - 128), centred
+    // residues:  0: { W1 (d-128), - };  1: { W2a (d-128), W2b (d-128) };  2: { W2a W1 (d-128), W2b W1 (d-128) }
+    I2 lut[2][3][256];
 };
 constexpr int kTeamSTableWords = sizeof(TeamSTables) / 4;
-static_assert(sizeof(TeamSTables) == 1024 + 16384 + 4096 + 12288 + 16384 + 10240, "table layout");
+static_assert(sizeof(TeamSTables) == 45056 + 4096 + 1024 + 12288, "table layout");
 struct TeamSConst {
     Tws iv1[2][16];         // inverse t = 1..8, warp-uniform: index (2^u - 1) + j (those with j = 0 are 1)
     Tws fw01[2][4];         // forward stages 0, 1 for general inputs: psi^brv(1), psi^brv(2), psi^brv(3)
@@ -156,7 +166,7 @@ inline void make_tables16s(TeamSTables& L, TeamSConst& C)
         const uint32_t iw = h_mulmod(ipsi, ipsi, p);
         const uint32_t ninv = h_powmod(kN, p - 2, p);
         auto psirev = [&](unsigned idx) { return h_powmod(psi, brv10(idx), p); };
-        auto put = [&](V4* vec, int vstride, int idx, Tws t) {      // Tws number idx of a 16-entry set
+        auto put = [&](V4* vec, int vstride, int idx, Tws t) {      // Tws number idx of a set
             V4& v = vec[(idx >> 1) * vstride];
             if (idx & 1) { v.z = t.w; v.w = t.ws; } else { v.x = t.w; v.y = t.ws; }
         };
@@ -170,8 +180,8 @@ inline void make_tables16s(TeamSTables& L, TeamSConst& C)
         for (int T = 0; T < 64; T++) {
             for (int s = 0; s < 4; s++)
                 for (int g = 0; g < (1 << s); g++)
-                    put(&L.f3[q][0][T], 64, (1 << s) - 1 + g, h_tws(psirev((64u << s) + ((unsigned)T << s) + g), p));
-            put(&L.f3[q][0][T], 64, 15, Tws{0, 0});
+                    put(&L.perT[q][kVecF3][T], 64, (1 << s) - 1 + g, h_tws(psirev((64u << s) + ((unsigned)T << s) + g), p));
+            put(&L.perT[q][kVecF3][T], 64, 15, Tws{0, 0});
         }
         // inverse DIT: half-size t uses w^-(j 512 / t), j = e mod t
         for (int u = 0; u < 4; u++)
@@ -184,46 +194,46 @@ inline void make_tables16s(TeamSTables& L, TeamSConst& C)
             put(&L.i2[q][0][lo], 16, 15, Tws{0, 0});
         }
         for (int T = 0; T < 64; T++) {
-            for (int g = 0; g < 4; g++) put(&L.i3[q][0][T], 64, g, h_tws(h_powmod(iw, (uint64_t)(T + 64 * g) * 2, p), p));   // t = 256
-            for (int g = 0; g < 8; g++) put(&L.i3[q][0][T], 64, 4 + g, h_tws(h_powmod(iw, (uint64_t)(T + 64 * g), p), p));   // t = 512
-            for (int k = 0; k < 16; k++) put(&L.sc[q][0][T], 64, k, h_tws(h_mulmod(ninv, h_powmod(ipsi, T + 64 * k, p), p), p));
+            for (int g = 0; g < 4; g++) put(&L.perT[q][kVecI3][T], 64, g, h_tws(h_powmod(iw, (uint64_t)(T + 64 * g) * 2, p), p));   // t = 256
+            for (int g = 0; g < 8; g++) put(&L.perT[q][kVecI3][T], 64, 4 + g, h_tws(h_powmod(iw, (uint64_t)(T + 64 * g), p), p));   // t = 512
+            for (int k = 0; k < 16; k++) put(&L.perT[q][kVecSc][T], 64, k, h_tws(h_mulmod(ninv, h_powmod(ipsi, T + 64 * k, p), p), p));
         }
         const uint32_t w1 = psirev(1), w2a = psirev(2), w2b = psirev(3);
         C.fw01[q][0] = h_tws(w1, p); C.fw01[q][1] = h_tws(w2a, p); C.fw01[q][2] = h_tws(w2b, p); C.fw01[q][3] = Tws{0, 0};
         C.r2[q] = h_centre((uint32_t)((((unsigned __int128)1) << 64) % p), p);
         for (int d = 0; d < 256; d++) {
             const uint32_t v = d >= 128 ? (uint32_t)(d - 128) : p - (uint32_t)(128 - d);     // d - 128 mod p
-            L.lut1[q][d] = h_centre(h_mulmod(w1, v, p), p);
-            L.lut24[q][d] = I2{h_centre(h_mulmod(w2a, v, p), p), h_centre(h_mulmod(w2b, v, p), p)};
-            L.lut35[q][d] = I2{h_centre(h_mulmod(h_mulmod(w2a, w1, p), v, p), p), h_centre(h_mulmod(h_mulmod(w2b, w1, p), v, p), p)};
+            L.lut[q][0][d] = I2{h_centre(h_mulmod(w1, v, p), p), 0};
+            L.lut[q][1][d] = I2{h_centre(h_mulmod(w2a, v, p), p), h_centre(h_mulmod(w2b, v, p), p)};
+            L.lut[q][2][d] = I2{h_centre(h_mulmod(h_mulmod(w2a, w1, p), v, p), p), h_centre(h_mulmod(h_mulmod(w2b, w1, p), v, p), p)};
         }
     }
     C.crt = h_tws(h_powmod(kP[0] % kP[1], kP[1] - 2, kP[1]), kP[1]);
 }
 
-// Tws number idx of a 16-entry set held as eight V4
-B2_HD Tws tws_of(const V4 (&tv)[8], int idx)
-{
-    const V4& v = tv[idx >> 1];
-    return (idx & 1) ? Tws{v.z, v.w} : Tws{v.x, v.y};
-}
+B2_HD Tws tws_lo(const V4& v) { return Tws{v.x, v.y}; }
+B2_HD Tws tws_hi(const V4& v) { return Tws{v.z, v.w}; }
 
 // ---- in-register passes ---------------------------------------------------------------------
-// Table stages 0 and 1 on raw gadget digits x[k] in [0, 256) (meaning x[k] - 128), layout A:
-// the four digits of a radix-4 group (k, k+4, k+8, k+12) -> five table entries + eight additions.
-// |output| < 3p/2 + 128.
-B2_HD void spass_digits(int32_t (&x)[16], const int32_t* l1, const I2* l24, const I2* l35)
+// Loader functors: ld(v) returns twiddle vector v of the pass (Tws 2v and 2v + 1); vectors are
+// fetched stage by stage so that at most 18 twiddle registers are live.
+//
+// Table stages 0 and 1 on gadget digits, layout A.  The four digits of a radix-4 group
+// (k, k+4, k+8, k+12): x[k] holds the SIGNED digit, the other three hold table HANDLES (whatever
+// the look-up functors take: the raw digit byte on the host, a shared-memory address on the
+// device).  Three look-ups + six 3-input additions.  |output| < 3p/2 + 128.
+template <class L0, class L1, class L2>
+B2_HD void spass_digits(int32_t (&x)[16], L0 l0, L1 l1, L2 l2)
 {
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        const int32_t d0 = x[k] - 128, t1 = l1[x[k + 8]];
-        const I2 u = l24[x[k + 4]], v = l35[x[k + 12]];
-        const int32_t A = d0 + t1, C = d0 - t1;           // x0 +- W1 x2
+        const int32_t d0 = x[k], t1 = l0(x[k + 8]);
+        const I2 u = l1(x[k + 4]), v = l2(x[k + 12]);
         const int32_t B = u.x + v.x, D = u.y - v.y;       // W2a (x1 + W1 x3),  W2b (x1 - W1 x3)
-        x[k] = A + B;
-        x[k + 4] = A - B;
-        x[k + 8] = C + D;
-        x[k + 12] = C - D;
+        x[k] = d0 + t1 + B;                               // x0 + W1 x2 + B
+        x[k + 4] = d0 + t1 - B;
+        x[k + 8] = d0 - t1 + D;                           // x0 - W1 x2 + D
+        x[k + 12] = d0 - t1 - D;
     }
 }
 // stages 0 and 1 by butterflies for general inputs (key conversion, standalone transforms):
@@ -231,41 +241,41 @@ B2_HD void spass_digits(int32_t (&x)[16], const int32_t* l1, const I2* l24, cons
 B2_HD void spass_fwd01(int32_t (&x)[16], const Tws w1, const Tws w2a, const Tws w2b, const int32_t p)
 {
 #pragma unroll
-    for (int k = 0; k < 8; k++) sbfly<false>(x[k], x[k + 8], w1, p, 0);
+    for (int k = 0; k < 8; k++) sbfly(x[k], x[k + 8], w1, p);
 #pragma unroll
-    for (int k = 0; k < 4; k++) { sbfly<false>(x[k], x[k + 4], w2a, p, 0); sbfly<false>(x[k + 8], x[k + 12], w2b, p, 0); }
+    for (int k = 0; k < 4; k++) { sbfly(x[k], x[k + 4], w2a, p); sbfly(x[k + 8], x[k + 12], w2b, p); }
+}
+// one stage of NP (1 or 2) polynomials: butterflies (k, k + tp), twiddle tw(k)
+template <int NP, class TW>
+B2_HD void sstage(int32_t (&x0)[16], int32_t (&x1)[16], const int tp, TW tw, const int32_t p)
+{
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+        if ((k & tp) == 0) {
+            const Tws t = tw(k);
+            sbfly(x0[k], x0[k + tp], t, p);
+            if (NP == 2) sbfly(x1[k], x1[k + tp], t, p);
+        }
 }
 // four forward stages on register strides 8, 4, 2, 1; twiddle (2^s - 1) + k / (2 tp)
-template <bool SOL>
-B2_HD void spass_fwd(int32_t (&x)[16], const V4 (&tv)[8], const int32_t p, const int sk)
+template <int NP, class LD>
+B2_HD void spass_fwd(int32_t (&x0)[16], int32_t (&x1)[16], LD ld, const int32_t p)
 {
-#pragma unroll
-    for (int s = 0; s < 4; s++) {
-        const int tp = 8 >> s;
-#pragma unroll
-        for (int k = 0; k < 16; k++)
-            if ((k & tp) == 0) sbfly<SOL>(x[k], x[k + tp], tws_of(tv, (1 << s) - 1 + k / (2 * tp)), p, sk);
-    }
+    const V4 c0 = ld(0), c1 = ld(1);
+    sstage<NP>(x0, x1, 8, [&](int) { return tws_lo(c0); }, p);
+    const V4 c2 = ld(2), c3 = ld(3);
+    sstage<NP>(x0, x1, 4, [&](int k) { return (k >> 3) ? tws_lo(c1) : tws_hi(c0); }, p);
+    const V4 c4 = ld(4), c5 = ld(5), c6 = ld(6), c7 = ld(7);
+    sstage<NP>(x0, x1, 2, [&](int k) { const int g = k >> 2; return g == 0 ? tws_hi(c1) : g == 1 ? tws_lo(c2) : g == 2 ? tws_hi(c2) : tws_lo(c3); }, p);
+    sstage<NP>(x0, x1, 1, [&](int k) {
+        const int g = k >> 1;           // Tws 7 + g
+        return g == 0 ? tws_hi(c3) : g == 1 ? tws_lo(c4) : g == 2 ? tws_hi(c4) : g == 3 ? tws_lo(c5) : g == 4 ? tws_hi(c5)
+             : g == 5 ? tws_lo(c6) : g == 6 ? tws_hi(c6) : tws_lo(c7); }, p);
 }
-template <bool SOL>
-B2_HD void spass_fwd2(int32_t (&x0)[16], int32_t (&x1)[16], const V4 (&tv)[8], const int32_t p, const int sk)
-{
-#pragma unroll
-    for (int s = 0; s < 4; s++) {
-        const int tp = 8 >> s;
-#pragma unroll
-        for (int k = 0; k < 16; k++)
-            if ((k & tp) == 0) {
-                const Tws t = tws_of(tv, (1 << s) - 1 + k / (2 * tp));
-                sbfly<SOL>(x0[k], x0[k + tp], t, p, sk);
-                sbfly<SOL>(x1[k], x1[k + tp], t, p, sk);
-            }
-    }
-}
-// inverse register strides 1, 2, 4, 8; twiddle (2^u - 1) + (k mod tp).  UNIT: twiddle 0 of every
-// stage is 1 (pass I1, warp-uniform table): plain reduction instead of the Shoup product.
-template <bool SOL, bool UNIT, class TW>
-B2_HD void spass_inv(int32_t (&x)[16], const TW& tw, const int32_t p, const int sk)
+// inverse pass I1: register strides 1, 2, 4, 8 with WARP-UNIFORM twiddles tw(i), i = (2^u - 1) + (k mod tp);
+// twiddle 0 of every stage is 1: plain reduction instead of the Shoup product
+template <int NP, class TW>
+B2_HD void spass_inv1(int32_t (&x0)[16], int32_t (&x1)[16], TW tw, const int32_t p)
 {
 #pragma unroll
     for (int u = 0; u < 4; u++) {
@@ -273,25 +283,53 @@ B2_HD void spass_inv(int32_t (&x)[16], const TW& tw, const int32_t p, const int 
 #pragma unroll
         for (int k = 0; k < 16; k++)
             if ((k & tp) == 0) {
-                if (UNIT && (k & (tp - 1)) == 0) sbfly_unit(x[k], x[k + tp], p);
-                else sbfly<SOL>(x[k], x[k + tp], tw((1 << u) - 1 + (k & (tp - 1))), p, sk);
+                if ((k & (tp - 1)) == 0) {
+                    sbfly_unit(x0[k], x0[k + tp], p);
+                    if (NP == 2) sbfly_unit(x1[k], x1[k + tp], p);
+                } else {
+                    const Tws t = tw((1 << u) - 1 + (k & (tp - 1)));
+                    sbfly(x0[k], x0[k + tp], t, p);
+                    if (NP == 2) sbfly(x1[k], x1[k + tp], t, p);
+                }
             }
     }
 }
-// I3: register strides 4 (t = 256, slots 0..3) then 8 (t = 512, slots 4..11), then the scale factors
-template <bool SOL, bool SOLSC>
-B2_HD void spass_inv3(int32_t (&x)[16], const V4 (&tv)[6], const V4 (&sv)[8], const int32_t p, const int sk)
+// inverse pass I2: register strides 1, 2, 4, 8; twiddle (2^u - 1) + (k mod tp) from eight vectors
+template <int NP, class LD>
+B2_HD void spass_inv2(int32_t (&x0)[16], int32_t (&x1)[16], LD ld, const int32_t p)
 {
-    auto tw = [&](int idx) { const V4& v = tv[idx >> 1]; return (idx & 1) ? Tws{v.z, v.w} : Tws{v.x, v.y}; };
+    const V4 c0 = ld(0), c1 = ld(1);
+    sstage<NP>(x0, x1, 1, [&](int) { return tws_lo(c0); }, p);
+    const V4 c2 = ld(2), c3 = ld(3);
+    sstage<NP>(x0, x1, 2, [&](int k) { return (k & 1) ? tws_lo(c1) : tws_hi(c0); }, p);
+    const V4 c4 = ld(4), c5 = ld(5), c6 = ld(6), c7 = ld(7);
+    sstage<NP>(x0, x1, 4, [&](int k) { const int g = k & 3; return g == 0 ? tws_hi(c1) : g == 1 ? tws_lo(c2) : g == 2 ? tws_hi(c2) : tws_lo(c3); }, p);
+    sstage<NP>(x0, x1, 8, [&](int k) {
+        const int g = k & 7;            // Tws 7 + g
+        return g == 0 ? tws_hi(c3) : g == 1 ? tws_lo(c4) : g == 2 ? tws_hi(c4) : g == 3 ? tws_lo(c5) : g == 4 ? tws_hi(c5)
+             : g == 5 ? tws_lo(c6) : g == 6 ? tws_hi(c6) : tws_lo(c7); }, p);
+}
+// I3: register strides 4 (t = 256, Tws 0..3) then 8 (t = 512, Tws 4..11) from six vectors, then the
+// sixteen scale factors from eight vectors
+template <int NP, class LD, class LS>
+B2_HD void spass_inv3(int32_t (&x0)[16], int32_t (&x1)[16], LD ld, LS ls, const int32_t p)
+{
+    const V4 c0 = ld(0), c1 = ld(1);
+    sstage<NP>(x0, x1, 4, [&](int k) { const int g = k & 3; return g == 0 ? tws_lo(c0) : g == 1 ? tws_hi(c0) : g == 2 ? tws_lo(c1) : tws_hi(c1); }, p);
+    const V4 c2 = ld(2), c3 = ld(3), c4 = ld(4), c5 = ld(5);
+    sstage<NP>(x0, x1, 8, [&](int k) {
+        const int g = k & 7;            // Tws 4 + g
+        return g == 0 ? tws_lo(c2) : g == 1 ? tws_hi(c2) : g == 2 ? tws_lo(c3) : g == 3 ? tws_hi(c3) : g == 4 ? tws_lo(c4)
+             : g == 5 ? tws_hi(c4) : g == 6 ? tws_lo(c5) : tws_hi(c5); }, p);
 #pragma unroll
-    for (int k = 0; k < 16; k++)
-        if ((k & 4) == 0) sbfly<SOL>(x[k], x[k + 4], tw(k & 3), p, sk);
-#pragma unroll
-    for (int k = 0; k < 8; k++) sbfly<SOL>(x[k], x[k + 8], tw(4 + k), p, sk);
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const Tws f = tws_of(sv, k);
-        x[k] = sshoup<SOLSC>(x[k], f.w, f.ws, p, sk);
+    for (int v = 0; v < 8; v++) {
+        const V4 f = ls(v);
+        x0[2 * v] = sshoup(x0[2 * v], f.x, f.y, p);
+        x0[2 * v + 1] = sshoup(x0[2 * v + 1], f.z, f.w, p);
+        if (NP == 2) {
+            x1[2 * v] = sshoup(x1[2 * v], f.x, f.y, p);
+            x1[2 * v + 1] = sshoup(x1[2 * v + 1], f.z, f.w, p);
+        }
     }
 }
 

@@ -3,7 +3,7 @@
 // exchange maps, thread by thread, checked against the oracle's exact CMUX step and the schoolbook
 // product.  Also checks (a) that every exchange store/load is shared-memory bank-conflict free
 // under the 32-bit / 128-bit access rules, (b) the lazy-residue bounds by interval propagation
-// over the real butterfly structure, (c) SOL and IMAD forms of the butterfly are bit-identical.
+// over the real butterfly structure, (c) the Solinas and IMAD forms of q*p are bit-identical.
 // Test infrastructure only.
 #include <algorithm>
 #include <cmath>
@@ -97,57 +97,43 @@ static void track(const Team x, int64_t& m)
         for (int k = 0; k < 16; k++) m = std::max<int64_t>(m, std::llabs((long long)x[t][k]));
 }
 
-template <bool SOL>
 static void fwd_tail(Team x, int q)   // after stages 0, 1 (layout A): layout C out
 {
     const int32_t p = (int32_t)kP[q];
+    int32_t dummy[16];
     xchg_AD(x);
-    for (int t = 0; t < 64; t++) {
-        V4 tv[8];
-        for (int v = 0; v < 8; v++) tv[v] = L.f2[q][t >> 4][v];
-        spass_fwd<SOL>(x[t], tv, p, kSolK[q]);
-    }
+    for (int t = 0; t < 64; t++) spass_fwd<1>(x[t], dummy, [&](int v) { return L.f2[q][t >> 4][v]; }, p);
     track(x, g_maxabs_fwd);
     xchg_DC(x);
-    for (int t = 0; t < 64; t++) {
-        V4 tv[8];
-        for (int v = 0; v < 8; v++) tv[v] = L.f3[q][v][t];
-        spass_fwd<SOL>(x[t], tv, p, kSolK[q]);
-    }
+    for (int t = 0; t < 64; t++) spass_fwd<1>(x[t], dummy, [&](int v) { return L.perT[q][kVecF3 + v][t]; }, p);
     track(x, g_maxabs_fwd);
 }
-template <bool SOL>
 static void fwd_digits(Team x, int q)   // raw digits in [0, 256), layout A
 {
-    for (int t = 0; t < 64; t++) spass_digits(x[t], L.lut1[q], L.lut24[q], L.lut35[q]);
-    fwd_tail<SOL>(x, q);
+    for (int t = 0; t < 64; t++) {
+        for (int k = 0; k < 4; k++) x[t][k] -= 128;          // slot k holds the signed digit, the others the raw byte (table handle)
+        spass_digits(x[t], [&](int32_t d) { return L.lut[q][0][d].x; }, [&](int32_t d) { return L.lut[q][1][d]; },
+                     [&](int32_t d) { return L.lut[q][2][d]; });
+    }
+    fwd_tail(x, q);
 }
-template <bool SOL>
 static void fwd_general(Team x, int q)  // centred residues, layout A
 {
     for (int t = 0; t < 64; t++) spass_fwd01(x[t], C.fw01[q][0], C.fw01[q][1], C.fw01[q][2], (int32_t)kP[q]);
-    fwd_tail<SOL>(x, q);
+    fwd_tail(x, q);
 }
-template <bool SOL>
 static void inv(Team x, int q)   // layout C in, layout A out, [-p/4, 5p/4)
 {
     const int32_t p = (int32_t)kP[q];
-    for (int t = 0; t < 64; t++) spass_inv<SOL, true>(x[t], [&](int i) { return C.iv1[q][i]; }, p, kSolK[q]);
+    int32_t dummy[16];
+    for (int t = 0; t < 64; t++) spass_inv1<1>(x[t], dummy, [&](int i) { return C.iv1[q][i]; }, p);
     track(x, g_maxabs_inv);
     xchg_DC(x);
-    for (int t = 0; t < 64; t++) {
-        V4 tv[8];
-        for (int v = 0; v < 8; v++) tv[v] = L.i2[q][v][t & 15];
-        spass_inv<SOL, false>(x[t], [&](int i) { return tws_of(tv, i); }, p, kSolK[q]);
-    }
+    for (int t = 0; t < 64; t++) spass_inv2<1>(x[t], dummy, [&](int v) { return L.i2[q][v][t & 15]; }, p);
     track(x, g_maxabs_inv);
     xchg_DA(x);
-    for (int t = 0; t < 64; t++) {
-        V4 tv[6], sv[8];
-        for (int v = 0; v < 6; v++) tv[v] = L.i3[q][v][t];
-        for (int v = 0; v < 8; v++) sv[v] = L.sc[q][v][t];
-        spass_inv3<SOL, SOL>(x[t], tv, sv, p, kSolK[q]);
-    }
+    for (int t = 0; t < 64; t++)
+        spass_inv3<1>(x[t], dummy, [&](int v) { return L.perT[q][kVecI3 + v][t]; }, [&](int v) { return L.perT[q][kVecSc + v][t]; }, p);
 }
 
 // key polynomial -> NTT domain, Montgomery form in [0, p), bk16_slot order
@@ -157,7 +143,7 @@ static void key_to_ntt(uint32_t* dst, const uint32_t* src, int q)
     const uint32_t p = kP[q];
     for (int t = 0; t < 64; t++)
         for (int k = 0; k < 16; k++) x[t][k] = h_centre(src[eA(t, k)] % p, p);
-    fwd_general<false>(x, q);
+    fwd_general(x, q);
     for (int t = 0; t < 64; t++)
         for (int k = 0; k < 16; k++) {
             int32_t m = smontmul1(x[t][k], (uint32_t)C.r2[q] + (C.r2[q] < 0 ? p : 0), (int32_t)p, q ? Prime<1>::pinv : Prime<0>::pinv);
@@ -166,7 +152,6 @@ static void key_to_ntt(uint32_t* dst, const uint32_t* src, int q)
         }
 }
 
-template <bool SOL>
 static int check_polymul(std::mt19937_64& rng)
 {
     uint32_t a[kN], b[kN], ref[kN], out[kN];
@@ -178,11 +163,11 @@ static int check_polymul(std::mt19937_64& rng)
         key_to_ntt(an[q], a, q);
         for (int t = 0; t < 64; t++)
             for (int k = 0; k < 16; k++) x[q][t][k] = (int32_t)b[eA(t, k)] + 128;        // raw digit
-        fwd_digits<SOL>(x[q], q);
+        fwd_digits(x[q], q);
         for (int t = 0; t < 64; t++)
             for (int k = 0; k < 16; k++)
                 x[q][t][k] = smontmul1(x[q][t][k], an[q][bk16_slot(t, k)], (int32_t)kP[q], q ? Prime<1>::pinv : Prime<0>::pinv);
-        inv<SOL>(x[q], q);
+        inv(x[q], q);
     }
     for (int t = 0; t < 64; t++)
         for (int k = 0; k < 16; k++) out[eA(t, k)] = scrt_lift32(x[0][t][k], x[1][t][k], C.crt.w, C.crt.ws);
@@ -191,7 +176,6 @@ static int check_polymul(std::mt19937_64& rng)
 
 // one CMUX step exactly as k_blind_rotate_s runs it: digits of acc_j transformed in pairs, row pairs
 // share one Montgomery reduction, both outputs inverse-transformed, CRT, accumulate
-template <bool SOL>
 static int check_cmux(std::mt19937_64& rng, int worst)
 {
     static uint32_t bk[8 * kN], bkn[2][8 * kN], acc[2 * kN], ref[2 * kN];
@@ -216,8 +200,8 @@ static int check_cmux(std::mt19937_64& rng, int worst)
             Team x0, x1;
             for (int t = 0; t < 64; t++)
                 for (int k = 0; k < 16; k++) { x0[t][k] = dig[0][eA(t, k)]; x1[t][k] = dig[1][eA(t, k)]; }
-            fwd_digits<SOL>(x0, q);
-            fwd_digits<SOL>(x1, q);
+            fwd_digits(x0, q);
+            fwd_digits(x1, q);
             const uint32_t pinv = q ? Prime<1>::pinv : Prime<0>::pinv;
             for (int o = 0; o < 2; o++)
                 for (int t = 0; t < 64; t++)
@@ -229,7 +213,7 @@ static int check_cmux(std::mt19937_64& rng, int worst)
         }
     }
     for (int o = 0; o < 2; o++) {
-        for (int q = 0; q < 2; q++) { track(s[q][o], g_maxabs_inv); inv<SOL>(s[q][o], q); }
+        for (int q = 0; q < 2; q++) { track(s[q][o], g_maxabs_inv); inv(s[q][o], q); }
         for (int t = 0; t < 64; t++)
             for (int k = 0; k < 16; k++) acc[o * kN + eA(t, k)] += scrt_lift32(s[0][o][t][k], s[1][o][t][k], C.crt.w, C.crt.ws);
     }
@@ -286,7 +270,7 @@ static int check_primitives(std::mt19937_64& rng)
         const Tws t = h_tws((uint32_t)(rng() % kP[q]), kP[q]);
         int32_t v = it < 8 ? (it & 2 ? INT32_MIN : INT32_MAX) : (int32_t)rng();
         const int32_t vr = v / 17 * 16;          // sreduce is specified for |v| < 2^31 - 2^26
-        const int32_t r0 = sshoup<false>(v, t.w, t.ws, p, kSolK[q]), r1 = sshoup<true>(v, t.w, t.ws, p, kSolK[q]);
+        const int32_t r0 = sshoup(v, t.w, t.ws, p), r1 = sshoup_solinas(v, t.w, t.ws, kSolK[q]);
         const int64_t want = (((int64_t)v * t.w) % p + p) % p;
         if (r0 != r1) bad++;
         if (((int64_t)r0 % p + p) % p != want) bad++;
@@ -313,9 +297,9 @@ int main(int argc, char** argv)
     const int bad_p = check_primitives(rng);
     printf("primitive mismatches (SOL == IMAD form, residues, ranges): %d\n", bad_p);
     int bad_m = 0, bad_c = 0;
-    for (int i = 0; i < trials; i++) bad_m += (i & 1) ? check_polymul<true>(rng) : check_polymul<false>(rng);
+    for (int i = 0; i < trials; i++) bad_m += check_polymul(rng);
     printf("polymul mismatches: %d / %d\n", bad_m, trials);
-    for (int i = 0; i < trials; i++) bad_c += (i & 1) ? check_cmux<true>(rng, i % 4 == 3) : check_cmux<false>(rng, i % 4 == 2);
+    for (int i = 0; i < trials; i++) bad_c += check_cmux(rng, i % 4 == 3);
     printf("cmux mismatches: %d / %d\n", bad_c, trials);
     printf("bank conflicts: %d\n", g_conflicts);
     const double bf = bound_forward();

@@ -9,10 +9,10 @@
 using namespace b2;
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %d\n", cudaGetErrorString(e_), __LINE__); exit(1); } } while (0)
 
-template <int G, int SOLM, int ABL>
+template <int G, int ABL>
 static float run(const char* name, BrParams P, const TeamSTables* tabs, int reps = 2)
 {
-    auto kern = k_blind_rotate_s<G, SOLM, false, ABL>;
+    auto kern = k_blind_rotate_s<G, false, ABL>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(G)));
     cudaEvent_t a, b;
     CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
@@ -27,8 +27,8 @@ static float run(const char* name, BrParams P, const TeamSTables* tabs, int reps
         float ms; CK(cudaEventElapsedTime(&ms, a, b));
         if (r && ms < best) best = ms;
     }
-    printf("{\"probe\": \"ablate\", \"gates_per_cta\": %d, \"solinas_mask\": %d, \"ablate_mask\": %d, \"what\": \"%s\", \"count\": %d, \"ms\": %.3f, \"gates_per_s\": %.0f}\n",
-           G, SOLM, ABL, name, P.count, best, P.count / best * 1e3);
+    printf("{\"probe\": \"ablate\", \"gates_per_cta\": %d, \"ablate_mask\": %d, \"what\": \"%s\", \"count\": %d, \"ms\": %.3f, \"gates_per_s\": %.0f}\n",
+           G, ABL, name, P.count, best, P.count / best * 1e3);
     fflush(stdout);
     return best;
 }
@@ -52,19 +52,15 @@ int main(int argc, char** argv)
     CK(cudaMalloc(&dout, (size_t)count * kLvl1Words * 4));
     BrParams P{};
     P.in0 = dct; P.out = dout; P.bk = dbk; P.count = count; P.ca = 1; P.cb = 0; P.off = 0; P.mu = kMu1;
-#define R(S, A, name) run<4, S, A>(name, P, tabs)
-    R(0, 0, "full kernel");
-    R(0, ABL_LUT, "conflict-free table look-ups");
-    R(0, ABL_DIG, "no rotation/decomposition");
-    R(0, ABL_KEY, "no key loads");
-    R(0, ABL_BAR, "no barriers");
-    R(0, ABL_TWD, "no twiddle loads");
-    R(0, ABL_XCH, "no exchanges (still barriers)");
-    R(0, ABL_XCH | ABL_BAR, "no exchanges, no barriers");
-    R(0, ABL_FMA, "no multiplies (data movement + ALU only)");
-    R(0, ABL_LUT | ABL_DIG | ABL_KEY | ABL_BAR | ABL_XCH | ABL_TWD, "multiplies only (butterflies + key products + CRT)");
-    R(0, ABL_LUT | ABL_KEY | ABL_TWD, "no conflicts, no key loads, no twiddle loads");
-    R(63, ABL_LUT | ABL_DIG | ABL_KEY | ABL_BAR | ABL_XCH | ABL_TWD, "multiplies only, all Solinas");
-    R(3, ABL_LUT | ABL_DIG | ABL_KEY | ABL_BAR | ABL_XCH | ABL_TWD, "multiplies only, Solinas F2|F3");
+#define R(A, name) run<4, A>(name, P, tabs)
+    R(0, "full kernel");
+    R(ABL_LUT, "conflict-free table look-ups");
+    R(ABL_DIG, "no rotation/decomposition");
+    R(ABL_KEY, "no key loads");
+    R(ABL_BAR, "no barriers");
+    R(ABL_TWD, "no twiddle loads");
+    R(ABL_XCH, "no exchanges (still barriers)");
+    R(ABL_LUT | ABL_DIG | ABL_KEY | ABL_BAR | ABL_XCH | ABL_TWD, "multiplies only (butterflies + key products + CRT)");
+    R(ABL_LUT | ABL_KEY | ABL_TWD, "no conflicts, no key loads, no twiddle loads");
     return 0;
 }

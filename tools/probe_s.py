@@ -19,7 +19,7 @@ keys = orc.Keys(20261104)
 cf.SetGPUNum(1)
 cf.Initialize(keys.bk, keys.ksk)
 rng = np.random.default_rng(0)
-MASKS = {40: 0, 41: 1, 42: 2, 43: 3, 44: 24, 45: 27, 46: 59, 47: 63}
+MASKS = {40: 0}
 variants = [int(v) for v in sys.argv[2].split(",")] if len(sys.argv) > 2 else sorted(MASKS)
 
 
