@@ -257,53 +257,69 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, c
         const uint32_t abar = s_abar[i];
         const uint32_t rot0 = own0 - 4 * (abar & (kN - 1));
         const bool flip = (abar >> kNbit) != 0;
-        int32_t sa[16], sb[16];
+        // the four digit polynomials of the step: (y0, y1) = digits of acc_0, (x0, x1) = digits of acc_1
+        int32_t y0[16], y1[16], x0[16], x1[16];
+        if (ABL & ABL_DIG) {
 #pragma unroll
-        for (int k = 0; k < 16; k++) sa[k] = sb[k] = 0;
-#pragma unroll 1
-        for (int j = 0; j < 2; j++) {
-            int32_t x0[16], x1[16];
-            if (ABL & ABL_DIG) {
-#pragma unroll
-                for (int k = 0; k < 16; k++) {
-                    const uint32_t t = ((uint32_t)lds32<0>(own0 + j * 8192 + 256 * k) & dbg) + (uint32_t)(T + 5 * k);
-                    x0[k] = k < 4 ? (int32_t)(t & 0xFFu) - 128 : (int32_t)(a.lut + ((t & 0xFFu) << 3));
-                    x1[k] = k < 4 ? (int32_t)((t + 7u) & 0xFFu) - 128 : (int32_t)(a.lut + (((t + 7u) & 0xFFu) << 3));
-                }
-            } else if (flip) digits_dev<true>(x0, x1, own0 + j * 8192, rot0 + j * 8192, a.lut);
-            else digits_dev<false>(x0, x1, own0 + j * 8192, rot0 + j * 8192, a.lut);
-            if (ABL & ABL_LUT) {
-#pragma unroll
-                for (int k = 4; k < 16; k++) {
-                    x0[k] = (int32_t)((((uint32_t)x0[k] - a.lut) & dbg) + a.lut + 8 * ((T & 31) | ((k & 7) << 5)));
-                    x1[k] = (int32_t)((((uint32_t)x1[k] - a.lut) & dbg) + a.lut + 8 * ((T & 31) | (((k + 3) & 7) << 5)));
-                }
+            for (int k = 0; k < 16; k++) {
+                const uint32_t t = ((uint32_t)lds32<0>(own0 + 256 * k) & dbg) + (uint32_t)(T + 5 * k);
+                y0[k] = k < 4 ? (int32_t)(t & 0xFFu) - 128 : (int32_t)(a.lut + ((t & 0xFFu) << 3));
+                y1[k] = k < 4 ? (int32_t)((t + 7u) & 0xFFu) - 128 : (int32_t)(a.lut + (((t + 7u) & 0xFFu) << 3));
             }
-            sfwd2_dev<ABL>(x0, x1, a, p, tbar, j != 0, T);       // j = 0 follows the step's closing barrier
-            const uint4* row1 = row0 + 4 * (kN / 4);
+        } else if (flip) digits_dev<true>(y0, y1, own0, rot0, a.lut);
+        else digits_dev<false>(y0, y1, own0, rot0, a.lut);
+        if (ABL & ABL_LUT) {
 #pragma unroll
-            for (int v = 0; v < 4; v++) {
-                uint4 b0, b1;
-                if (ABL & ABL_KEY) { b0 = make_uint4(i + v, j + 5, T, p - v); b1 = make_uint4(T + v, i, 9 + j, p - 2 * v); }
-                else { b0 = __ldg(row0 + off_a + v * 64); b1 = __ldg(row1 + off_a + v * 64); }
-                sa[4 * v + 0] += smontmul2(x0[4 * v + 0], b0.x, x1[4 * v + 0], b1.x, p, pinv);
-                sa[4 * v + 1] += smontmul2(x0[4 * v + 1], b0.y, x1[4 * v + 1], b1.y, p, pinv);
-                sa[4 * v + 2] += smontmul2(x0[4 * v + 2], b0.z, x1[4 * v + 2], b1.z, p, pinv);
-                sa[4 * v + 3] += smontmul2(x0[4 * v + 3], b0.w, x1[4 * v + 3], b1.w, p, pinv);
+            for (int k = 4; k < 16; k++) {
+                y0[k] = (int32_t)((((uint32_t)y0[k] - a.lut) & dbg) + a.lut + 8 * ((T & 31) | ((k & 7) << 5)));
+                y1[k] = (int32_t)((((uint32_t)y1[k] - a.lut) & dbg) + a.lut + 8 * ((T & 31) | (((k + 3) & 7) << 5)));
             }
-#pragma unroll
-            for (int v = 0; v < 4; v++) {
-                uint4 b0, b1;
-                if (ABL & ABL_KEY) { b0 = make_uint4(i + v, j + 5, T, p - v); b1 = make_uint4(T + v, i, 9 + j, p - 2 * v); }
-                else { b0 = __ldg(row0 + off_b + v * 64); b1 = __ldg(row1 + off_b + v * 64); }
-                sb[4 * v + 0] += smontmul2(x0[4 * v + 0], b0.x, x1[4 * v + 0], b1.x, p, pinv);
-                sb[4 * v + 1] += smontmul2(x0[4 * v + 1], b0.y, x1[4 * v + 1], b1.y, p, pinv);
-                sb[4 * v + 2] += smontmul2(x0[4 * v + 2], b0.z, x1[4 * v + 2], b1.z, p, pinv);
-                sb[4 * v + 3] += smontmul2(x0[4 * v + 3], b0.w, x1[4 * v + 3], b1.w, p, pinv);
-            }
-            row0 += 2 * 4 * (kN / 4);
         }
-        if (ROW0) row0 = bk4;                            // timing experiment: key row 0 at every step
+        sfwd2_dev<ABL>(y0, y1, a, p, tbar, false, T);        // follows the step's closing barrier
+        if (ABL & ABL_DIG) {
+#pragma unroll
+            for (int k = 0; k < 16; k++) {
+                const uint32_t t = ((uint32_t)lds32<8192>(own0 + 256 * k) & dbg) + (uint32_t)(T + 3 * k);
+                x0[k] = k < 4 ? (int32_t)(t & 0xFFu) - 128 : (int32_t)(a.lut + ((t & 0xFFu) << 3));
+                x1[k] = k < 4 ? (int32_t)((t + 7u) & 0xFFu) - 128 : (int32_t)(a.lut + (((t + 7u) & 0xFFu) << 3));
+            }
+        } else if (flip) digits_dev<true>(x0, x1, own0 + 8192, rot0 + 8192, a.lut);
+        else digits_dev<false>(x0, x1, own0 + 8192, rot0 + 8192, a.lut);
+        if (ABL & ABL_LUT) {
+#pragma unroll
+            for (int k = 4; k < 16; k++) {
+                x0[k] = (int32_t)((((uint32_t)x0[k] - a.lut) & dbg) + a.lut + 8 * ((T & 31) | ((k & 7) << 5)));
+                x1[k] = (int32_t)((((uint32_t)x1[k] - a.lut) & dbg) + a.lut + 8 * ((T & 31) | (((k + 3) & 7) << 5)));
+            }
+        }
+        sfwd2_dev<ABL>(x0, x1, a, p, tbar, true, T);
+        // key multiply: the four row products of an output coefficient are summed in 64 bits (< 2^33 p)
+        // and reduced ONCE; out 1-q first (its inverse transform input is sb), then out q
+        int32_t sa[16], sb[16];
+        const uint4* r1 = row0 + 4 * (kN / 4);
+        const uint4* r2 = row0 + 8 * (kN / 4);
+        const uint4* r3 = row0 + 12 * (kN / 4);
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+            uint4 b0, b1, b2, b3;
+            if (ABL & ABL_KEY) { b0 = make_uint4(i + v, 5, T, p - v); b1 = make_uint4(T + v, i, 9, p - 2 * v); b2 = make_uint4(i, T, v, p - 5); b3 = make_uint4(v, v + i, T, p - 6); }
+            else { b0 = __ldg(row0 + off_b + v * 64); b1 = __ldg(r1 + off_b + v * 64); b2 = __ldg(r2 + off_b + v * 64); b3 = __ldg(r3 + off_b + v * 64); }
+            sb[4 * v + 0] = smontmul4(y0[4 * v + 0], b0.x, y1[4 * v + 0], b1.x, x0[4 * v + 0], b2.x, x1[4 * v + 0], b3.x, p, pinv);
+            sb[4 * v + 1] = smontmul4(y0[4 * v + 1], b0.y, y1[4 * v + 1], b1.y, x0[4 * v + 1], b2.y, x1[4 * v + 1], b3.y, p, pinv);
+            sb[4 * v + 2] = smontmul4(y0[4 * v + 2], b0.z, y1[4 * v + 2], b1.z, x0[4 * v + 2], b2.z, x1[4 * v + 2], b3.z, p, pinv);
+            sb[4 * v + 3] = smontmul4(y0[4 * v + 3], b0.w, y1[4 * v + 3], b1.w, x0[4 * v + 3], b2.w, x1[4 * v + 3], b3.w, p, pinv);
+        }
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+            uint4 b0, b1, b2, b3;
+            if (ABL & ABL_KEY) { b0 = make_uint4(i + v, 5, T, p - v); b1 = make_uint4(T + v, i, 9, p - 2 * v); b2 = make_uint4(i, T, v, p - 5); b3 = make_uint4(v, v + i, T, p - 6); }
+            else { b0 = __ldg(row0 + off_a + v * 64); b1 = __ldg(r1 + off_a + v * 64); b2 = __ldg(r2 + off_a + v * 64); b3 = __ldg(r3 + off_a + v * 64); }
+            sa[4 * v + 0] = smontmul4(y0[4 * v + 0], b0.x, y1[4 * v + 0], b1.x, x0[4 * v + 0], b2.x, x1[4 * v + 0], b3.x, p, pinv);
+            sa[4 * v + 1] = smontmul4(y0[4 * v + 1], b0.y, y1[4 * v + 1], b1.y, x0[4 * v + 1], b2.y, x1[4 * v + 1], b3.y, p, pinv);
+            sa[4 * v + 2] = smontmul4(y0[4 * v + 2], b0.z, y1[4 * v + 2], b1.z, x0[4 * v + 2], b2.z, x1[4 * v + 2], b3.z, p, pinv);
+            sa[4 * v + 3] = smontmul4(y0[4 * v + 3], b0.w, y1[4 * v + 3], b1.w, x0[4 * v + 3], b2.w, x1[4 * v + 3], b3.w, p, pinv);
+        }
+        if (!ROW0) row0 += 16 * (kN / 4);                // timing experiment ROW0: key row 0 at every step
         sinv2_dev<ABL>(sb, sa, a, q, p, tbar, T);
         // sa = INTT(out q) (mine), sb = INTT(out 1-q): hand sb to the other team through my own chunk
         sts128<0>(a.own, sb[0], sb[1], sb[2], sb[3]);

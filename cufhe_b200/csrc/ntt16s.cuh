@@ -106,6 +106,15 @@ B2_HD int32_t smontmul2(int32_t a0, uint32_t b0, int32_t a1, uint32_t b1, int32_
     const int32_t m = (int32_t)((uint32_t)prod * pinv);
     return (int32_t)(prod >> 32) - smulhi(m, p);
 }
+// all four TRGSW rows in one reduction: |sum| < 2^33 p, |result| < |sum| / 2^32 + p/2
+B2_HD int32_t smontmul4(int32_t a0, uint32_t b0, int32_t a1, uint32_t b1, int32_t a2, uint32_t b2, int32_t a3, uint32_t b3,
+                        int32_t p, uint32_t pinv)
+{
+    const int64_t prod = (int64_t)a0 * (int64_t)(int32_t)b0 + (int64_t)a1 * (int64_t)(int32_t)b1 +
+                         (int64_t)a2 * (int64_t)(int32_t)b2 + (int64_t)a3 * (int64_t)(int32_t)b3;
+    const int32_t m = (int32_t)((uint32_t)prod * pinv);
+    return (int32_t)(prod >> 32) - smulhi(m, p);
+}
 B2_HD int32_t smontmul1(int32_t a0, uint32_t b0, int32_t p, uint32_t pinv)
 {
     const int64_t prod = (int64_t)a0 * (int64_t)(int32_t)b0;
