@@ -35,7 +35,7 @@ template <int G> int launch_brs_g(const DevCtx& c, const BrParams& P, cudaStream
 int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
 {
     if (P.count <= 0) return 0;
-    const int variant = g_br_variant ? g_br_variant : 19;
+    const int variant = g_br_variant ? g_br_variant : 40;
     int g = g_gates_per_cta;
     const int per_sm = (P.count + c.sm_count - 1) / c.sm_count;
     // The two latency kernels spend several SMs (or a whole SM) on one gate: right for an
@@ -77,13 +77,28 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
         LAUNCHED();
         return 0;
     }
-    if (variant == 40 || variant == 48) {      // second generation (signed residues, vector exchanges, doubled accumulator)
+    if (variant == 40 || variant == 48) {      // second generation (signed residues, vector exchanges, doubled accumulator): the default
         P.bk = c.bk_ntt16;
         if (variant == 48) {      // key row 0 at every step (timing experiment: key traffic vs arithmetic; wrong results)
             const int grid = (P.count - P.first + 3) / 4;
             k_blind_rotate_s<4, true><<<grid, 512, brs_smem_bytes(4), st>>>(P, c.tabs);
             LAUNCHED();
             return 0;
+        }
+        if (g == 0 && g_br_tail_split) {
+            // Waves of 4 gates per SM take the same time whether full or not; a last partial wave of at
+            // most 3 gates per SM runs as its own launch with fewer gates per CTA.
+            const int wave = 4 * c.sm_count;
+            const int full = (P.count / wave) * wave, rest = P.count - full;
+            if (full > 0 && rest > 0 && rest <= 3 * c.sm_count) {
+                BrParams M = P;
+                M.count = full;
+                if (int r = launch_brs_g<4>(c, M, st)) return r;
+                P.first = full;
+                // 1 or 2 gates per SM: one-gate CTAs (two fit an SM)
+                if (rest <= 2 * c.sm_count) return launch_brs_g<1>(c, P, st);
+                return launch_brs_g<3>(c, P, st);
+            }
         }
         if (g == 0) g = per_sm >= 4 ? 4 : per_sm == 3 ? 3 : 1;
         switch (g) {

@@ -74,6 +74,20 @@ template <int OFF> __device__ __forceinline__ void sts128(uint32_t a, int32_t x,
     asm volatile("st.shared.v4.s32 [%0 + %1], {%2, %3, %4, %5};" ::"r"(a), "n"(OFF), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
 
+// key vector load flavours (A/B in tools/ablate_brs.cu): 0 = ld.global.nc (through L1), 1 = ld.global.cg (L2 only),
+// 2 = ld.global.cs (streaming), 3 = ld.global.nc.L1::no_allocate
+template <int KEYLD> __device__ __forceinline__ uint4 ld_key(const uint4* p)
+{
+    if (KEYLD == 1) return __ldcg(p);
+    if (KEYLD == 2) return __ldcs(p);
+    if (KEYLD == 3) {
+        uint4 r;
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+        return r;
+    }
+    return __ldg(p);
+}
+
 struct SAddr {              // per-thread shared-window byte addresses
     uint32_t own;           // chunk_of(T) in array 0 of my team; array 1 = + 4 kXsWords
     uint32_t vw;            // vector scatter base 20 (T&15) + 4 (T>>4) words  (+ 336 words per kh)   A->D, D->A
@@ -240,7 +254,7 @@ __device__ __forceinline__ void acc_update(const uint32_t mine, const int32_t (&
 
 // One code copy serves both primes (q is team-uniform).  sa = residues of output polynomial q
 // ("mine", finished by this team), sb = residues of output polynomial 1-q (handed over).
-template <bool ROW0, int ABL>
+template <bool ROW0, int ABL, int KEYLD>
 __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, const uint32_t accb, const SAddr& a,
                                               const uint16_t* s_abar, const int T, const int q, const int tbar, const int gbar,
                                               const uint32_t dbg)
@@ -303,7 +317,7 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, c
         for (int v = 0; v < 4; v++) {
             uint4 b0, b1, b2, b3;
             if (ABL & ABL_KEY) { b0 = make_uint4(i + v, 5, T, p - v); b1 = make_uint4(T + v, i, 9, p - 2 * v); b2 = make_uint4(i, T, v, p - 5); b3 = make_uint4(v, v + i, T, p - 6); }
-            else { b0 = __ldg(row0 + off_b + v * 64); b1 = __ldg(r1 + off_b + v * 64); b2 = __ldg(r2 + off_b + v * 64); b3 = __ldg(r3 + off_b + v * 64); }
+            else { b0 = ld_key<KEYLD>(row0 + off_b + v * 64); b1 = ld_key<KEYLD>(r1 + off_b + v * 64); b2 = ld_key<KEYLD>(r2 + off_b + v * 64); b3 = ld_key<KEYLD>(r3 + off_b + v * 64); }
             sb[4 * v + 0] = smontmul4(y0[4 * v + 0], b0.x, y1[4 * v + 0], b1.x, x0[4 * v + 0], b2.x, x1[4 * v + 0], b3.x, p, pinv);
             sb[4 * v + 1] = smontmul4(y0[4 * v + 1], b0.y, y1[4 * v + 1], b1.y, x0[4 * v + 1], b2.y, x1[4 * v + 1], b3.y, p, pinv);
             sb[4 * v + 2] = smontmul4(y0[4 * v + 2], b0.z, y1[4 * v + 2], b1.z, x0[4 * v + 2], b2.z, x1[4 * v + 2], b3.z, p, pinv);
@@ -313,7 +327,7 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, c
         for (int v = 0; v < 4; v++) {
             uint4 b0, b1, b2, b3;
             if (ABL & ABL_KEY) { b0 = make_uint4(i + v, 5, T, p - v); b1 = make_uint4(T + v, i, 9, p - 2 * v); b2 = make_uint4(i, T, v, p - 5); b3 = make_uint4(v, v + i, T, p - 6); }
-            else { b0 = __ldg(row0 + off_a + v * 64); b1 = __ldg(r1 + off_a + v * 64); b2 = __ldg(r2 + off_a + v * 64); b3 = __ldg(r3 + off_a + v * 64); }
+            else { b0 = ld_key<KEYLD>(row0 + off_a + v * 64); b1 = ld_key<KEYLD>(r1 + off_a + v * 64); b2 = ld_key<KEYLD>(r2 + off_a + v * 64); b3 = ld_key<KEYLD>(r3 + off_a + v * 64); }
             sa[4 * v + 0] = smontmul4(y0[4 * v + 0], b0.x, y1[4 * v + 0], b1.x, x0[4 * v + 0], b2.x, x1[4 * v + 0], b3.x, p, pinv);
             sa[4 * v + 1] = smontmul4(y0[4 * v + 1], b0.y, y1[4 * v + 1], b1.y, x0[4 * v + 1], b2.y, x1[4 * v + 1], b3.y, p, pinv);
             sa[4 * v + 2] = smontmul4(y0[4 * v + 2], b0.z, y1[4 * v + 2], b1.z, x0[4 * v + 2], b2.z, x1[4 * v + 2], b3.z, p, pinv);
@@ -336,7 +350,7 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, c
     }
 }
 
-template <int G, bool ROW0 = false, int ABL = 0>
+template <int G, bool ROW0 = false, int ABL = 0, int KEYLD = 0>
 __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P, const TeamSTables* __restrict__ tabs)
 {
     extern __shared__ __align__(16) uint32_t smem[];
@@ -389,7 +403,7 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P,
     }
     named_bar_sync(gbar, 128);
 
-    brs_gate_loop<ROW0, ABL>(P.bk, smem_u32(acc), a, s_abar, T, q, tbar, gbar, P.dbg);
+    brs_gate_loop<ROW0, ABL, KEYLD>(P.bk, smem_u32(acc), a, s_abar, T, q, tbar, gbar, P.dbg);
 
     // ---- SampleExtract(0) (src/bootstrap_gpu.cu:366-381) ----
     const uint32_t* acc0 = acc + kN;                         // +acc_0

@@ -9,10 +9,10 @@
 using namespace b2;
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %d\n", cudaGetErrorString(e_), __LINE__); exit(1); } } while (0)
 
-template <int G, int ABL>
+template <int G, int ABL, int KEYLD = 0>
 static float run(const char* name, BrParams P, const TeamSTables* tabs, int reps = 2)
 {
-    auto kern = k_blind_rotate_s<G, false, ABL>;
+    auto kern = k_blind_rotate_s<G, false, ABL, KEYLD>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(G)));
     cudaEvent_t a, b;
     CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
@@ -53,6 +53,11 @@ int main(int argc, char** argv)
     BrParams P{};
     P.in0 = dct; P.out = dout; P.bk = dbk; P.count = count; P.ca = 1; P.cb = 0; P.off = 0; P.mu = kMu1;
 #define R(A, name) run<4, A>(name, P, tabs)
+    run<4, 0, 1>("key loads ld.global.cg", P, tabs);
+    run<4, 0, 2>("key loads ld.global.cs", P, tabs);
+    run<4, 0, 3>("key loads nc.L1::no_allocate", P, tabs);
+    run<3, 0, 0>("3 gates per CTA (12 warps, more L1)", P, tabs);
+    run<3, 0, 1>("3 gates per CTA, ld.global.cg", P, tabs);
     R(0, "full kernel");
     R(ABL_LUT, "conflict-free table look-ups");
     R(ABL_DIG, "no rotation/decomposition");
