@@ -28,6 +28,7 @@ SYMBOLS = [
     "b2fhe_defer_flush", "b2fhe_defer_fence", "b2fhe_defer_fence_buffer", "b2fhe_defer_query", "b2fhe_defer_pending", "b2fhe_blind_rotate_batch", "b2fhe_bootstrap_batch", "b2fhe_keyswitch_batch",
     "b2fhe_bootstrap_tlwe2trlwe_batch", "b2fhe_sample_extract_keyswitch_batch", "b2fhe_refresh_batch", "b2fhe_trgsw2ntt_batch", "b2fhe_cmux_ntt_batch",
     "b2fhe_ntt1024_batch", "b2fhe_intt1024_batch", "b2fhe_polymul1024_batch",
+    "b2fhe_gate_batch_noalloc", "b2fhe_noalloc_max_gates",
     "b2fhe_set_gates_per_cta", "b2fhe_set_br_variant", "b2fhe_set_ks_variant", "b2fhe_kernel_launches", "b2fhe_int_peak",
 ]
 
@@ -102,6 +103,9 @@ def lib():
     L.b2fhe_ntt1024_batch.argtypes = [i32, vp, vp, vp, sz]
     L.b2fhe_intt1024_batch.argtypes = [i32, vp, vp, vp, sz]
     L.b2fhe_polymul1024_batch.argtypes = [i32, vp, vp, vp, vp, sz]
+    L.b2fhe_gate_batch_noalloc.argtypes = [i32, vp, i32, vp, vp, vp, sz]
+    L.b2fhe_noalloc_max_gates.restype = sz
+    L.b2fhe_noalloc_max_gates.argtypes = []
     L.b2fhe_set_gates_per_cta.argtypes = [i32]
     L.b2fhe_set_br_variant.argtypes = [i32]
     L.b2fhe_set_ks_variant.argtypes = [i32]
@@ -115,7 +119,7 @@ class B2FheError(RuntimeError):
     pass
 
 
-E_NOT_INITIALIZED, E_BAD_ARGUMENT, E_NO_DEVICE, E_BAD_FORMAT = 10001, 10002, 10003, 10004   # include/b2fhe.h
+E_NOT_INITIALIZED, E_BAD_ARGUMENT, E_NO_DEVICE, E_BAD_FORMAT, E_TOO_LARGE = 10001, 10002, 10003, 10004, 10005   # include/b2fhe.h
 
 
 def check(code):

@@ -94,6 +94,8 @@ template <int G> int set_brs_attr()
     return 0;
 }
 
+int noalloc_setup(int device);   // b2fhe_noalloc.inl: device address of the fixed scratch array
+
 // twiddle tables + kernel attributes on `device` (InitializeNTThandlers, src/bootstrap_gpu.cu:97-109)
 int setup_device(int device)
 {
@@ -163,7 +165,7 @@ int setup_device(int device)
     CK(cudaFuncSetAttribute(k_ntt_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
     CK(cudaFuncSetAttribute(k_ntt_inv, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
     CK(cudaFuncSetAttribute(k_polymul, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
-    return 0;
+    return noalloc_setup(device);
 }
 
 int ntt_grid(const DevCtx& c, size_t npoly)
@@ -356,3 +358,4 @@ int b2fhe_synchronize(void)
 #include "b2fhe_gates.inl"
 #include "b2fhe_defer.inl"
 #include "b2fhe_wire.inl"
+#include "b2fhe_noalloc.inl"

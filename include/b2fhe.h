@@ -30,6 +30,7 @@ extern "C" {
 #define B2FHE_E_BAD_ARGUMENT    10002
 #define B2FHE_E_NO_DEVICE       10003
 #define B2FHE_E_BAD_FORMAT      10004   /* wire-format reader: not a blob this engine understands */
+#define B2FHE_E_TOO_LARGE       10005   /* b2fhe_gate_batch_noalloc: batch beyond the fixed scratch */
 
 /* gate op codes; (casign, cbsign, offset) per src/bootstrap_gpu.cu:424-512,590-679 */
 enum b2fhe_op {
@@ -118,6 +119,20 @@ int b2fhe_blind_rotate_batch(int device, b2fhe_stream_t stream, uint32_t* out_lv
 /* identity key switch lvl1 -> lvl0 (SampleExtractAndKeySwitch tail, src/keyswitch_gpu.cu:26-40) */
 int b2fhe_keyswitch_batch(int device, b2fhe_stream_t stream, uint16_t* out_lvl0,
                           const uint32_t* in_lvl1, size_t count);
+
+/* A gate batch that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same result as b2fhe_gate_batch(op, level 0) for the ten
+ * two-input gates (op < B2FHE_MUX), device pointers, out may alias an input; the lvl1 scratch between
+ * blind rotation and key switch lives in a fixed device array of B2FHE_NOALLOC_MAX_GATES x 4100 B
+ * (8.4 MB, held by every GPU that loads the library until exit).  count > B2FHE_NOALLOC_MAX_GATES
+ * returns B2FHE_E_TOO_LARGE.  Calls no cudaMalloc / cudaFree / allocating routine: two kernel
+ * launches on `stream`.  All calls on a device share the array: back-to-back calls on one stream are
+ * ordered, calls that OVERLAP on the GPU (different streams) race.  Needs b2fhe_init* first. */
+#define B2FHE_NOALLOC_MAX_GATES 2048
+size_t b2fhe_noalloc_max_gates(void);
+int b2fhe_gate_batch_noalloc(int device, b2fhe_stream_t stream, int op, uint16_t* out_lvl0,
+                             const uint16_t* in0_lvl0, const uint16_t* in1_lvl0, size_t count);
 
 /* Bootstrap (src/bootstrap_gpu.cu:290-301,782-789): blind rotation with a RUN-TIME test-vector
  * constant mu, SampleExtract(0), identity key switch: lvl0 TLWE -> lvl0 TLWE.  out may alias in. */
