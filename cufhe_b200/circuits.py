@@ -60,6 +60,11 @@ def ripple_carry_add(a, b, st, scratch=None):
     c = Wires(n, inst, a.level, a.device)       # c[i] = carry INTO bit i (c[0] unused)
     t = Wires(1, inst, a.level, a.device)
     s = Wires(n, inst, a.level, a.device)
+    # the temporaries are allocated on torch's CURRENT stream but used by kernels on `st`: tell the caching
+    # allocator, or their blocks could be reused while those kernels still run
+    if st._st is not None and st._st != torch.cuda.current_stream(st._st.device):
+        for w in (x, g, c, t, s):
+            w.t.record_stream(st._st)
     gates = 0
     gates += _gate("XOR", x, 0, a, 0, b, 0, st, wires=n)
     gates += _gate("AND", g, 0, a, 0, b, 0, st, wires=n - 1)     # g_{n-1} is never needed
