@@ -20,12 +20,12 @@ NVCC_FLAGS = [
 
 # every symbol include/b2fhe.h declares
 SYMBOLS = [
-    "b2fhe_init", "b2fhe_init_device", "b2fhe_adopt_keys", "b2fhe_key_pointers", "b2fhe_cleanup",
+    "b2fhe_init", "b2fhe_setup_devices", "b2fhe_init_device", "b2fhe_adopt_keys", "b2fhe_key_pointers", "b2fhe_cleanup",
     "b2fhe_num_devices", "b2fhe_last_error_string", "b2fhe_gate_batch", "b2fhe_gate_batch_mixed",
     "b2fhe_gate_batch_host", "b2fhe_wire_evalkey_size", "b2fhe_wire_evalkey_write", "b2fhe_wire_evalkey_parse",
     "b2fhe_init_from_evalkey", "b2fhe_wire_tlwes_size", "b2fhe_wire_tlwes_write", "b2fhe_wire_tlwes_parse",
     "b2fhe_key_cache_size", "b2fhe_key_cache_export", "b2fhe_init_from_key_cache", "b2fhe_synchronize", "b2fhe_gate_batch_ptrs", "b2fhe_defer_gate", "b2fhe_defer_h2d", "b2fhe_defer_d2h",
-    "b2fhe_defer_flush", "b2fhe_defer_fence", "b2fhe_defer_fence_buffer", "b2fhe_defer_query", "b2fhe_defer_pending", "b2fhe_blind_rotate_batch", "b2fhe_bootstrap_batch", "b2fhe_keyswitch_batch",
+    "b2fhe_defer_flush", "b2fhe_defer_fence", "b2fhe_defer_fence_buffer", "b2fhe_defer_query", "b2fhe_defer_query_stream", "b2fhe_defer_pending", "b2fhe_blind_rotate_batch", "b2fhe_bootstrap_batch", "b2fhe_keyswitch_batch",
     "b2fhe_bootstrap_tlwe2trlwe_batch", "b2fhe_sample_extract_keyswitch_batch", "b2fhe_refresh_batch", "b2fhe_trgsw2ntt_batch", "b2fhe_cmux_ntt_batch",
     "b2fhe_ntt1024_batch", "b2fhe_intt1024_batch", "b2fhe_polymul1024_batch",
     "b2fhe_gate_batch_noalloc", "b2fhe_noalloc_max_gates",
@@ -63,6 +63,7 @@ def lib():
     L = C.CDLL(LIB_PATH)
     vp, i32, sz = C.c_void_p, C.c_int, C.c_size_t
     L.b2fhe_init.argtypes = [i32, vp, vp]
+    L.b2fhe_setup_devices.argtypes = [i32]
     L.b2fhe_init_device.argtypes = [i32, vp, vp]
     L.b2fhe_adopt_keys.argtypes = [i32, vp, vp]
     L.b2fhe_key_pointers.argtypes = [i32, C.POINTER(vp), C.POINTER(vp)]
@@ -91,6 +92,7 @@ def lib():
     L.b2fhe_defer_fence.argtypes = [i32, vp]
     L.b2fhe_defer_fence_buffer.argtypes = [i32, vp, vp]
     L.b2fhe_defer_query.argtypes = [i32, C.POINTER(i32)]
+    L.b2fhe_defer_query_stream.argtypes = [i32, vp, C.POINTER(i32)]
     L.b2fhe_defer_pending.argtypes = [i32]
     L.b2fhe_blind_rotate_batch.argtypes = [i32, vp, vp, vp, C.c_uint32, sz]
     L.b2fhe_bootstrap_batch.argtypes = [i32, vp, vp, vp, C.c_uint32, sz]

@@ -278,6 +278,15 @@ int b2fhe_num_devices(void)
     return n;
 }
 
+int b2fhe_setup_devices(int ngpu)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    REQUIRE(ngpu >= 1 && ngpu <= kMaxDev, B2FHE_E_BAD_ARGUMENT);
+    for (int d = 0; d < ngpu; d++)
+        if (int r = setup_device(d)) return r;
+    return 0;
+}
+
 int b2fhe_init_device(int device, const uint32_t* bk_raw, const uint16_t* ksk_raw)
 {
     std::lock_guard<std::mutex> lk(g_mu);

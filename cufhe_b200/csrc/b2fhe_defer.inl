@@ -106,6 +106,7 @@ struct DeferCtx {
     std::unordered_map<const void*, size_t> d2h_index;       // host destination -> entry of d2h
     std::vector<Pinned*> pinned;                             // staging areas, reused
     std::unordered_set<const void*> produced;                // outputs of flushed gates, until the next completed wait
+    std::unordered_set<const void*> backed;                  // flushed outputs whose copy-back into the caller's host ciphertext went with them
     std::unordered_map<const void*, int> wlevel, rlevel;     // buffer -> level of its pending writer / last reader
     std::unordered_map<cudaStream_t, cudaEvent_t> seen;      // user streams with work this queue depends on
     std::vector<cudaEvent_t> pool;                           // events of flushed entries, reused
@@ -239,6 +240,10 @@ int defer_flush_body(int device, HostJob* job, bool& handed_over)
     // the user may destroy its streams after Synchronize(): keep no handle past the flush
     D.seen.clear();
     for (const Pending& p : D.q) D.produced.insert(p.out);
+    for (const PendingCopy& pc : D.d2h) {          // copy-backs taken right after the buffer's (last) producer
+        const auto w = D.wlevel.find(pc.dev);
+        if (w == D.wlevel.end() || pc.lvl == w->second + 1) D.backed.insert(pc.dev);
+    }
     return 0;
 }
 
@@ -259,11 +264,20 @@ int defer_flush(int device)
 }
 
 // after a wait that covered every flushed gate, host copies are authoritative again
-void defer_mark_idle(int device) { g_defer[device].produced.clear(); }
+void defer_mark_idle(int device) { g_defer[device].produced.clear(); g_defer[device].backed.clear(); }
 void defer_mark_idle_all()
 {
     std::lock_guard<std::mutex> lk(g_defer_mu);
-    for (int d = 0; d < kMaxDev; d++) g_defer[d].produced.clear();
+    for (int d = 0; d < kMaxDev; d++) defer_mark_idle(d);
+}
+// the caller may have waited through raw CUDA (cudaDeviceSynchronize / cudaStreamSynchronize, as the
+// reference's test/test_intensive.cc:43 does): once the last flush has completed, host copies are
+// authoritative again whoever did the waiting
+void defer_refresh_idle(DeferCtx& D, int device)
+{
+    if (D.produced.empty() || !D.done) return;
+    if (cudaEventQuery(D.done) == cudaSuccess) defer_mark_idle(device);
+    else (void)cudaGetLastError();
 }
 
 int defer_flush_all()
@@ -319,6 +333,7 @@ int b2fhe_defer_gate(int device, b2fhe_stream_t user_stream, int op, int level, 
     REQUIRE((!two && !three) || in1, B2FHE_E_BAD_ARGUMENT);
     REQUIRE(!three || in2, B2FHE_E_BAD_ARGUMENT);
     DeferCtx& D = g_defer[device];
+    defer_refresh_idle(D, device);
     // a long run of INDEPENDENT gates (the reference's benchmark loop) starts executing while the
     // caller is still issuing: two full waves of the blind-rotation kernel lose nothing by going
     // now.  Checked BEFORE queueing, so that the copy-back of every flushed gate goes with it.
@@ -367,15 +382,28 @@ int b2fhe_defer_d2h(int device, void* host_dst, const void* dev_src, size_t byte
 }
 
 /* queued host-to-device copy of a gate operand, performed when the queue runs (all of them as
- * one transfer).  Skipped when a queued gate writes `dev_dst`: the value that gate leaves on the
- * device is what the caller's host copy would hold by then (this also holds for gates already
- * running, until b2fhe_synchronize or a b2fhe_defer_query that reports idle). */
+ * one transfer).  When a queued or still-running gate writes `dev_dst`:
+ *   - if a copy-back of that buffer into the caller's host ciphertext is queued after that gate (or went
+ *     with it), host and device will agree: the upload is dropped;
+ *   - otherwise (the producer was a non-copying g* gate) the reference's stream order makes the HOST bytes
+ *     win: the queue is flushed and waited for, then the upload is queued like any other. */
 int b2fhe_defer_h2d(int device, void* dev_dst, const void* host_src, size_t bytes)
 {
     std::lock_guard<std::mutex> lk(g_defer_mu);
     REQUIRE(device >= 0 && device < kMaxDev && host_src && dev_dst && bytes % 2 == 0 && bytes < (1u << 30), B2FHE_E_BAD_ARGUMENT);
     DeferCtx& D = g_defer[device];
-    if (D.wlevel.find(dev_dst) != D.wlevel.end() || D.produced.count(dev_dst)) return 0;
+    defer_refresh_idle(D, device);
+    const auto w = D.wlevel.find(dev_dst);
+    if (w != D.wlevel.end() || D.produced.count(dev_dst)) {
+        bool agrees = w == D.wlevel.end() && D.backed.count(dev_dst) != 0;
+        if (w != D.wlevel.end())
+            for (const PendingCopy& pc : D.d2h)
+                if (pc.dev == dev_dst && pc.lvl == w->second + 1) { agrees = true; break; }
+        if (agrees) return 0;
+        if (int r = defer_flush(device)) return r;
+        if (D.done) { CK(cudaSetDevice(device)); CK(cudaEventSynchronize(D.done)); }
+        defer_mark_idle(device);
+    }
     auto it = D.h2d_index.find(dev_dst);
     if (it != D.h2d_index.end()) { D.h2d[it->second] = PendingCopy{const_cast<void*>(host_src), dev_dst, bytes}; return 0; }
     D.h2d_index.emplace(dev_dst, D.h2d.size());
@@ -420,7 +448,13 @@ int b2fhe_defer_pending(int device)
 {
     std::lock_guard<std::mutex> lk(g_defer_mu);
     if (device < 0 || device >= kMaxDev) return 0;
-    return (int)(g_defer[device].q.size() + g_defer[device].d2h.size() + g_defer[device].h2d.size());
+    DeferCtx& D = g_defer[device];
+    int inflight = 0;       // a flush that is still running may yet write a caller's host / device buffer (~Ctxt asks)
+    if (D.done) {
+        if (cudaEventQuery(D.done) == cudaErrorNotReady) inflight = 1;
+        (void)cudaGetLastError();
+    }
+    return (int)(D.q.size() + D.d2h.size() + D.h2d.size()) + inflight;
 }
 
 /* flush, then 0 = everything flushed so far has completed, 1 = still running */
@@ -438,6 +472,28 @@ int b2fhe_defer_query(int device, int* busy)
         else if (e != cudaSuccess) return fail((int)e, "cudaStreamQuery", __FILE__, __LINE__);
     }
     if (!*busy) defer_mark_idle(device);
+    return 0;
+}
+
+/* StreamQuery for ONE user stream: flushes only when `stream` itself has queued work (a polling loop over
+ * many streams -- test/test_intensive.cc:21-57 -- then keeps forming full batches instead of one-gate
+ * flushes); busy = work flushed so far is still running. */
+int b2fhe_defer_query_stream(int device, b2fhe_stream_t stream, int* busy)
+{
+    std::lock_guard<std::mutex> lk(g_defer_mu);
+    REQUIRE(device >= 0 && device < kMaxDev && busy, B2FHE_E_BAD_ARGUMENT);
+    DeferCtx& D = g_defer[device];
+    // (copies queued without any gate carry no stream: they go with the first query)
+    if (D.seen.find((cudaStream_t)stream) != D.seen.end() || (D.q.empty() && (!D.d2h.empty() || !D.h2d.empty())))
+        if (int r = defer_flush(device)) return r;
+    *busy = 0;
+    if (D.fs) {
+        CK(cudaSetDevice(device));
+        const cudaError_t e = cudaStreamQuery(D.fs);
+        if (e == cudaErrorNotReady) *busy = 1;
+        else if (e != cudaSuccess) return fail((int)e, "cudaStreamQuery", __FILE__, __LINE__);
+    }
+    if (!*busy && D.q.empty()) defer_mark_idle(device);
     return 0;
 }
 

@@ -56,6 +56,9 @@ typedef void* b2fhe_stream_t;   /* a cudaStream_t (0 = default stream) */
  * the key on GPU 0 and replicates it to GPUs 1..ngpu-1 with peer copies. */
 int b2fhe_init(int ngpu, const uint32_t* bk_raw, const uint16_t* ksk_raw);
 /* one device only (one process per GPU): device = CUDA ordinal of this process */
+/* Initialize() without keys (include/cufhe_gpu.cuh:56-57, InitializeNTThandlers src/bootstrap_gpu.cu:97-109):
+ * twiddle tables + kernel attributes on devices 0..ngpu-1.  b2fhe_init* do this themselves. */
+int b2fhe_setup_devices(int ngpu);
 int b2fhe_init_device(int device, const uint32_t* bk_raw, const uint16_t* ksk_raw);
 /* keys already converted and resident on `device` (after an NCCL broadcast of the
  * buffers produced on rank 0): adopts the pointers, does not copy or free them. */
@@ -109,6 +112,9 @@ int b2fhe_defer_fence(int device, b2fhe_stream_t stream);   /* flush; `stream` w
 int b2fhe_defer_fence_buffer(int device, b2fhe_stream_t stream, const void* buffer); /* the fence, only
                                                                if a queued gate reads or writes `buffer` */
 int b2fhe_defer_query(int device, int* busy);               /* flush; *busy = 1 while running */
+/* the same for ONE user stream (StreamQuery(st), include/cufhe_gpu.cuh:68-74): flushes only when `stream`
+ * itself has queued work; busy = flushed work still running */
+int b2fhe_defer_query_stream(int device, b2fhe_stream_t stream, int* busy);
 int b2fhe_defer_pending(int device);                        /* queued operations */
 
 /* ---- stages (next-tier entry points) ---------------------------------

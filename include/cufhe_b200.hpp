@@ -28,8 +28,10 @@
 
 namespace cufhe {
 
-inline int& _gpuNumRef() { static int n = 1; return n; }
-inline int& _streamCountRef() { static int n = 0; return n; }
+// the reference's public globals (include/cufhe_gpu.cuh:44-46, src/cufhe_gates_gpu.cu:34-36): C++17 inline
+// variables, so this header-only shim still gives ONE cufhe::_gpuNum / cufhe::streamCount per program
+inline int _gpuNum = 1;
+inline int streamCount = 0;
 
 inline void _b2check(int rc, const char* file, int line)
 {
@@ -42,17 +44,20 @@ inline void _b2check(int rc, const char* file, int line)
 
 template <class P> constexpr int _level() { return sizeof(typename P::T) == 2 ? 0 : 1; }
 
-inline void SetGPUNum(int gpuNum) { _gpuNumRef() = gpuNum; }
+inline void SetGPUNum(int gpuNum) { _gpuNum = gpuNum; }
+// Initialize NTT handlers only (include/cufhe_gpu.cuh:56-57, src/cufhe_gates_gpu.cu:40): twiddle tables and
+// kernel attributes on every device, no keys
+inline void Initialize() { B2CHECK(b2fhe_setup_devices(_gpuNum)); }
 inline void Initialize(const TFHEpp::EvalKey& ek)
 {
-    B2CHECK(b2fhe_init(_gpuNumRef(), reinterpret_cast<const uint32_t*>(&ek.getbk<TFHEpp::lvl01param>()),
+    B2CHECK(b2fhe_init(_gpuNum, reinterpret_cast<const uint32_t*>(&ek.getbk<TFHEpp::lvl01param>()),
                        reinterpret_cast<const uint16_t*>(&ek.getiksk<TFHEpp::lvl10param>())));
 }
 // Not in the reference: Initialize from the bytes of a serialised TFHEpp::EvalKey (cereal
 // portable_binary, TFHEpp/include/cloudkey.hpp:103-107 -- e.g. the tutorial's cloud.key) without
 // linking TFHEpp's loader, and from / to a cache of the converted keys (skips the conversion).
-inline void InitializeFromArchive(const void* blob, size_t len) { B2CHECK(b2fhe_init_from_evalkey(_gpuNumRef(), blob, len)); }
-inline void InitializeFromKeyCache(const void* blob, size_t len) { B2CHECK(b2fhe_init_from_key_cache(_gpuNumRef(), blob, len)); }
+inline void InitializeFromArchive(const void* blob, size_t len) { B2CHECK(b2fhe_init_from_evalkey(_gpuNum, blob, len)); }
+inline void InitializeFromKeyCache(const void* blob, size_t len) { B2CHECK(b2fhe_init_from_key_cache(_gpuNum, blob, len)); }
 inline std::vector<uint8_t> ExportKeyCache(int device = 0)
 {
     std::vector<uint8_t> blob(b2fhe_key_cache_size());
@@ -77,8 +82,8 @@ inline void SetDeferred(bool on)
 
 class Stream {
 public:
-    Stream() : st_(0), device_id_(_streamCountRef()++ % _gpuNumRef()) {}
-    explicit Stream(int device_id) : st_(0), device_id_(device_id) { _streamCountRef()++; }
+    Stream() : st_(0), device_id_(streamCount++ % _gpuNum) {}
+    explicit Stream(int device_id) : st_(0), device_id_(device_id) { streamCount++; }
     void Create()
     {
         cudaSetDevice(device_id_);
@@ -100,7 +105,7 @@ private:
 inline bool StreamQuery(Stream st)
 {
     int busy = 0;
-    B2CHECK(b2fhe_defer_query(st.device_id(), &busy));      // queued gates start now
+    B2CHECK(b2fhe_defer_query_stream(st.device_id(), (b2fhe_stream_t)st.st(), &busy));      // this stream's queued gates start now
     cudaSetDevice(st.device_id());
     return !busy && cudaStreamQuery(st.st()) == cudaSuccess;
 }
@@ -112,8 +117,8 @@ struct CtxtBatch {
     {
         const size_t bytes = count * sizeof(TFHEpp::TLWE<P>);
         cudaMallocHost((void**)&tlwehost, bytes);
-        tlwedevices.resize(_gpuNumRef());
-        for (int i = 0; i < _gpuNumRef(); i++) {
+        tlwedevices.resize(_gpuNum);
+        for (int i = 0; i < _gpuNum; i++) {
             cudaSetDevice(i);
             cudaMalloc((void**)&tlwedevices[i], bytes);
         }
@@ -140,8 +145,8 @@ struct Ctxt {
     Ctxt()
     {
         cudaHostRegister(tlwehost.data(), sizeof(tlwehost), cudaHostRegisterDefault);
-        tlwedevices.resize(_gpuNumRef());
-        for (int i = 0; i < _gpuNumRef(); i++) {
+        tlwedevices.resize(_gpuNum);
+        for (int i = 0; i < _gpuNum; i++) {
             cudaSetDevice(i);
             cudaMalloc((void**)&tlwedevices[i], sizeof(tlwehost));
         }
@@ -272,8 +277,8 @@ struct cuFHETRLWElvl1 {
     cuFHETRLWElvl1()
     {
         cudaHostRegister(trlwehost.data(), sizeof(trlwehost), cudaHostRegisterDefault);
-        trlwedevices.resize(_gpuNumRef());
-        for (int i = 0; i < _gpuNumRef(); i++) {
+        trlwedevices.resize(_gpuNum);
+        for (int i = 0; i < _gpuNum; i++) {
             cudaSetDevice(i);
             cudaMalloc((void**)&trlwedevices[i], sizeof(trlwehost));
         }
@@ -356,8 +361,8 @@ struct cuFHETRGSWNTTlvl1 {
     cuFHETRGSWNTTlvl1()
     {
         cudaHostRegister(trgswhost.data(), sizeof(trgswhost), cudaHostRegisterDefault);
-        trgswdevices.resize(_gpuNumRef());
-        for (int i = 0; i < _gpuNumRef(); i++) {
+        trgswdevices.resize(_gpuNum);
+        for (int i = 0; i < _gpuNum; i++) {
             cudaSetDevice(i);
             cudaMalloc((void**)&trgswdevices[i], sizeof(trgswhost));
         }

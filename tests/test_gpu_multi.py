@@ -123,3 +123,24 @@ def test_deferred_queue_on_second_gpu(engine, keys):
         cf.CleanUp()
         cf.SetGPUNum(1)
         cf.Initialize(keys.bk, keys.ksk)
+
+
+def test_torchrun_broadcast_parity():
+    """The one-process-per-GPU path every SCALE number comes from: torch.distributed.run --nproc-per-node 2,
+    rank 0 converts the keys, rank 1 receives them by NCCL broadcast (InitializeBroadcast -> b2fhe_adopt_keys);
+    bench.py's post-timing parity check compares gates of EVERY rank's own slice with the oracle."""
+    import json
+    import os
+    import subprocess
+    import sys
+    n = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", os.path.join(root, "bench.py"), "--gpus", "2", "--steps", "1", "--warmup", "3",
+           "--gates", "1200", "--no-extras"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=root)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    assert line["parity"]["ranks_ok"] == 2 and line["parity"]["gates_checked"] == 2 * 78

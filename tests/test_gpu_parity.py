@@ -105,6 +105,7 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     # every gates-per-CTA instantiation
     for variant, gs in ((5, (0,)), (4, (0,)), (2, (0,)), (1, (0,)), (16, (0, 1, 2, 3, 4, 5, 6)),
                         (17, (0, 3, 5)), (18, (0, 3, 5)), (19, (0, 1, 2, 3, 4, 5)), (20, (0, 3)), (21, (0, 1, 2, 3, 4)),
+                        (40, (0, 1, 2, 3, 4)),
                         (32, (0, 1, 2, 4, 6, 8))):
         cf._lib.check(L.b2fhe_set_br_variant(variant))
         for g in gs:
@@ -124,7 +125,7 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     dx = dev_u32(x)
     dks = torch.empty((cnt, 637), dtype=torch.int16, device="cuda")
     want = [orc.keyswitch(keys, x[i]) for i in range(cnt)]
-    for ks_variant in (1, 2, 10, 11, 12, 13, 14, 15, 16, 17, 18, 0):   # 16 warps per gate / one warp per gate / in-step CTAs (W x SYNCJ) / by batch size
+    for ks_variant in (1, 2, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 0):   # 16 warps per gate / one warp per gate / in-step CTAs (W x SYNCJ) / by batch size
         cf._lib.check(L.b2fhe_set_ks_variant(ks_variant))
         dks.zero_()
         cf._lib.check(L.b2fhe_keyswitch_batch(0, None, dks.data_ptr(), dx.data_ptr(), cnt))
@@ -399,3 +400,36 @@ def test_default_large_batch_paths_against_single_row_kernel(engine):
         cf._lib.check(L.b2fhe_set_br_variant(-2))
         cf._lib.check(L.b2fhe_set_br_variant(0))
         cf._lib.check(L.b2fhe_set_ks_variant(0))
+
+
+@pytest.mark.gpu
+def test_default_keyswitch_step_above_latency_threshold(engine, keys):
+    """Above 32 gates per SM the default key switch is k_keyswitch_step<16, 8> (below: k_keyswitch_lat).
+    A batch just over the threshold with a PARTIAL last CTA: every gate compared with the first-generation
+    k_keyswitch (variant 2), the first ones and the extreme rows with the oracle."""
+    cf = engine
+    L = cf._lib.lib()
+    sm = torch.cuda.get_device_properties(0).multi_processor_count
+    cnt = 32 * sm + 37                      # 4773 on a B200: 298 full CTAs of 16 gates + one of 5
+    rng = np.random.default_rng(123)
+    x = rng.integers(0, 2**32, (cnt, 1025), dtype=np.uint64).astype(np.uint32)
+    x[1, :] = 0
+    x[2, :] = 0xFFFFFFFF
+    x[cnt - 1, :] = 0x80000000
+    dx = dev_u32(x)
+    want = torch.zeros((cnt, 637), dtype=torch.int16, device="cuda")
+    got = torch.zeros_like(want)
+    try:
+        cf._lib.check(L.b2fhe_set_ks_variant(2))
+        cf._lib.check(L.b2fhe_keyswitch_batch(0, None, want.data_ptr(), dx.data_ptr(), cnt))
+        for variant in (0, 21):
+            cf._lib.check(L.b2fhe_set_ks_variant(variant))
+            got.zero_()
+            cf._lib.check(L.b2fhe_keyswitch_batch(0, None, got.data_ptr(), dx.data_ptr(), cnt))
+            torch.cuda.synchronize()
+            assert torch.equal(got, want), variant
+    finally:
+        cf._lib.check(L.b2fhe_set_ks_variant(0))
+    g = to_np(got, np.uint16)
+    for i in (0, 1, 2, 3, cnt - 1):
+        assert np.array_equal(g[i], orc.keyswitch(keys, x[i])), i

@@ -42,19 +42,23 @@ def ref_gate(L, op, level, x0, x1, x2):
 @pytest.mark.parametrize("level", [0, 1])
 def test_reference_gpu_equals_oracle_equals_engine(engine, keys, ref, level):
     cf = engine
-    cnt = 5
+    cnt, nchk = 64, 6          # 64 gates per op against the reference GPU build; the (slow) oracle on the first 6
     rng = np.random.default_rng(40 + level)
     st = cf.Stream(0).Create()
     for name in orc.OPS:
         op = orc.OP[name]
         b = [rng.integers(0, 2, cnt) for _ in range(3)]
         x = [orc.encrypt(keys, b[k], level, base_index=70000 + 1000 * op + 100 * k) for k in range(3)]
+        # ragged / edge inputs go to the reference too: all-zero ciphertext, maximal mask, all-ones
+        x[0][3, :] = 0
+        x[1][4, :-1] = 0xFFFF if level == 0 else 0xFFFFFFFF
+        x[0][5, :] = 0xFFFF if level == 0 else 0xFFFFFFFF
         unary, ternary = name in ("NOT", "COPY"), name in ("MUX", "NMUX")
         x1 = None if unary else x[1]
         x2 = x[2] if ternary else None
-        want = orc.gate_batch(keys, op, level, x[0], x1, x2)
         got_ref = ref_gate(ref, op, level, x[0], x1, x2)
-        assert np.array_equal(got_ref, want), f"{name} lvl{level}: oracle differs from the reference cuFHE GPU build"
+        want = orc.gate_batch(keys, op, level, x[0][:nchk], None if x1 is None else x1[:nchk], None if x2 is None else x2[:nchk])
+        assert np.array_equal(got_ref[:nchk], want), f"{name} lvl{level}: oracle differs from the reference cuFHE GPU build"
         cts = [cf.Ctxt(cnt, level).set(v) for v in x]
         out = cf.Ctxt(cnt, level)
         for c in cts:

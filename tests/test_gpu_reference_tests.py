@@ -1,0 +1,61 @@
+"""The reference's OWN test programs, unmodified (/root/reference/test/test_gate_gpu.cc,
+test_gate_gpu_multi.cc, test_intensive.cc, test_perf.cc + test_util.h / plain.h), compiled against this
+engine's header-only cufhe:: shim with REAL TFHEpp types (include/cufhe_b200.hpp, -DB2FHE_WITH_TFHEPP;
+`<include/cufhe_gpu.cuh>` resolves to oracle/shim) and linked with TFHEpp + libb2fhe.so by
+`make -C oracle reftests`.  The binaries are built where /root/reference exists and travel to the GPU
+box under oracle/_ref/reftests/.  This is the drop-in proof: the reference's user code, its harness and
+its truth tables, our engine underneath."""
+import os
+import re
+import subprocess
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "oracle", "_ref", "reftests")
+OUT = os.path.join(ROOT, "gpurun_out")
+
+
+def _run(name, timeout=900):
+    exe = os.path.join(BIN, name)
+    if not os.path.exists(exe):
+        pytest.skip(f"{exe} not built (needs /root/reference at build time)")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+    os.makedirs(OUT, exist_ok=True)
+    with open(os.path.join(OUT, f"r2_reftest_{name}.log"), "w") as f:
+        f.write(r.stdout + "\n--- stderr ---\n" + r.stderr)
+    assert r.returncode == 0, f"{name} exited {r.returncode}\n{r.stdout[-1500:]}\n{r.stderr[-1500:]}"
+    assert "FAIL" not in r.stdout and "FAILED" not in r.stderr, r.stdout[-2000:] + r.stderr[-500:]
+    return r.stdout
+
+
+def test_reference_test_gate_gpu():
+    """test/test_gate_gpu.cc:36-91: 13 gate types x (32 x SMs) gates, one gate per call round-robin over one
+    stream per SM, decrypted and compared with test/plain.h's truth tables."""
+    out = _run("test_gate_gpu")
+    assert out.count("PASS") == 13, out[-2000:]
+    thr = [float(x) for x in re.findall(r"Throughput: ([0-9.eE+-]+) ms/gate", out)]
+    assert len(thr) == 13
+    print("reference test_gate_gpu through the shim: ms/gate per gate type =", thr)
+
+
+def test_reference_test_intensive():
+    """test/test_intensive.cc:21-114: 1000 streams x 20 dependent launches each, progress by StreamQuery
+    polling, results read after a raw cudaDeviceSynchronize (asserts inside the program)."""
+    _run("test_intensive")
+
+
+def test_reference_test_perf():
+    """test/test_perf.cc:60-75: GateBootstrappingTLWE2TRLWElvl01NTT then a Refresh loop over TRLWEs."""
+    out = _run("test_perf")
+    assert "ms / operation" in out
+
+
+def test_reference_test_gate_gpu_multi():
+    """test/test_gate_gpu_multi.cc:36-72: the same gate test with SetGPUNum(2), streams alternating GPUs."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    out = _run("test_gate_gpu_multi")
+    assert "PASS" in out
