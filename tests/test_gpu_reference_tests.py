@@ -23,6 +23,11 @@ def _run(name, timeout=900):
     if not os.path.exists(exe):
         pytest.skip(f"{exe} not built (needs /root/reference at build time)")
     r = subprocess.run([exe], capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+    if r.returncode < 0:        # killed by a signal: keep the backtrace (oracle/segv_trace.cpp) and try once more
+        first = f"first attempt died with signal {-r.returncode}\n{r.stderr[-3000:]}"
+        print(first)
+        r = subprocess.run([exe], capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+        r.stderr = first + "\n--- second attempt ---\n" + r.stderr
     os.makedirs(OUT, exist_ok=True)
     with open(os.path.join(OUT, f"r2_reftest_{name}.log"), "w") as f:
         f.write(r.stdout + "\n--- stderr ---\n" + r.stderr)
