@@ -27,7 +27,7 @@ SYMBOLS = [
     "b2fhe_key_cache_size", "b2fhe_key_cache_export", "b2fhe_init_from_key_cache", "b2fhe_synchronize", "b2fhe_gate_batch_ptrs", "b2fhe_defer_gate", "b2fhe_defer_h2d", "b2fhe_defer_d2h",
     "b2fhe_defer_flush", "b2fhe_defer_fence", "b2fhe_defer_fence_buffer", "b2fhe_defer_query", "b2fhe_defer_query_stream", "b2fhe_defer_pending", "b2fhe_blind_rotate_batch", "b2fhe_bootstrap_batch", "b2fhe_keyswitch_batch",
     "b2fhe_bootstrap_tlwe2trlwe_batch", "b2fhe_sample_extract_keyswitch_batch", "b2fhe_refresh_batch", "b2fhe_trgsw2ntt_batch", "b2fhe_cmux_ntt_batch",
-    "b2fhe_ntt1024_batch", "b2fhe_intt1024_batch", "b2fhe_polymul1024_batch",
+    "b2fhe_ntt1024_batch", "b2fhe_intt1024_batch", "b2fhe_polymul1024_batch", "b2fhe_polymul1024_exact_batch", "b2fhe_set_latency_mode",
     "b2fhe_gate_batch_noalloc", "b2fhe_noalloc_max_gates",
     "b2fhe_set_gates_per_cta", "b2fhe_set_br_variant", "b2fhe_set_ks_variant", "b2fhe_kernel_launches", "b2fhe_int_peak",
 ]
@@ -105,6 +105,8 @@ def lib():
     L.b2fhe_ntt1024_batch.argtypes = [i32, vp, vp, vp, sz]
     L.b2fhe_intt1024_batch.argtypes = [i32, vp, vp, vp, sz]
     L.b2fhe_polymul1024_batch.argtypes = [i32, vp, vp, vp, vp, sz]
+    L.b2fhe_polymul1024_exact_batch.argtypes = [i32, vp, vp, vp, vp, sz]
+    L.b2fhe_set_latency_mode.argtypes = [i32]
     L.b2fhe_gate_batch_noalloc.argtypes = [i32, vp, i32, vp, vp, vp, sz]
     L.b2fhe_noalloc_max_gates.restype = sz
     L.b2fhe_noalloc_max_gates.argtypes = []

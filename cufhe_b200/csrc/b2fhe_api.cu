@@ -2,7 +2,6 @@
 // Host-side counterpart of the reference's launch wrappers and key upload
 // (src/bootstrap_gpu.cu:97-155,782-1292, src/keyswitch_gpu.cu, src/cufhe_gates_gpu.cu).
 #include <atomic>
-#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -11,16 +10,12 @@
 
 #include "../../include/b2fhe.h"
 #include "k_blindrotate.cuh"
-#include "k_blindrotate16.cuh"
-#include "k_blindrotate16q.cuh"
 #include "k_blindrotate_s.cuh"
 #include "k_blindrotate_lat.cuh"
-#include "k_blindrotate_cl.cuh"
 #include "k_blindrotate_cl4.cuh"
 #include "k_cmux.cuh"
-#include "k_polymul16.cuh"
 #include "k_keyswitch.cuh"
-#include "k_ntt.cuh"
+#include "k_ntt_s.cuh"
 
 using namespace b2;
 
@@ -30,12 +25,10 @@ constexpr int kMaxDev = 16;
 struct DevCtx {
     bool ready = false;
     bool owns_keys = false;
-    uint32_t* bk_ntt = nullptr;     // [636][4][2 primes][2][1024] Montgomery residues
+    uint32_t* bk = nullptr;         // NTT-domain key [636][4][2 primes][2][1024], Montgomery residues in [0, p), bk16_slot order
     uint32_t* ksk = nullptr;        // T[1024][7][3][320]
-    LaneTables* tab = nullptr;
-    uint32_t* bk_ntt16 = nullptr;   // same key in bk16_slot order (k_blind_rotate16), built lazily
-    Lane16Tables* tab16 = nullptr;
-    TeamSTables* tabs = nullptr;    // second-generation tables (k_blind_rotate_s)
+    Lane16Tables* tab16 = nullptr;  // first-generation team tables (latency kernels, stand-alone CMUX)
+    TeamSTables3* tabs = nullptr;   // second-generation tables, three primes (the blind rotation stages the first two)
     int sm_count = 0;
 };
 DevCtx g_ctx[kMaxDev];
@@ -44,10 +37,9 @@ int g_gates_per_cta = 0;
 int g_ks_variant = 0;            // 0 = by batch size, 1 = k_keyswitch_lat, 2 = k_keyswitch
 int g_ks_lat_max_per_sm = 32;    // k_keyswitch_lat up to this many gates per SM (measured faster up to there)
 int g_br_cluster_max = 70;       // k_blind_rotate_cl4 up to this many gates: 33 four-CTA clusters run one CTA per SM (1.63 ms), up to 70 two per SM (2.2 ms); beyond that k_blind_rotate_lat (3.5 ms) wins
-int g_br_burst_detect = 1;       // small calls arriving back to back use the throughput kernel
-constexpr int64_t kBurstGapNs = 300000;
+int g_latency_mode = 1;          // small calls: 1 = latency kernels (one gate over several SMs), 0 = always the throughput kernel (b2fhe_set_latency_mode)
 bool g_br_tail_split = true;     // last partial wave of k_blind_rotate16 as its own launch (b2fhe_set_br_variant(-1) / (-2) = off / on)
-int g_br_variant = 0;            // 0 = default, 1 = k_blind_rotate_lat, 2 = k_blind_rotate_cl, 16 = k_blind_rotate16, 32 = k_blind_rotate
+int g_br_variant = 0;            // 0 = by batch size, 1 = k_blind_rotate_lat, 5 = k_blind_rotate_cl4, 40 = k_blind_rotate_s, 48 = its key-row-0 timing experiment
 std::atomic<uint64_t> g_launches{0};
 thread_local std::string t_err;
 
@@ -70,24 +62,6 @@ int fail(int code, const char* what, const char* file, int line)
     } while (0)
 #define LAUNCHED() do { g_launches.fetch_add(1, std::memory_order_relaxed); CK(cudaGetLastError()); } while (0)
 
-template <int G> int set_br_attr()
-{
-    CK(cudaFuncSetAttribute(k_blind_rotate<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, br_smem_bytes(G)));
-    return 0;
-}
-template <int G> int set_br16_attr()
-{
-    CK(cudaFuncSetAttribute(k_blind_rotate16<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
-    if (G <= 4) CK(cudaFuncSetAttribute(k_blind_rotate16q<(G <= 4 ? G : 4)>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16q_smem_bytes(G <= 4 ? G : 4)));
-    if (G <= 5) {
-        CK(cudaFuncSetAttribute(k_blind_rotate16<(G <= 5 ? G : 5), 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
-        CK(cudaFuncSetAttribute(k_blind_rotate16<(G <= 5 ? G : 5), 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
-        CK(cudaFuncSetAttribute(k_blind_rotate16<(G <= 5 ? G : 5), 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
-        CK(cudaFuncSetAttribute(k_blind_rotate16<(G <= 5 ? G : 5), 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, br16_smem_bytes(G)));
-    }
-    return 0;
-}
-
 template <int G> int set_brs_attr()
 {
     CK(cudaFuncSetAttribute(k_blind_rotate_s<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(G)));
@@ -104,29 +78,21 @@ int setup_device(int device)
     REQUIRE(device >= 0 && device < ndev && device < kMaxDev, B2FHE_E_NO_DEVICE);
     CK(cudaSetDevice(device));
     DevCtx& c = g_ctx[device];
-    if (c.tab) return 0;
+    if (c.tabs) return 0;
     static NttTables T;
+    static Lane16Tables L16;
+    static TeamSTables3 LS;
+    static TeamSConst CS;
     static bool made = false;
-    if (!made) { make_tables(T); made = true; }
+    if (!made) { make_tables(T); make_tables16(L16); make_tables16s(LS, CS); made = true; }
     CK(cudaMemcpyToSymbol(c_fw1, T.fw1, sizeof T.fw1));
     CK(cudaMemcpyToSymbol(c_iv1, T.iv1, sizeof T.iv1));
     CK(cudaMemcpyToSymbol(c_r2, T.r2, sizeof T.r2));
     CK(cudaMemcpyToSymbol(c_crt_p0inv, &T.crt_p0inv, sizeof(Tw)));
-    static LaneTables L;
-    memcpy(L.fw2, T.fw2, sizeof L.fw2);
-    memcpy(L.iv2, T.iv2, sizeof L.iv2);
-    memcpy(L.scale, T.scale, sizeof L.scale);
-    CK(cudaMalloc(&c.tab, sizeof(LaneTables)));
-    CK(cudaMemcpy(c.tab, &L, sizeof L, cudaMemcpyHostToDevice));
-    static Lane16Tables L16;
-    make_tables16(L16);
+    CK(cudaMemcpyToSymbol(c_s, &CS, sizeof CS));
     CK(cudaMalloc(&c.tab16, sizeof(Lane16Tables)));
     CK(cudaMemcpy(c.tab16, &L16, sizeof L16, cudaMemcpyHostToDevice));
-    static TeamSTables LS;
-    static TeamSConst CS;
-    make_tables16s(LS, CS);
-    CK(cudaMemcpyToSymbol(c_s, &CS, sizeof CS));
-    CK(cudaMalloc(&c.tabs, sizeof(TeamSTables)));
+    CK(cudaMalloc(&c.tabs, sizeof(TeamSTables3)));
     CK(cudaMemcpy(c.tabs, &LS, sizeof LS, cudaMemcpyHostToDevice));
     CK(cudaDeviceGetAttribute(&c.sm_count, cudaDevAttrMultiProcessorCount, device));
     // keep stream-ordered scratch cached between calls
@@ -134,57 +100,34 @@ int setup_device(int device)
     CK(cudaDeviceGetDefaultMemPool(&pool, device));
     uint64_t keep = ~0ull;
     CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
-    if (int r = set_br_attr<1>()) return r;
-    if (int r = set_br_attr<2>()) return r;
-    if (int r = set_br_attr<4>()) return r;
-    if (int r = set_br_attr<6>()) return r;
-    if (int r = set_br_attr<8>()) return r;
-    CK(cudaFuncSetAttribute(k_blind_rotate_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatSmemBytes));
-    CK(cudaFuncSetAttribute(k_blind_rotate_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, kClSmemBytes));
-    CK(cudaFuncSetAttribute(k_blind_rotate_cl4<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
-    CK(cudaFuncSetAttribute(k_blind_rotate_cl4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
-    CK(cudaFuncSetAttribute(k_cmux16<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(1)));
-    CK(cudaFuncSetAttribute(k_cmux16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(4)));
-    CK(cudaFuncSetAttribute(k_polymul16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, polymul16_smem_bytes(4)));
     if (int r = set_brs_attr<1>()) return r;
     if (int r = set_brs_attr<2>()) return r;
     if (int r = set_brs_attr<3>()) return r;
     if (int r = set_brs_attr<4>()) return r;
     CK(cudaFuncSetAttribute(k_blind_rotate_s<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(4)));
-    if (int r = set_br16_attr<1>()) return r;
-    if (int r = set_br16_attr<2>()) return r;
-    if (int r = set_br16_attr<3>()) return r;
-    if (int r = set_br16_attr<4>()) return r;
-    if (int r = set_br16_attr<5>()) return r;
-    if (int r = set_br16_attr<6>()) return r;
+    CK(cudaFuncSetAttribute(k_blind_rotate_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatSmemBytes));
+    CK(cudaFuncSetAttribute(k_blind_rotate_cl4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
+    CK(cudaFuncSetAttribute(k_cmux16<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(1)));
+    CK(cudaFuncSetAttribute(k_cmux16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(4)));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
-    CK(cudaFuncSetAttribute(k_ntt_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
-    CK(cudaFuncSetAttribute(k_ntt_inv, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
-    CK(cudaFuncSetAttribute(k_polymul, cudaFuncAttributeMaxDynamicSharedMemorySize, kNttSmemBytes));
+    CK(cudaFuncSetAttribute(k_ntt_fwd_s<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, kNttTeams>()));
+    CK(cudaFuncSetAttribute(k_ntt_fwd_s<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, kNttTeams>()));
+    CK(cudaFuncSetAttribute(k_ntt_inv_s, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, kNttTeams>()));
+    CK(cudaFuncSetAttribute(k_polymul_s<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, 4>()));
+    CK(cudaFuncSetAttribute(k_polymul_s<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<3, 6>()));
     return noalloc_setup(device);
 }
 
-int ntt_grid(const DevCtx& c, size_t npoly)
+// persistent CTAs of the stand-alone transform kernels: `per_sm` per SM, fewer for small batches
+int ntt_grid(const DevCtx& c, size_t npoly, int polys_per_cta, int per_sm)
 {
-    size_t blocks = (npoly + kNttPolysPerCta - 1) / kNttPolysPerCta;
-    size_t cap = (size_t)c.sm_count * 16;
+    size_t blocks = (npoly + polys_per_cta - 1) / polys_per_cta;
+    size_t cap = (size_t)c.sm_count * per_sm;
     return (int)(blocks < cap ? (blocks ? blocks : 1) : cap);
-}
-
-// the key in k_blind_rotate16's storage order, permuted on the device from the
-// 32-coefficient order (which stays the interchange format of b2fhe_key_pointers/adopt_keys)
-int build_bk16(DevCtx& c)
-{
-    if (!c.bk_ntt16) CK(cudaMalloc(&c.bk_ntt16, B2FHE_BK_NTT_BYTES));
-    const size_t npoly = (size_t)kLwe * kRows * 2 * 2;
-    k_bk_to_layout16<<<c.sm_count * 8, 256>>>(c.bk_ntt, c.bk_ntt16, npoly);
-    LAUNCHED();
-    CK(cudaDeviceSynchronize());
-    return 0;
 }
 
 // BootstrappingKeyToNTT + KeySwitchingKeyToDevice on one device (src/bootstrap_gpu.cu:111-138,
@@ -195,7 +138,7 @@ int convert_keys(int device, const uint32_t* bk_raw, const uint16_t* ksk_raw)
     CK(cudaSetDevice(device));
     uint32_t* d_raw = nullptr;
     uint16_t* d_kraw = nullptr;
-    CK(cudaMalloc(&c.bk_ntt, B2FHE_BK_NTT_BYTES));
+    CK(cudaMalloc(&c.bk, B2FHE_BK_NTT_BYTES));
     CK(cudaMalloc(&c.ksk, B2FHE_KSK_DEV_BYTES));
     c.owns_keys = true;
     CK(cudaMalloc(&d_raw, B2FHE_BK_RAW_WORDS * 4));
@@ -203,14 +146,13 @@ int convert_keys(int device, const uint32_t* bk_raw, const uint16_t* ksk_raw)
     CK(cudaMemcpy(d_raw, bk_raw, B2FHE_BK_RAW_WORDS * 4, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_kraw, ksk_raw, B2FHE_KSK_RAW_WORDS * 2, cudaMemcpyHostToDevice));
     const int npoly = kLwe * kRows * 2;
-    k_ntt_fwd<<<ntt_grid(c, npoly), kNttThreads, kNttSmemBytes>>>(d_raw, c.bk_ntt, npoly, 1, 0, c.tab);
+    k_ntt_fwd_s<1><<<ntt_grid(c, npoly, kNttTeams / 2, 1), kNttThreadsS, ntt_s_smem_bytes<2, kNttTeams>()>>>(d_raw, c.bk, npoly, c.tabs->pr);
     LAUNCHED();
     k_ksk_layout<<<c.sm_count * 8, 256>>>(d_kraw, c.ksk);
     LAUNCHED();
     CK(cudaDeviceSynchronize());
     CK(cudaFree(d_raw));
     CK(cudaFree(d_kraw));
-    if (int r = build_bk16(c)) return r;
     c.ready = true;
     return 0;
 }
@@ -226,12 +168,11 @@ int replicate_keys(int ngpu)
     for (int d = 1; d < ngpu; d++) {
         DevCtx& c = g_ctx[d];
         CK(cudaSetDevice(d));
-        CK(cudaMalloc(&c.bk_ntt, B2FHE_BK_NTT_BYTES));
+        CK(cudaMalloc(&c.bk, B2FHE_BK_NTT_BYTES));
         CK(cudaMalloc(&c.ksk, B2FHE_KSK_DEV_BYTES));
         c.owns_keys = true;
-        CK(cudaMemcpyPeer(c.bk_ntt, d, g_ctx[0].bk_ntt, 0, B2FHE_BK_NTT_BYTES));
+        CK(cudaMemcpyPeer(c.bk, d, g_ctx[0].bk, 0, B2FHE_BK_NTT_BYTES));
         CK(cudaMemcpyPeer(c.ksk, d, g_ctx[0].ksk, 0, B2FHE_KSK_DEV_BYTES));
-        if (int r = build_bk16(c)) return r;
         c.ready = true;
     }
     return 0;
@@ -267,8 +208,14 @@ int b2fhe_set_ks_variant(int variant)
 int b2fhe_set_br_variant(int variant)
 {
     if (variant == -1 || variant == -2) { g_br_tail_split = variant == -2; return 0; }
-    REQUIRE(variant == 0 || variant == 1 || variant == 2 || variant == 4 || variant == 5 || variant == 16 || (variant >= 17 && variant <= 21) || variant == 32 || variant == 40 || variant == 48, B2FHE_E_BAD_ARGUMENT);
+    REQUIRE(variant == 0 || variant == 1 || variant == 5 || variant == 40 || variant == 48, B2FHE_E_BAD_ARGUMENT);
     g_br_variant = variant;
+    return 0;
+}
+int b2fhe_set_latency_mode(int on)
+{
+    REQUIRE(on == 0 || on == 1, B2FHE_E_BAD_ARGUMENT);
+    g_latency_mode = on;
     return 0;
 }
 int b2fhe_num_devices(void)
@@ -315,11 +262,9 @@ int b2fhe_adopt_keys(int device, const void* bk_ntt_dev, const void* ksk_dev)
     if (int r = setup_device(device)) return r;
     DevCtx& c = g_ctx[device];
     REQUIRE(!c.ready, B2FHE_E_BAD_ARGUMENT);
-    c.bk_ntt = (uint32_t*)bk_ntt_dev;
+    c.bk = (uint32_t*)bk_ntt_dev;
     c.ksk = (uint32_t*)ksk_dev;
     c.owns_keys = false;
-    CK(cudaSetDevice(device));
-    if (int r = build_bk16(c)) return r;
     c.ready = true;
     return 0;
 }
@@ -328,7 +273,7 @@ int b2fhe_key_pointers(int device, void** bk_ntt_dev, void** ksk_dev)
 {
     DevCtx* c;
     if (int r = get_ctx(device, c)) return r;
-    if (bk_ntt_dev) *bk_ntt_dev = c->bk_ntt;
+    if (bk_ntt_dev) *bk_ntt_dev = c->bk;
     if (ksk_dev) *ksk_dev = c->ksk;
     return 0;
 }
@@ -339,14 +284,12 @@ int b2fhe_cleanup(void)
     std::lock_guard<std::mutex> lk(g_mu);
     for (int d = 0; d < kMaxDev; d++) {
         DevCtx& c = g_ctx[d];
-        if (!c.tab && !c.ready) continue;
+        if (!c.tabs && !c.ready) continue;
         CK(cudaSetDevice(d));
         CK(cudaDeviceSynchronize());
-        if (c.owns_keys) { CK(cudaFree(c.bk_ntt)); CK(cudaFree(c.ksk)); }
-        if (c.tab) CK(cudaFree(c.tab));
+        if (c.owns_keys) { CK(cudaFree(c.bk)); CK(cudaFree(c.ksk)); }
         if (c.tab16) CK(cudaFree(c.tab16));
         if (c.tabs) CK(cudaFree(c.tabs));
-        if (c.bk_ntt16) CK(cudaFree(c.bk_ntt16));
         c = DevCtx();
     }
     defer_destroy_all();

@@ -4,190 +4,75 @@
 
 namespace {
 
-template <int G> int launch_br_g(const BrParams& P, cudaStream_t st)
-{
-    const int grid = (P.count + G - 1) / G;
-    k_blind_rotate<G><<<grid, 64 * G, br_smem_bytes(G), st>>>(P);
-    LAUNCHED();
-    return 0;
-}
-template <int G, int PAIR = 0> int launch_br16_g(const DevCtx& c, const BrParams& P, cudaStream_t st)
-{
-    const int grid = (P.count - P.first + G - 1) / G;
-    k_blind_rotate16<G, PAIR><<<grid, 128 * G, br16_smem_bytes(G), st>>>(P, c.tab16);
-    LAUNCHED();
-    return 0;
-}
-template <int G> int launch_br16q_g(const DevCtx& c, const BrParams& P, cudaStream_t st)
-{
-    const int grid = (P.count + G - 1) / G;
-    k_blind_rotate16q<G><<<grid, 128 * G, br16q_smem_bytes(G), st>>>(P, c.tab16);
-    LAUNCHED();
-    return 0;
-}
 template <int G> int launch_brs_g(const DevCtx& c, const BrParams& P, cudaStream_t st)
 {
     const int grid = (P.count - P.first + G - 1) / G;
-    k_blind_rotate_s<G><<<grid, 128 * G, brs_smem_bytes(G), st>>>(P, c.tabs);
+    k_blind_rotate_s<G><<<grid, 128 * G, brs_smem_bytes(G), st>>>(P, reinterpret_cast<const TeamSTables*>(c.tabs));
     LAUNCHED();
     return 0;
 }
+// Kernel choice is a function of the batch size and of explicit settings only (b2fhe_set_br_variant,
+// b2fhe_set_latency_mode): the same call always runs the same kernels.
 int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
 {
     if (P.count <= 0) return 0;
-    const int variant = g_br_variant ? g_br_variant : 40;
+    P.bk = c.bk;
     int g = g_gates_per_cta;
     const int per_sm = (P.count + c.sm_count - 1) / c.sm_count;
-    // The two latency kernels spend several SMs (or a whole SM) on one gate: right for an
-    // isolated small call, wrong when small calls arrive back to back on many streams (the
-    // reference's usage, test/test_gate_gpu.cc: one gate per call, one stream per SM) -- then
-    // throughput matters and the 128-thread-per-gate kernel packs 3 gates per SM.  A small
-    // call issued within kBurstGapNs of the previous one on this device counts as a burst.
-    bool burst = false;
-    if (per_sm <= 1) {
-        static std::atomic<int64_t> last_ns[kMaxDev];
-        const int64_t now = std::chrono::duration_cast<std::chrono::nanoseconds>(
-                                std::chrono::steady_clock::now().time_since_epoch()).count();
-        int dev = 0;
-        cudaGetDevice(&dev);
-        const int64_t prev = last_ns[dev].exchange(now, std::memory_order_relaxed);
-        burst = g_br_burst_detect && prev != 0 && now - prev < kBurstGapNs;
-    }
-    // up to 70 gates: one gate per cluster of 4 CTAs x 128 threads (70 clusters are resident at once, two CTAs per SM)
-    if (variant == 4 || variant == 5 || (g_br_variant == 0 && g == 0 && !burst && P.count <= g_br_cluster_max)) {
-        P.bk = c.bk_ntt16;
-        // default: hand-overs by st.async + mbarrier (variant 5); variant 4 = cluster barriers (A/B)
-        if (variant == 4) k_blind_rotate_cl4<false><<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, c.tab16);
-        else k_blind_rotate_cl4<true><<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, c.tab16);
+    const bool small_ok = g_br_variant == 0 && g == 0 && g_latency_mode;
+    // up to 70 gates: one gate per cluster of 4 CTAs x 128 threads (70 clusters are resident at once, two CTAs
+    // per SM); hand-overs by st.async + mbarrier
+    if (g_br_variant == 5 || (small_ok && P.count <= g_br_cluster_max)) {
+        k_blind_rotate_cl4<true><<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, c.tab16);
         LAUNCHED();
         return 0;
     }
-    // first cluster design (A/B): one gate per cluster of 8 CTAs x 64 threads
-    if (variant == 2) {
-        P.bk = c.bk_ntt16;
-        k_blind_rotate_cl<<<P.count * kClCtas, 64, kClSmemBytes, st>>>(P, c.tab16);
-        LAUNCHED();
-        return 0;
-    }
-    // small batches (<= 1 gate per SM; measured faster than k_blind_rotate16 only there): one gate per 512-thread CTA, 1 + 1 transforms on the
-    // critical path of a CMUX step instead of 4 + 2
-    if (variant == 1 || (g_br_variant == 0 && g == 0 && !burst && per_sm <= 1)) {
-        P.bk = c.bk_ntt16;
+    // up to one gate per SM: one gate per 512-thread CTA, 1 + 1 transforms on the critical path of a CMUX
+    // step instead of 4 + 2
+    if (g_br_variant == 1 || (small_ok && per_sm <= 1)) {
         k_blind_rotate_lat<<<P.count, kLatThreads, kLatSmemBytes, st>>>(P, c.tab16);
         LAUNCHED();
         return 0;
     }
-    if (variant == 40 || variant == 48) {      // second generation (signed residues, vector exchanges, doubled accumulator): the default
-        P.bk = c.bk_ntt16;
-        if (variant == 48) {      // key row 0 at every step (timing experiment: key traffic vs arithmetic; wrong results)
-            const int grid = (P.count - P.first + 3) / 4;
-            k_blind_rotate_s<4, true><<<grid, 512, brs_smem_bytes(4), st>>>(P, c.tabs);
-            LAUNCHED();
-            return 0;
-        }
-        if (g == 0 && g_br_tail_split) {
-            // Waves of 4 gates per SM take the same time whether full or not; a last partial wave of at
-            // most 3 gates per SM runs as its own launch with fewer gates per CTA.
-            const int wave = 4 * c.sm_count;
-            const int full = (P.count / wave) * wave, rest = P.count - full;
-            if (full > 0 && rest > 0 && rest <= 3 * c.sm_count) {
-                BrParams M = P;
-                M.count = full;
-                if (int r = launch_brs_g<4>(c, M, st)) return r;
-                P.first = full;
-                // 1 or 2 gates per SM: one-gate CTAs (two fit an SM)
-                if (rest <= 2 * c.sm_count) return launch_brs_g<1>(c, P, st);
-                return launch_brs_g<3>(c, P, st);
-            }
-        }
-        if (g == 0) g = per_sm >= 4 ? 4 : per_sm == 3 ? 3 : 1;
-        switch (g) {
-            case 1: return launch_brs_g<1>(c, P, st);
-            case 2: return launch_brs_g<2>(c, P, st);
-            case 3: return launch_brs_g<3>(c, P, st);
-            default: return launch_brs_g<4>(c, P, st);
+    if (g_br_variant == 48) {      // key row 0 at every step (timing experiment: key traffic vs arithmetic; wrong results)
+        const int grid = (P.count - P.first + 3) / 4;
+        k_blind_rotate_s<4, true><<<grid, 512, brs_smem_bytes(4), st>>>(P, reinterpret_cast<const TeamSTables*>(c.tabs));
+        LAUNCHED();
+        return 0;
+    }
+    // the throughput kernel: four gates per CTA (16 warps at 128 registers fill the register file)
+    if (g == 0 && g_br_tail_split) {
+        // Waves of 4 gates per SM take the same time whether full or not; a last partial wave of at
+        // most 3 gates per SM runs as its own launch with fewer gates per CTA.
+        const int wave = 4 * c.sm_count;
+        const int full = (P.count / wave) * wave, rest = P.count - full;
+        if (full > 0 && rest > 0 && rest <= 3 * c.sm_count) {
+            BrParams M = P;
+            M.count = full;
+            if (int r = launch_brs_g<4>(c, M, st)) return r;
+            P.first = full;
+            // 1 or 2 gates per SM: one-gate CTAs (two fit an SM)
+            if (rest <= 2 * c.sm_count) return launch_brs_g<1>(c, P, st);
+            return launch_brs_g<3>(c, P, st);
         }
     }
-    if (variant == 21) {      // paired transforms + four exchange buffers per team (8 barriers per step)
-        P.bk = c.bk_ntt16;
-        if (g == 0) g = per_sm >= 4 ? 4 : per_sm >= 1 ? per_sm : 1;
-        switch (g) {
-            case 1: return launch_br16q_g<1>(c, P, st);
-            case 2: return launch_br16q_g<2>(c, P, st);
-            case 3: return launch_br16q_g<3>(c, P, st);
-            default: return launch_br16q_g<4>(c, P, st);
-        }
-    }
-    if (variant >= 17 && variant <= 20) {      // row-pair key multiply (17), + paired digit transforms (18), + paired inverse (19, default), 4-row reduction (20)
-        P.bk = c.bk_ntt16;
-        if (g == 0 && variant == 19 && g_br_tail_split) {
-            // Waves of 4 gates per SM take ~9 ms each whether full or not; a last partial wave of at
-            // most 3 gates per SM runs as its own launch with fewer gates per CTA (3 per SM: ~7 ms).
-            const int wave = 4 * c.sm_count;
-            const int full = (P.count / wave) * wave, rest = P.count - full;
-            if (full > 0 && rest > 0 && rest <= 3 * c.sm_count) {
-                BrParams M = P;
-                M.count = full;
-                if (int r = launch_br16_g<4, 3>(c, M, st)) return r;
-                P.first = full;
-                // 1 or 2 gates per SM: one-gate CTAs (two fit an SM; 5.2 ms vs 5.4 ms for a two-gate CTA)
-                if (rest <= 2 * c.sm_count) return launch_br16_g<1, 3>(c, P, st);
-                return launch_br16_g<3, 3>(c, P, st);
-            }
-        }
-        if (g == 0) g = per_sm >= 4 ? 4 : per_sm == 3 ? 3 : 1;      // two one-gate CTAs share an SM faster than one two-gate CTA
-        if (variant == 17) switch (g) {
-            case 1: return launch_br16_g<1, 1>(c, P, st);
-            case 2: return launch_br16_g<2, 1>(c, P, st);
-            case 3: return launch_br16_g<3, 1>(c, P, st);
-            case 4: return launch_br16_g<4, 1>(c, P, st);
-            default: return launch_br16_g<5, 1>(c, P, st);
-        }
-        if (variant == 20) switch (g) {
-            case 1: return launch_br16_g<1, 4>(c, P, st);
-            case 2: return launch_br16_g<2, 4>(c, P, st);
-            case 3: return launch_br16_g<3, 4>(c, P, st);
-            case 4: return launch_br16_g<4, 4>(c, P, st);
-            default: return launch_br16_g<5, 4>(c, P, st);
-        }
-        if (variant == 19) switch (g) {
-            case 1: return launch_br16_g<1, 3>(c, P, st);
-            case 2: return launch_br16_g<2, 3>(c, P, st);
-            case 3: return launch_br16_g<3, 3>(c, P, st);
-            case 4: return launch_br16_g<4, 3>(c, P, st);
-            default: return launch_br16_g<5, 3>(c, P, st);
-        }
-        switch (g) {
-            case 1: return launch_br16_g<1, 2>(c, P, st);
-            case 2: return launch_br16_g<2, 2>(c, P, st);
-            case 3: return launch_br16_g<3, 2>(c, P, st);
-            case 4: return launch_br16_g<4, 2>(c, P, st);
-            default: return launch_br16_g<5, 2>(c, P, st);
-        }
-    }
-    if (variant == 16) {
-        P.bk = c.bk_ntt16;
-        // spread small batches over all SMs; large batches use the widest CTA
-        if (g == 0) g = per_sm >= 4 ? 4 : per_sm >= 1 ? per_sm : 1;   // 4 gates = 16 warps at 128 registers measured fastest
-        switch (g) {
-            case 1: return launch_br16_g<1>(c, P, st);
-            case 2: return launch_br16_g<2>(c, P, st);
-            case 3: return launch_br16_g<3>(c, P, st);
-            case 4: return launch_br16_g<4>(c, P, st);
-            case 5: return launch_br16_g<5>(c, P, st);
-            default: return launch_br16_g<6>(c, P, st);
-        }
-    }
-    P.bk = c.bk_ntt;
-    P.tab = c.tab;
-    if (g == 0) g = per_sm >= 6 ? 6 : per_sm >= 4 ? 4 : per_sm >= 2 ? 2 : 1;
+    if (g == 0) g = per_sm >= 4 ? 4 : per_sm == 3 ? 3 : 1;      // two one-gate CTAs share an SM faster than one two-gate CTA
     switch (g) {
-        case 1: return launch_br_g<1>(P, st);
-        case 2: return launch_br_g<2>(P, st);
-        case 4: return launch_br_g<4>(P, st);
-        case 8: return launch_br_g<8>(P, st);
-        default: return launch_br_g<6>(P, st);
+        case 1: return launch_brs_g<1>(c, P, st);
+        case 2: return launch_brs_g<2>(c, P, st);
+        case 3: return launch_brs_g<3>(c, P, st);
+        default: return launch_brs_g<4>(c, P, st);
     }
+}
+// work items of a uniform lvl0 Mux / NMux batch: [0, count) = inc AND in1, [count, 2 count) = (NOT inc) AND in0
+__global__ void k_mux_items(BrItem* items, int count, int off)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * count) return;
+    const int g = i < count ? i : i - count;
+    BrItem b{};
+    b.g0 = b.g1 = (uint32_t)g; b.ca = i < count ? 1 : -1; b.cb = 1; b.src1 = i < count ? 0 : 1; b.off = off; b.slot = (uint32_t)i;
+    items[i] = b;
 }
 int launch_ks(const DevCtx& c, KsParams P, cudaStream_t st)
 {
@@ -290,15 +175,19 @@ int uniform_gate(const DevCtx& c, cudaStream_t st, int op, int level, void* out,
     REQUIRE(in1 != nullptr && in2 != nullptr, B2FHE_E_BAD_ARGUMENT);
     const int sg = op == B2FHE_NMUX ? -1 : 1;
     if (level == 0) {           // src/bootstrap_gpu.cu:515-588
-        uint32_t *ta, *tb;
-        if (int r = S.get((void**)&ta, (size_t)count * kLvl1Words * 4)) return r;
-        if (int r = S.get((void**)&tb, (size_t)count * kLvl1Words * 4)) return r;
-        B.in0 = (const uint16_t*)in0; B.in1 = (const uint16_t*)in1; B.out = ta;
-        B.ca = 1; B.cb = 1; B.off = -(int)kMu0;
+        uint32_t *ta, *tb = nullptr;
+        if (int r = S.get((void**)&ta, 2 * (size_t)count * kLvl1Words * 4)) return r;
+        // both branches as ONE blind-rotation launch of 2 * count work items (one wave quantisation, not two):
+        // item g = inc AND in1 -> ta[g], item count + g = (NOT inc) AND in0 -> tb[g] = ta[count + g]
+        (void)tb;
+        BrItem* d_items;
+        if (int r = S.get((void**)&d_items, 2 * (size_t)count * sizeof(BrItem))) return r;
+        k_mux_items<<<(2 * count + 255) / 256, 256, 0, st>>>(d_items, count, -(int)kMu0);
+        LAUNCHED();
+        B.in0 = (const uint16_t*)in0; B.in1 = (const uint16_t*)in1; B.in2 = (const uint16_t*)in2; B.out = ta;
+        B.items = d_items; B.count = 2 * count;
         if (int r = launch_br(c, B, st)) return r;
-        B.in1 = (const uint16_t*)in2; B.out = tb; B.ca = -1;
-        if (int r = launch_br(c, B, st)) return r;
-        K.A = ta; K.B = tb; K.out = (uint16_t*)out; K.ca = sg; K.cb = sg; K.off = (uint32_t)sg * kMu1;
+        K.A = ta; K.B = ta + (size_t)count * kLvl1Words; K.out = (uint16_t*)out; K.ca = sg; K.cb = sg; K.off = (uint32_t)sg * kMu1;
         return launch_ks(c, K, st);
     }
     // src/bootstrap_gpu.cu:706-780
@@ -570,14 +459,9 @@ int b2fhe_trgsw2ntt_batch(int device, b2fhe_stream_t stream, uint32_t* out_ntt, 
     REQUIRE(count < (1u << 24), B2FHE_E_BAD_ARGUMENT);
     if (count == 0) return 0;
     REQUIRE(out_ntt && in_raw, B2FHE_E_BAD_ARGUMENT);
-    cudaStream_t st = (cudaStream_t)stream;
-    Scratch scratch(st);
-    void* tmp = nullptr;
-    if (int r = scratch.get(&tmp, count * B2FHE_TRGSW_NTT_BYTES)) return r;
     const int npoly = (int)count * kRows * 2;
-    k_ntt_fwd<<<ntt_grid(*c, npoly), kNttThreads, kNttSmemBytes, st>>>(in_raw, (uint32_t*)tmp, npoly, 1, 0, c->tab);
-    LAUNCHED();
-    k_bk_to_layout16<<<c->sm_count * 8, 256, 0, st>>>((const uint32_t*)tmp, out_ntt, (size_t)npoly * 2);
+    k_ntt_fwd_s<1><<<ntt_grid(*c, npoly, kNttTeams / 2, 1), kNttThreadsS, ntt_s_smem_bytes<2, kNttTeams>(), (cudaStream_t)stream>>>(
+        in_raw, out_ntt, npoly, c->tabs->pr);
     LAUNCHED();
     return 0;
 }
@@ -616,7 +500,8 @@ int b2fhe_ntt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const 
     if (int r = get_ctx(device, c)) return r;
     if (count == 0) return 0;
     REQUIRE(out && in && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    k_ntt_fwd<<<ntt_grid(*c, count), kNttThreads, kNttSmemBytes, (cudaStream_t)stream>>>(in, out, (int)count, 0, 0, c->tab);
+    k_ntt_fwd_s<0><<<ntt_grid(*c, count, kNttTeams / 2, 1), kNttThreadsS, ntt_s_smem_bytes<2, kNttTeams>(), (cudaStream_t)stream>>>(
+        in, out, (int)count, c->tabs->pr);
     LAUNCHED();
     return 0;
 }
@@ -626,7 +511,8 @@ int b2fhe_intt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const
     if (int r = get_ctx(device, c)) return r;
     if (count == 0) return 0;
     REQUIRE(out && in && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    k_ntt_inv<<<ntt_grid(*c, count), kNttThreads, kNttSmemBytes, (cudaStream_t)stream>>>(in, out, (int)count, c->tab);
+    k_ntt_inv_s<<<ntt_grid(*c, count, kNttTeams / 2, 1), kNttThreadsS, ntt_s_smem_bytes<2, kNttTeams>(), (cudaStream_t)stream>>>(
+        in, out, (int)count, c->tabs->pr);
     LAUNCHED();
     return 0;
 }
@@ -636,15 +522,17 @@ int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, co
     if (int r = get_ctx(device, c)) return r;
     if (count == 0) return 0;
     REQUIRE(out && a && b && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    if (g_br_variant == 32) {             // first design (A/B): one warp x 32 coefficients per (product, prime)
-        k_polymul<<<ntt_grid(*c, count), kNttThreads, kNttSmemBytes, (cudaStream_t)stream>>>(a, b, out, (int)count, c->tab);
-        LAUNCHED();
-        return 0;
-    }
-    constexpr int G = 4;
-    const int ctas = (int)((count + G - 1) / G);
-    k_polymul16<G><<<ctas < c->sm_count ? ctas : c->sm_count, 128 * G, polymul16_smem_bytes(G), (cudaStream_t)stream>>>(
-        a, b, out, (int)count, c->tab16);
+    k_polymul_s<2><<<ntt_grid(*c, count, 2, 2), 256, ntt_s_smem_bytes<2, 4>(), (cudaStream_t)stream>>>(a, b, out, (int)count, c->tabs->pr);
+    LAUNCHED();
+    return 0;
+}
+int b2fhe_polymul1024_exact_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* a, const uint32_t* b, size_t count)
+{
+    DevCtx* c;
+    if (int r = get_ctx(device, c)) return r;
+    if (count == 0) return 0;
+    REQUIRE(out && a && b && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
+    k_polymul_s<3><<<ntt_grid(*c, count, 2, 1), 384, ntt_s_smem_bytes<3, 6>(), (cudaStream_t)stream>>>(a, b, out, (int)count, c->tabs->pr);
     LAUNCHED();
     return 0;
 }

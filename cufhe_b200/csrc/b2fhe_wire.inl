@@ -189,10 +189,10 @@ int b2fhe_wire_tlwes_parse(const void* blob, size_t len, int level, size_t* coun
 
 /* ---- cache of the converted keys ---------------------------------------------------------
  * "B2FHEKC1" | u32 layout version | u32 reserved | u64 bk bytes | u64 ksk bytes |
- * u64 FNV-1a of the payload | bk_ntt (interchange order) | ksk (device layout) */
+ * u64 FNV-1a of the payload | bk (bk16_slot order) | ksk (device layout) */
 namespace {
 constexpr size_t kCacheHeader = 8 + 4 + 4 + 8 + 8 + 8;
-constexpr uint32_t kCacheLayoutVersion = 1;
+constexpr uint32_t kCacheLayoutVersion = 2;      // 2: bk16_slot order, primes 2^27 - 2^11 + 1 / 2^27 - 2^21 + 1
 uint64_t fnv1a64(const uint8_t* p, size_t n)
 {
     // 8 interleaved lanes so that ~70 MB hash in tens of milliseconds
@@ -217,7 +217,7 @@ int b2fhe_key_cache_export(int device, void* blob, size_t cap, size_t* written)
     REQUIRE(blob && cap >= b2fhe_key_cache_size(), B2FHE_E_BAD_ARGUMENT);
     uint8_t* p = static_cast<uint8_t*>(blob);
     uint8_t* payload = p + kCacheHeader;
-    CK(cudaMemcpy(payload, c->bk_ntt, B2FHE_BK_NTT_BYTES, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(payload, c->bk, B2FHE_BK_NTT_BYTES, cudaMemcpyDeviceToHost));
     CK(cudaMemcpy(payload + B2FHE_BK_NTT_BYTES, c->ksk, B2FHE_KSK_DEV_BYTES, cudaMemcpyDeviceToHost));
     WireOut w(p, kCacheHeader);
     w.raw("B2FHEKC1", 8);
@@ -246,12 +246,11 @@ int b2fhe_init_from_key_cache(int ngpu, const void* blob, size_t len)
     }
     DevCtx& c = g_ctx[0];
     CK(cudaSetDevice(0));
-    CK(cudaMalloc(&c.bk_ntt, B2FHE_BK_NTT_BYTES));
+    CK(cudaMalloc(&c.bk, B2FHE_BK_NTT_BYTES));
     CK(cudaMalloc(&c.ksk, B2FHE_KSK_DEV_BYTES));
     c.owns_keys = true;
-    CK(cudaMemcpy(c.bk_ntt, payload, B2FHE_BK_NTT_BYTES, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c.bk, payload, B2FHE_BK_NTT_BYTES, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(c.ksk, payload + B2FHE_BK_NTT_BYTES, B2FHE_KSK_DEV_BYTES, cudaMemcpyHostToDevice));
-    if (int r = build_bk16(c)) return r;
     c.ready = true;
     return replicate_keys(ngpu);
 }

@@ -26,7 +26,7 @@
 // (reference include/gatebootstrapping_gpu.cuh:115-345), SampleExtract src/bootstrap_gpu.cu:366-381.
 #pragma once
 #include <cooperative_groups.h>
-#include "k_blindrotate16.cuh"
+#include "team16_dev.cuh"
 
 namespace b2 {
 

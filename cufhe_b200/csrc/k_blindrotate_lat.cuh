@@ -14,7 +14,7 @@
 // (__BlindRotatePreAdd__ + Accumulate, include/gatebootstrapping_gpu.cuh:115-345;
 // SampleExtract src/bootstrap_gpu.cu:366-381).
 #pragma once
-#include "k_blindrotate16.cuh"
+#include "team16_dev.cuh"
 
 namespace b2 {
 

@@ -93,10 +93,10 @@ struct SAddr {              // per-thread shared-window byte addresses
     uint32_t vw;            // vector scatter base 20 (T&15) + 4 (T>>4) words  (+ 336 words per kh)   A->D, D->A
     uint32_t sw;            // word scatter base 336 (T>>4) + (T&15) words     (+ 20 words per k)     D<->C
     uint32_t oth;           // the other team's chunk_of(T) in its array 0 (residue hand-over)
-    uint32_t tT;            // &tab.perT[q][0][T]    (+ 1024 bytes per vector)
-    uint32_t tLo;           // &tab.i2[q][0][T&15]   (+ 256 bytes per vector)
-    uint32_t tHi;           // &tab.f2[q][T>>4][0]   (+ 16 bytes per vector)
-    uint32_t lut;           // &tab.lut[q][0][0]     (+ 2048 bytes per table, 8 bytes per entry)
+    uint32_t tT;            // &tab.pr[q].perT[0][T]   (+ 1024 bytes per vector)
+    uint32_t tLo;           // &tab.pr[q].i2[0][T&15]   (+ 256 bytes per vector)
+    uint32_t tHi;           // &tab.pr[q].f2[T>>4][0]   (+ 16 bytes per vector)
+    uint32_t lut;           // &tab.pr[q].lut[0][0]   (+ 2048 bytes per table, 8 bytes per entry)
 };
 constexpr int kXsBytes = kXsWords * 4;
 
@@ -375,10 +375,10 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P,
     a.vw = smem_u32(xs + 20 * (T & 15) + 4 * (T >> 4));
     a.sw = smem_u32(xs + 336 * (T >> 4) + (T & 15));
     a.oth = smem_u32(xs_other + chunk_of(T));
-    a.tT = smem_u32(&tab->perT[q][0][T]);
-    a.tLo = smem_u32(&tab->i2[q][0][T & 15]);
-    a.tHi = smem_u32(&tab->f2[q][T >> 4][0]);
-    a.lut = smem_u32(&tab->lut[q][0][0]);
+    a.tT = smem_u32(&tab->pr[q].perT[0][T]);
+    a.tLo = smem_u32(&tab->pr[q].i2[0][T & 15]);
+    a.tHi = smem_u32(&tab->pr[q].f2[T >> 4][0]);
+    a.lut = smem_u32(&tab->pr[q].lut[0][0]);
 
     // ---- pre-add + modulus switch (gatebootstrapping_gpu.cuh:316-345) ----
     BrItem it;

@@ -10,7 +10,7 @@
 // [4 rows][2 primes][2 outputs][1024] u32 Montgomery residues in bk16_slot order (65536 B)
 // -- the layout of one bootstrapping-key row.
 #pragma once
-#include "k_blindrotate16.cuh"
+#include "team16_dev.cuh"
 
 namespace b2 {
 

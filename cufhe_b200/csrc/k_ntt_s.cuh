@@ -1,0 +1,265 @@
+// k_ntt_s.cuh -- batched stand-alone transforms on the 64-thread x 16-coefficient team schedule
+// (ntt16s.cuh): bootstrapping-key conversion, TRGSW conversion, and the NTT / INTT / negacyclic
+// product microbenchmark entry points (BASELINE config 2).
+//
+// Replaces: __TRGSW2NTT__ / BootstrappingKeyToNTT (reference src/bootstrap_gpu.cu:43-70,111-138)
+// and the test-only ForwardNTT / PointwiseMultiply / InverseNTT kernels
+// (test/test_polynomial_mult_1024.cu:76-99).
+//
+// A team of 64 threads transforms one polynomial for one prime; a CTA holds several teams and loops
+// over its share of the batch (persistent CTAs: the 61 KB / 92 KB of tables are staged once).
+// Global traffic is coalesced on both sides: natural-order polynomials are read / written 256
+// contiguous bytes per team and register (layout A), NTT-domain polynomials as one 128-bit vector
+// per thread in bk16_slot order (the order the bootstrapping key is stored in).  These kernels sit
+// on the HBM side of the ridge: a forward transform moves 4 + 4 KB per prime for 5120 butterflies.
+#pragma once
+#include "k_blindrotate_s.cuh"
+
+namespace b2 {
+
+constexpr int kNttTeams = 8;                         // teams per CTA of the transform kernels
+constexpr int kNttThreadsS = 64 * kNttTeams;
+template <int NPR, int TEAMS> __host__ __device__ constexpr int ntt_s_smem_bytes() { return NPR * (int)sizeof(PrimeSTables) + TEAMS * 2 * kXsBytes; }
+
+template <int NPR>
+__device__ __forceinline__ void stage_prime_tables(uint32_t* s_tab, const PrimeSTables* g_tab)
+{
+    const uint4* src = reinterpret_cast<const uint4*>(g_tab);
+    uint4* dst = reinterpret_cast<uint4*>(s_tab);
+    for (int i = threadIdx.x; i < NPR * (int)sizeof(PrimeSTables) / 16; i += blockDim.x) dst[i] = __ldg(src + i);
+}
+__device__ __forceinline__ SAddr team_addr(uint32_t* smem, int nprimes, int team, int q, int T)
+{
+    const PrimeSTables* tab = reinterpret_cast<const PrimeSTables*>(smem) + q;
+    uint32_t* xs = smem + nprimes * (sizeof(PrimeSTables) / 4) + team * 2 * kXsWords;
+    SAddr a;
+    a.own = smem_u32(xs + chunk_of(T));
+    a.vw = smem_u32(xs + 20 * (T & 15) + 4 * (T >> 4));
+    a.sw = smem_u32(xs + 336 * (T >> 4) + (T & 15));
+    a.oth = 0;
+    a.tT = smem_u32(&tab->perT[0][T]);
+    a.tLo = smem_u32(&tab->i2[0][T & 15]);
+    a.tHi = smem_u32(&tab->f2[T >> 4][0]);
+    a.lut = smem_u32(&tab->lut[0][0]);
+    return a;
+}
+__device__ __forceinline__ int32_t prime_of(int q) { return (int32_t)(q == 0 ? Prime<0>::p : q == 1 ? Prime<1>::p : Prime<2>::p); }
+__device__ __forceinline__ uint32_t pinv_of(int q) { return q == 0 ? Prime<0>::pinv : q == 1 ? Prime<1>::pinv : Prime<2>::pinv; }
+
+// NP general polynomials (lazy residues, |x| < 2p, layout A) -> NTT domain (layout C).  `lead`: a
+// team barrier first (the arrays were read by their owners since the last barrier).
+template <int NP>
+__device__ __forceinline__ void sfwd_general_dev(int32_t (&x0)[16], int32_t (&x1)[16], const SAddr& a, const int q, const int32_t p,
+                                                 const int tbar, const bool lead, const int T)
+{
+    const Tws w1 = c_s.fw01[q][0], w2a = c_s.fw01[q][1], w2b = c_s.fw01[q][2];
+    spass_fwd01(x0, w1, w2a, w2b, p);
+    if (NP == 2) spass_fwd01(x1, w1, w2a, w2b, p);
+    if (lead) named_bar_sync(tbar, 64);
+    st_vec_contig<0>(x0, a.vw);
+    if (NP == 2) st_vec_contig<1>(x1, a.vw);
+    named_bar_sync(tbar, 64);
+    ld_own_strided<0>(x0, a.own);
+    if (NP == 2) ld_own_strided<1>(x1, a.own);
+    spass_fwd<NP>(x0, x1, TwLd<16, 0, false>{a.tHi, p, T}, p);
+    __syncwarp();
+    st_words<0>(x0, a.sw);
+    if (NP == 2) st_words<1>(x1, a.sw);
+    __syncwarp();
+    ld_own<0>(x0, a.own);
+    if (NP == 2) ld_own<1>(x1, a.own);
+    spass_fwd<NP>(x0, x1, TwLd<1024, 1024 * kVecF3, false>{a.tT, p, T}, p);
+}
+// one inverse transform incl. n^-1 psi^-e: layout C in, layout A out, values in [-p/4, 5p/4)
+__device__ __forceinline__ void sinv1_dev(int32_t (&x0)[16], const SAddr& a, const int q, const int32_t p, const int tbar, const int T)
+{
+    int32_t dummy[16];
+    const Tws* c1 = c_s.iv1[q];
+    spass_inv1<1>(x0, dummy, [&](int i) { return c1[i]; }, p);
+    __syncwarp();
+    st_words<0>(x0, a.sw);
+    __syncwarp();
+    ld_own<0>(x0, a.own);
+    spass_inv2<1>(x0, dummy, TwLd<256, 0, false>{a.tLo, p, T}, p);
+    named_bar_sync(tbar, 64);
+    st_vec_strided<0>(x0, a.vw);
+    named_bar_sync(tbar, 64);
+    ld_own<0>(x0, a.own);
+    spass_inv3<1>(x0, dummy, TwLd<1024, 1024 * kVecI3, false>{a.tT, p, T}, TwLd<1024, 1024 * kVecSc, false>{a.tT, p, T}, p);
+}
+// any u32 -> lazy residue in [0, 2p);  any int32 -> lazy residue with |r| < 1.3 p
+__device__ __forceinline__ int32_t lazy_u32(uint32_t v, int32_t p) { return (int32_t)(v - (v >> 27) * (uint32_t)p); }
+__device__ __forceinline__ int32_t lazy_s32(int32_t v, int32_t p) { return (int32_t)((uint32_t)v - (uint32_t)(v >> 27) * (uint32_t)p); }
+__device__ __forceinline__ uint32_t canon_s(int32_t r, int32_t p) { return (uint32_t)(r < 0 ? r + p : r); }
+
+// MODE 0: polynomials -> canonical residues, out[poly][2][1024]
+// MODE 1: bootstrapping key / TRGSW rows -> Montgomery-form residues in [0, p), out index
+//         ((pl>>1)*2 + q)*2 + (pl&1), i.e. [i][row][prime][out poly][1024]
+// both in bk16_slot order: thread T writes vector v = positions 16 T + 4 v .. + 3 at word (64 v + T) 4
+template <int MODE>
+__global__ void __launch_bounds__(kNttThreadsS) k_ntt_fwd_s(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int npoly,
+                                                            const PrimeSTables* __restrict__ g_tab)
+{
+    extern __shared__ __align__(16) uint32_t smem[];
+    stage_prime_tables<2>(smem, g_tab);
+    __syncthreads();
+    const int team = threadIdx.x >> 6, T = threadIdx.x & 63;
+    const int q = team & 1;
+    const SAddr a = team_addr(smem, 2, team, q, T);
+    const int32_t p = prime_of(q);
+    const uint32_t pinv = pinv_of(q);
+    const int tbar = 1 + team;
+    bool lead = false;
+    for (int pl = blockIdx.x * (kNttTeams / 2) + (team >> 1); pl < npoly; pl += gridDim.x * (kNttTeams / 2)) {
+        int32_t x[16], dummy[16];
+        const uint32_t* src = in + (size_t)pl * kN + T;
+#pragma unroll
+        for (int k = 0; k < 16; k++) x[k] = lazy_u32(__ldg(src + 64 * k), p);
+        sfwd_general_dev<1>(x, dummy, a, q, p, tbar, lead, T);
+        lead = true;
+        uint4* dst = reinterpret_cast<uint4*>(MODE == 1 ? out + ((size_t)((pl >> 1) * 2 + q) * 2 + (pl & 1)) * kN
+                                                        : out + ((size_t)pl * 2 + q) * kN) + T;
+        const uint32_t r2 = canon_s(c_s.r2[q], p);
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+            uint32_t r[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                if (MODE == 1) r[e] = canon_s(sreduce(smontmul1(x[4 * v + e], r2, p, pinv), p), p);      // x 2^32 mod p
+                else r[e] = canon_s(sreduce(x[4 * v + e], p), p);
+            }
+            dst[64 * v] = make_uint4(r[0], r[1], r[2], r[3]);
+        }
+    }
+}
+
+// inverse of MODE 0: in[poly][2][1024] residues -> out[poly][1024] = centred CRT value mod 2^32.
+// The two teams of a polynomial (one per prime) swap halves and each finishes 512 coefficients.
+__global__ void __launch_bounds__(kNttThreadsS) k_ntt_inv_s(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int npoly,
+                                                            const PrimeSTables* __restrict__ g_tab)
+{
+    extern __shared__ __align__(16) uint32_t smem[];
+    stage_prime_tables<2>(smem, g_tab);
+    __syncthreads();
+    const int team = threadIdx.x >> 6, T = threadIdx.x & 63;
+    const int q = team & 1;
+    SAddr a = team_addr(smem, 2, team, q, T);
+    a.oth = team_addr(smem, 2, team ^ 1, q ^ 1, T).own;
+    const int32_t p = prime_of(q);
+    const int tbar = 1 + team, pbar = 1 + kNttTeams + (team >> 1);
+    for (int pl = blockIdx.x * (kNttTeams / 2) + (team >> 1); pl < npoly; pl += gridDim.x * (kNttTeams / 2)) {   // pair-uniform
+        int32_t x[16];
+        const uint4* src = reinterpret_cast<const uint4*>(in + ((size_t)pl * 2 + q) * kN) + T;
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+            const uint4 t = __ldg(src + 64 * v);
+            x[4 * v] = (int32_t)t.x; x[4 * v + 1] = (int32_t)t.y; x[4 * v + 2] = (int32_t)t.z; x[4 * v + 3] = (int32_t)t.w;
+        }
+        named_bar_sync(pbar, 128);                      // the partner has read my chunk of the previous polynomial
+        sinv1_dev(x, a, q, p, tbar, T);
+        // team 0 finishes registers 0..7 (coefficients T + 64 k, k < 8), team 1 registers 8..15
+        if (q == 0) { sts128<0>(a.own, x[8], x[9], x[10], x[11]); sts128<16>(a.own, x[12], x[13], x[14], x[15]); }
+        else { sts128<0>(a.own, x[0], x[1], x[2], x[3]); sts128<16>(a.own, x[4], x[5], x[6], x[7]); }
+        named_bar_sync(pbar, 128);
+        const V4 o0 = lds128<0>(a.oth), o1 = lds128<16>(a.oth);
+        const int32_t ot[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
+        uint32_t* dst = out + (size_t)pl * kN + T;
+        const int32_t cw = c_s.crt.w, cws = c_s.crt.ws;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            if (q == 0) dst[64 * k] = scrt_lift32(x[k], ot[k], cw, cws);
+            else dst[64 * (8 + k)] = scrt_lift32(ot[k], x[8 + k], cw, cws);
+        }
+    }
+}
+
+// out = a (*) b negacyclic, mod 2^32.  a: any u32, b: int32.  NPR = 2: exact for |sum a_i b_j| < 2^52;
+// NPR = 3: exact for ALL inputs (|sum| < 2^73 < P/2 ~ 2^80), which covers the reference test's domain
+// a < 2^32, b < 2^18 (test/test_polynomial_mult_1024.cu:38-39) that a 2^53 modulus cannot.
+// A product is NPR teams (one per prime), two products per CTA; the last team finishes the CRT.
+template <int NPR>
+__global__ void __launch_bounds__(64 * NPR * 2) k_polymul_s(const uint32_t* __restrict__ a_in, const uint32_t* __restrict__ b_in,
+                                                            uint32_t* __restrict__ out, int npoly, const PrimeSTables* __restrict__ g_tab)
+{
+    extern __shared__ __align__(16) uint32_t smem[];
+    stage_prime_tables<NPR>(smem, g_tab);
+    __syncthreads();
+    const int team = threadIdx.x >> 6, T = threadIdx.x & 63;
+    const int slot = team / NPR, q = team - slot * NPR;
+    const SAddr a = team_addr(smem, NPR, team, q, T);
+    const int32_t p = prime_of(q);
+    const uint32_t pinv = pinv_of(q);
+    const int tbar = 1 + team, pbar = 1 + 2 * NPR + slot;
+    uint32_t own_of[NPR];                               // chunk T of array 0 of every team of my product
+#pragma unroll
+    for (int r = 0; r < NPR; r++) own_of[r] = team_addr(smem, NPR, slot * NPR + r, r, T).own;
+    bool lead = false;
+    for (int pl = blockIdx.x * 2 + slot; pl < npoly; pl += gridDim.x * 2) {                 // slot-uniform
+        int32_t x[16], y[16];
+        const uint32_t* pa = a_in + (size_t)pl * kN + T;
+        const uint32_t* pb = b_in + (size_t)pl * kN + T;
+#pragma unroll
+        for (int k = 0; k < 16; k++) { x[k] = lazy_u32(__ldg(pa + 64 * k), p); y[k] = lazy_s32((int32_t)__ldg(pb + 64 * k), p); }
+        if (lead) named_bar_sync(pbar, 64 * NPR);       // the finishing team has read the chunks of the previous product
+        sfwd_general_dev<2>(x, y, a, q, p, tbar, lead, T);
+        lead = true;
+        const uint32_t r2 = canon_s(c_s.r2[q], p);
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            const int32_t z = smontmul1(x[k], (uint32_t)sreduce(y[k], p), p, pinv);       // x y 2^-32, |z| < p
+            x[k] = smontmul1(z, r2, p, pinv);                                               // x y, |.| < p
+        }
+        sinv1_dev(x, a, q, p, tbar, T);
+        if (q != NPR - 1) {
+            sts128<0>(a.own, x[0], x[1], x[2], x[3]); sts128<16>(a.own, x[4], x[5], x[6], x[7]);
+            sts128<32>(a.own, x[8], x[9], x[10], x[11]); sts128<48>(a.own, x[12], x[13], x[14], x[15]);
+        }
+        named_bar_sync(pbar, 64 * NPR);
+        if (q == NPR - 1) {
+            int32_t s0[16];
+            ld_own<0>(s0, own_of[0]);
+            uint32_t* dst = out + (size_t)pl * kN + T;
+            if (NPR == 2) {
+                const int32_t cw = c_s.crt.w, cws = c_s.crt.ws;
+#pragma unroll
+                for (int k = 0; k < 16; k++) dst[64 * k] = scrt_lift32(s0[k], x[k], cw, cws);
+            } else {
+                int32_t s1[16];
+                ld_own<0>(s1, own_of[NPR - 2]);
+                const Tws c01 = c_s.crt, c02 = c_s.crt02, c12 = c_s.crt12;
+                const uint32_t p01 = c_s.p01;
+#pragma unroll
+                for (int k = 0; k < 16; k++) dst[64 * k] = scrt3_lift32(s0[k], s1[k], x[k], c01, c02, c12, p01);
+            }
+        }
+    }
+}
+
+// ---- integer-pipe peak probe (roofline denominator) -------------------
+// mode 0: independent IMAD (lo) chains; mode 1: the butterfly actually used
+// (IMAD.HI + 2 IMAD + IADD3 + IADD), 16 independent chains per thread, registers only.
+__global__ void __launch_bounds__(256) k_int_peak(uint32_t* out, int iters, int mode, uint32_t seed)
+{
+    uint32_t x[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) x[k] = seed * (threadIdx.x + 1) + k * 0x9E3779B9u;
+    const uint32_t w = (seed | 1u) % Prime<0>::p;
+    const Tw tw{w, seed * 2654435761u};
+    if (mode == 0) {
+        for (int it = 0; it < iters; it++) {
+#pragma unroll
+            for (int k = 0; k < 16; k++) x[k] = x[k] * w + seed;
+        }
+    } else {
+        for (int it = 0; it < iters; it++) {
+#pragma unroll
+            for (int k = 0; k < 16; k += 2) butterfly<0>(x[k], x[k + 1], tw);
+        }
+    }
+    uint32_t acc = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) acc ^= x[k];
+    if (acc == 0x12345678u) out[0] = acc;      // keeps the loop alive, practically never taken
+}
+
+}  // namespace b2

@@ -48,7 +48,14 @@ template <> struct Prime<1> {
     static constexpr uint32_t p = 132120577u;           // 63 * 2^21 + 1 = 2^27 - 2^21 + 1
     static constexpr uint32_t pinv = inv32(132120577u);
 };
-constexpr uint32_t kP[2] = {Prime<0>::p, Prime<1>::p};
+// third prime: ONLY for the exact polynomial product of the microbenchmark entry point (any u32 x int32
+// inputs, |sum| < 2^73 < P/2 ~ 2^80); the bootstrapping path needs two (|sum| < 2^51 < P/2 ~ 2^53)
+template <> struct Prime<2> {
+    static constexpr uint32_t p = 134250497u;           // 2^27 + 2^15 + 1
+    static constexpr uint32_t pinv = inv32(134250497u);
+};
+constexpr uint32_t kP[3] = {Prime<0>::p, Prime<1>::p, Prime<2>::p};
+constexpr uint32_t kPinv[3] = {Prime<0>::pinv, Prime<1>::pinv, Prime<2>::pinv};
 
 // a * b / 2^32 (mod p), result in (-p, p).  |a| < 2^31, 0 <= bt < p.
 // With bt = b * 2^32 mod p (Montgomery form) this is a * b mod p.

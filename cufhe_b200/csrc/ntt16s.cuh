@@ -48,6 +48,7 @@ struct alignas(8) I2 { int32_t x, y; };
 
 constexpr int kSolK[2] = {11, 21};                   // p_q = 2^27 - 2^k + 1
 static_assert(Prime<0>::p == (1u << 27) - (1u << 11) + 1u && Prime<1>::p == (1u << 27) - (1u << 21) + 1u, "Solinas primes");
+static_assert(16ull * Prime<2>::p > (1ull << 31) - (1ull << 24), "third prime: 2^31 / p > 15.9");
 
 constexpr int kChunkWords = 20;
 constexpr int kXsWords = 64 * kChunkWords + 48;      // 1328 words per exchange array
@@ -132,26 +133,42 @@ B2_HD uint32_t scrt_lift32(int32_t s0, int32_t s1, int32_t c, int32_t cs)
     return (uint32_t)s0 + (uint32_t)u * Prime<0>::p;
 }
 
+// three primes (Garner, centred at every level): the integer S, |S| < P/2 ~ 2^80, truncated to 32 bits
+B2_HD uint32_t scrt3_lift32(int32_t s0, int32_t s1, int32_t s2, const Tws c01, const Tws c02, const Tws c12, uint32_t p01)
+{
+    constexpr int32_t p1 = (int32_t)Prime<1>::p, p2 = (int32_t)Prime<2>::p;
+    int32_t u1 = sshoup(s1 - s0, c01.w, c01.ws, p1);
+    u1 = u1 > (p1 - 1) / 2 ? u1 - p1 : u1;                     // S = s0 + u1 p0 (mod p0 p1), centred
+    const int32_t t2 = sshoup(s2 - s0, c02.w, c02.ws, p2);    // (s2 - s0) / p0 mod p2
+    int32_t u2 = sshoup(t2 - u1, c12.w, c12.ws, p2);          // ((s2 - s0) / p0 - u1) / p1 mod p2
+    u2 = u2 > (p2 - 1) / 2 ? u2 - p2 : u2;
+    return (uint32_t)s0 + (uint32_t)u1 * Prime<0>::p + (uint32_t)u2 * p01;
+}
+
 // ---- tables ---------------------------------------------------------------------------------
 // Sixteen Tws per pass and thread = eight V4 vectors {w, ws, w', ws'}; index (2^s - 1) + g as in
 // ntt16.cuh.  [vec][T] order: a warp's LDS.128 is 512 contiguous bytes.  The three per-thread
 // sets share one base pointer.
 constexpr int kVecF3 = 0, kVecI3 = 8, kVecSc = 14, kVecPerT = 22;
-struct TeamSTables {
-    V4 perT[2][kVecPerT][64];   // [q][vec][T]: forward strides 8..1 (layout C) | inverse t = 256 (slots 0..3), 512 (4..11) | n^-1 psi^-(T + 64 k)
-    V4 i2[2][8][16];            // [q][vec][lo]      inverse t = 16..128     (layout D)
-    V4 f2[2][4][8];             // [q][hi][vec]      forward strides 128..16 (layout D); half-warp broadcast
+struct PrimeSTables {           // one prime; the shared-memory image a team works from
+    V4 perT[kVecPerT][64];      // [vec][T]: forward strides 8..1 (layout C) | inverse t = 256 (slots 0..3), 512 (4..11) | n^-1 psi^-(T + 64 k)
+    V4 i2[8][16];               // [vec][lo]      inverse t = 16..128     (layout D)
+    V4 f2[4][8];                // [hi][vec]      forward strides 128..16 (layout D); half-warp broadcast
     // gadget-digit tables, 8-byte entries indexed by the RAW digit byte d (standing for d - 128), centred
     // residues:  0: { W1 (d-128), - };  1: { W2a (d-128), W2b (d-128) };  2: { W2a W1 (d-128), W2b W1 (d-128) }
-    I2 lut[2][3][256];
+    I2 lut[3][256];
 };
+static_assert(sizeof(PrimeSTables) == 22528 + 2048 + 512 + 6144, "table layout");
+struct TeamSTables { PrimeSTables pr[2]; };          // the bootstrapping path: two primes
+struct TeamSTables3 { PrimeSTables pr[3]; };         // the exact polynomial product: three
 constexpr int kTeamSTableWords = sizeof(TeamSTables) / 4;
-static_assert(sizeof(TeamSTables) == 45056 + 4096 + 1024 + 12288, "table layout");
 struct TeamSConst {
-    Tws iv1[2][16];         // inverse t = 1..8, warp-uniform: index (2^u - 1) + j (those with j = 0 are 1)
-    Tws fw01[2][4];         // forward stages 0, 1 for general inputs: psi^brv(1), psi^brv(2), psi^brv(3)
+    Tws iv1[3][16];         // inverse t = 1..8, warp-uniform: index (2^u - 1) + j (those with j = 0 are 1)
+    Tws fw01[3][4];         // forward stages 0, 1 for general inputs: psi^brv(1), psi^brv(2), psi^brv(3)
     Tws crt;                // p0^-1 mod p1
-    int32_t r2[2];          // 2^64 mod p (to Montgomery form), centred
+    Tws crt02, crt12;       // p0^-1 mod p2, p1^-1 mod p2 (three-prime Garner)
+    uint32_t p01;           // p0 p1 mod 2^32
+    int32_t r2[3];          // 2^64 mod p (to Montgomery form), centred
 };
 
 inline int32_t h_centre(uint32_t v, uint32_t p) { return v > p / 2 ? (int32_t)v - (int32_t)p : (int32_t)v; }
@@ -166,58 +183,63 @@ inline Tws h_tws(uint32_t v, uint32_t p)
     return Tws{(int32_t)w, (int32_t)qv};
 }
 
-inline void make_tables16s(TeamSTables& L, TeamSConst& C)
+inline void make_prime_tables16s(PrimeSTables& L, TeamSConst& C, int q)
 {
-    for (int q = 0; q < 2; q++) {
-        const uint32_t p = kP[q];
-        const uint32_t psi = h_psi(p);
-        const uint32_t ipsi = h_powmod(psi, p - 2, p);
-        const uint32_t iw = h_mulmod(ipsi, ipsi, p);
-        const uint32_t ninv = h_powmod(kN, p - 2, p);
-        auto psirev = [&](unsigned idx) { return h_powmod(psi, brv10(idx), p); };
-        auto put = [&](V4* vec, int vstride, int idx, Tws t) {      // Tws number idx of a set
-            V4& v = vec[(idx >> 1) * vstride];
-            if (idx & 1) { v.z = t.w; v.w = t.ws; } else { v.x = t.w; v.y = t.ws; }
-        };
-        // forward stage st (2^st groups): element e uses psi^brv(2^st + (e >> (10 - st)))
-        for (int hi = 0; hi < 4; hi++) {
-            for (int s = 0; s < 4; s++)
-                for (int g = 0; g < (1 << s); g++)
-                    put(&L.f2[q][hi][0], 1, (1 << s) - 1 + g, h_tws(psirev((4u << s) + ((unsigned)hi << s) + g), p));
-            put(&L.f2[q][hi][0], 1, 15, Tws{0, 0});
-        }
-        for (int T = 0; T < 64; T++) {
-            for (int s = 0; s < 4; s++)
-                for (int g = 0; g < (1 << s); g++)
-                    put(&L.perT[q][kVecF3][T], 64, (1 << s) - 1 + g, h_tws(psirev((64u << s) + ((unsigned)T << s) + g), p));
-            put(&L.perT[q][kVecF3][T], 64, 15, Tws{0, 0});
-        }
-        // inverse DIT: half-size t uses w^-(j 512 / t), j = e mod t
-        for (int u = 0; u < 4; u++)
-            for (int j = 0; j < (1 << u); j++) C.iv1[q][(1 << u) - 1 + j] = h_tws(h_powmod(iw, (uint64_t)j * (512 >> u), p), p);
-        C.iv1[q][15] = Tws{0, 0};
-        for (int lo = 0; lo < 16; lo++) {
-            for (int u = 0; u < 4; u++)                   // t = 16 << u, j = lo + 16 g
-                for (int g = 0; g < (1 << u); g++)
-                    put(&L.i2[q][0][lo], 16, (1 << u) - 1 + g, h_tws(h_powmod(iw, (uint64_t)(lo + 16 * g) * (32 >> u), p), p));
-            put(&L.i2[q][0][lo], 16, 15, Tws{0, 0});
-        }
-        for (int T = 0; T < 64; T++) {
-            for (int g = 0; g < 4; g++) put(&L.perT[q][kVecI3][T], 64, g, h_tws(h_powmod(iw, (uint64_t)(T + 64 * g) * 2, p), p));   // t = 256
-            for (int g = 0; g < 8; g++) put(&L.perT[q][kVecI3][T], 64, 4 + g, h_tws(h_powmod(iw, (uint64_t)(T + 64 * g), p), p));   // t = 512
-            for (int k = 0; k < 16; k++) put(&L.perT[q][kVecSc][T], 64, k, h_tws(h_mulmod(ninv, h_powmod(ipsi, T + 64 * k, p), p), p));
-        }
-        const uint32_t w1 = psirev(1), w2a = psirev(2), w2b = psirev(3);
-        C.fw01[q][0] = h_tws(w1, p); C.fw01[q][1] = h_tws(w2a, p); C.fw01[q][2] = h_tws(w2b, p); C.fw01[q][3] = Tws{0, 0};
-        C.r2[q] = h_centre((uint32_t)((((unsigned __int128)1) << 64) % p), p);
-        for (int d = 0; d < 256; d++) {
-            const uint32_t v = d >= 128 ? (uint32_t)(d - 128) : p - (uint32_t)(128 - d);     // d - 128 mod p
-            L.lut[q][0][d] = I2{h_centre(h_mulmod(w1, v, p), p), 0};
-            L.lut[q][1][d] = I2{h_centre(h_mulmod(w2a, v, p), p), h_centre(h_mulmod(w2b, v, p), p)};
-            L.lut[q][2][d] = I2{h_centre(h_mulmod(h_mulmod(w2a, w1, p), v, p), p), h_centre(h_mulmod(h_mulmod(w2b, w1, p), v, p), p)};
-        }
+    const uint32_t p = kP[q];
+    const uint32_t psi = h_psi(p);
+    const uint32_t ipsi = h_powmod(psi, p - 2, p);
+    const uint32_t iw = h_mulmod(ipsi, ipsi, p);
+    const uint32_t ninv = h_powmod(kN, p - 2, p);
+    auto psirev = [&](unsigned idx) { return h_powmod(psi, brv10(idx), p); };
+    auto put = [&](V4* vec, int vstride, int idx, Tws t) {      // Tws number idx of a set
+        V4& v = vec[(idx >> 1) * vstride];
+        if (idx & 1) { v.z = t.w; v.w = t.ws; } else { v.x = t.w; v.y = t.ws; }
+    };
+    // forward stage st (2^st groups): element e uses psi^brv(2^st + (e >> (10 - st)))
+    for (int hi = 0; hi < 4; hi++) {
+        for (int s = 0; s < 4; s++)
+            for (int g = 0; g < (1 << s); g++)
+                put(&L.f2[hi][0], 1, (1 << s) - 1 + g, h_tws(psirev((4u << s) + ((unsigned)hi << s) + g), p));
+        put(&L.f2[hi][0], 1, 15, Tws{0, 0});
     }
+    for (int T = 0; T < 64; T++) {
+        for (int s = 0; s < 4; s++)
+            for (int g = 0; g < (1 << s); g++)
+                put(&L.perT[kVecF3][T], 64, (1 << s) - 1 + g, h_tws(psirev((64u << s) + ((unsigned)T << s) + g), p));
+        put(&L.perT[kVecF3][T], 64, 15, Tws{0, 0});
+    }
+    // inverse DIT: half-size t uses w^-(j 512 / t), j = e mod t
+    for (int u = 0; u < 4; u++)
+        for (int j = 0; j < (1 << u); j++) C.iv1[q][(1 << u) - 1 + j] = h_tws(h_powmod(iw, (uint64_t)j * (512 >> u), p), p);
+    C.iv1[q][15] = Tws{0, 0};
+    for (int lo = 0; lo < 16; lo++) {
+        for (int u = 0; u < 4; u++)                   // t = 16 << u, j = lo + 16 g
+            for (int g = 0; g < (1 << u); g++)
+                put(&L.i2[0][lo], 16, (1 << u) - 1 + g, h_tws(h_powmod(iw, (uint64_t)(lo + 16 * g) * (32 >> u), p), p));
+        put(&L.i2[0][lo], 16, 15, Tws{0, 0});
+    }
+    for (int T = 0; T < 64; T++) {
+        for (int g = 0; g < 4; g++) put(&L.perT[kVecI3][T], 64, g, h_tws(h_powmod(iw, (uint64_t)(T + 64 * g) * 2, p), p));   // t = 256
+        for (int g = 0; g < 8; g++) put(&L.perT[kVecI3][T], 64, 4 + g, h_tws(h_powmod(iw, (uint64_t)(T + 64 * g), p), p));   // t = 512
+        for (int k = 0; k < 16; k++) put(&L.perT[kVecSc][T], 64, k, h_tws(h_mulmod(ninv, h_powmod(ipsi, T + 64 * k, p), p), p));
+    }
+    const uint32_t w1 = psirev(1), w2a = psirev(2), w2b = psirev(3);
+    C.fw01[q][0] = h_tws(w1, p); C.fw01[q][1] = h_tws(w2a, p); C.fw01[q][2] = h_tws(w2b, p); C.fw01[q][3] = Tws{0, 0};
+    C.r2[q] = h_centre((uint32_t)((((unsigned __int128)1) << 64) % p), p);
+    for (int d = 0; d < 256; d++) {
+        const uint32_t v = d >= 128 ? (uint32_t)(d - 128) : p - (uint32_t)(128 - d);     // d - 128 mod p
+        L.lut[0][d] = I2{h_centre(h_mulmod(w1, v, p), p), 0};
+        L.lut[1][d] = I2{h_centre(h_mulmod(w2a, v, p), p), h_centre(h_mulmod(w2b, v, p), p)};
+        L.lut[2][d] = I2{h_centre(h_mulmod(h_mulmod(w2a, w1, p), v, p), p), h_centre(h_mulmod(h_mulmod(w2b, w1, p), v, p), p)};
+    }
+}
+inline void make_tables16s(TeamSTables3& L, TeamSConst& C)
+{
+    for (int q = 0; q < 3; q++) make_prime_tables16s(L.pr[q], C, q);
     C.crt = h_tws(h_powmod(kP[0] % kP[1], kP[1] - 2, kP[1]), kP[1]);
+    C.crt02 = h_tws(h_powmod(kP[0] % kP[2], kP[2] - 2, kP[2]), kP[2]);
+    C.crt12 = h_tws(h_powmod(kP[1] % kP[2], kP[2] - 2, kP[2]), kP[2]);
+    C.p01 = kP[0] * kP[1];
 }
 
 B2_HD Tws tws_lo(const V4& v) { return Tws{v.x, v.y}; }

@@ -176,11 +176,17 @@ int b2fhe_cmux_ntt_batch(int device, b2fhe_stream_t stream, uint32_t* out, const
  * All device pointers.  ntt: in[count][1024] u32 -> out[count][2][1024] residues mod the
  * two NTT primes (engine-internal order).  intt: inverse + centred CRT, mod 2^32.
  * polymul: out = a (*) b negacyclic mod 2^32, exact when |sum a_i b_j| < 2^52 with a read
- * as unsigned and b as SIGNED int32 (e.g. |b| <= 2^9). */
+ * as unsigned and b as SIGNED int32 (e.g. |b| <= 2^9); beyond that bound the words are wrong without
+ * an error (tests/test_gpu_parity.py pins the bound) -- use b2fhe_polymul1024_exact_batch. */
 int b2fhe_ntt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* in, size_t count);
 int b2fhe_intt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* in, size_t count);
 int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* a,
                             const uint32_t* b, size_t count);
+/* the same product, exact for EVERY input (a: any u32, b: any int32; |sum| < 2^73): three NTT primes,
+ * P ~ 2^80.  Covers the reference test's domain a < 2^32, b < 2^18 (test/test_polynomial_mult_1024.cu:
+ * 38-39,161-163; its own tolerance is <= 2, here 0), which the two-prime product above cannot. */
+int b2fhe_polymul1024_exact_batch(int device, b2fhe_stream_t stream, uint32_t* out, const uint32_t* a,
+                                  const uint32_t* b, size_t count);
 
 /* ---- wire formats.  Host memory, little-endian hosts. ----------------
  * TFHEpp's cereal portable_binary archives, default 128-bit parameter set:
@@ -205,18 +211,17 @@ int b2fhe_init_from_key_cache(int ngpu, const void* blob, size_t len);
 
 /* tuning / introspection */
 int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
-/* blind-rotation kernel: 0 = default (k_blind_rotate_cl4 up to 70 gates, k_blind_rotate_lat up
- * to one gate per SM, else k_blind_rotate16), 1 = k_blind_rotate_lat (one gate per 512-thread
- * CTA), 5 / 4 = k_blind_rotate_cl4 (one gate per cluster of 4 CTAs x 128 threads; hand-overs by
- * st.async + mbarrier / by cluster barriers), 2 =
- * k_blind_rotate_cl (first cluster design: 8 CTAs x 64 threads), 16 =
- * k_blind_rotate16 (128 threads x 16 coefficients per gate, one TRGSW row at a time), 19 = its
- * paired schedule (digit pairs and inverse pairs transformed together, one Montgomery reduction
- * per row pair; what 0 selects for large batches), 17 / 18 / 20 = steps towards / beyond it kept
- * for A/B, 21 = k_blind_rotate16q (paired, four exchange buffers per team), 32 = k_blind_rotate
- * (64 threads x 32 coefficients per gate).  All produce identical bits.  -1 / -2 switch off / on
- * the separate launch of a last partial wave (on by default; does not change the variant). */
+/* blind-rotation kernel: 0 = by batch size (k_blind_rotate_cl4 up to 70 gates, k_blind_rotate_lat up to
+ * one gate per SM -- both only while latency mode is on -- else k_blind_rotate_s), 1 = k_blind_rotate_lat
+ * (one gate per 512-thread CTA), 5 = k_blind_rotate_cl4 (one gate per cluster of 4 CTAs x 128 threads,
+ * hand-overs by st.async + mbarrier), 40 = k_blind_rotate_s (128 threads x 16 coefficients per gate, signed
+ * lazy residues, four gates per CTA), 48 = its timing experiment that reads key row 0 at every step (WRONG
+ * results, tools only).  0 / 1 / 5 / 40 produce identical bits.  -1 / -2 switch off / on the separate launch
+ * of a last partial wave (on by default; does not change the variant). */
 int b2fhe_set_br_variant(int variant);
+/* 1 (default): small batches use the latency kernels; 0: every batch uses the throughput kernel (right for
+ * many small calls in flight on many streams).  The choice depends on this setting and the batch size only. */
+int b2fhe_set_latency_mode(int on);
 /* key-switch kernel: 0 = by batch size (k_keyswitch_lat up to 32 gates per SM, else
  * k_keyswitch_step<16, 8>), 1 = k_keyswitch_lat (16 warps per gate), 2 = k_keyswitch (one
  * free-running warp per gate), 10..18 = k_keyswitch_step<W, SYNCJ> with W = 8 / 16 / 32 gates per

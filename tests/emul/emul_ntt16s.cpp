@@ -17,7 +17,7 @@
 #include "../../oracle/cufhe_oracle.h"
 
 using namespace b2;
-static TeamSTables L;
+static TeamSTables3 L;
 static TeamSConst C;
 static int g_conflicts = 0;
 static int64_t g_maxabs_fwd = 0, g_maxabs_inv = 0;
@@ -102,18 +102,18 @@ static void fwd_tail(Team x, int q)   // after stages 0, 1 (layout A): layout C 
     const int32_t p = (int32_t)kP[q];
     int32_t dummy[16];
     xchg_AD(x);
-    for (int t = 0; t < 64; t++) spass_fwd<1>(x[t], dummy, [&](int v) { return L.f2[q][t >> 4][v]; }, p);
+    for (int t = 0; t < 64; t++) spass_fwd<1>(x[t], dummy, [&](int v) { return L.pr[q].f2[t >> 4][v]; }, p);
     track(x, g_maxabs_fwd);
     xchg_DC(x);
-    for (int t = 0; t < 64; t++) spass_fwd<1>(x[t], dummy, [&](int v) { return L.perT[q][kVecF3 + v][t]; }, p);
+    for (int t = 0; t < 64; t++) spass_fwd<1>(x[t], dummy, [&](int v) { return L.pr[q].perT[kVecF3 + v][t]; }, p);
     track(x, g_maxabs_fwd);
 }
 static void fwd_digits(Team x, int q)   // raw digits in [0, 256), layout A
 {
     for (int t = 0; t < 64; t++) {
         for (int k = 0; k < 4; k++) x[t][k] -= 128;          // slot k holds the signed digit, the others the raw byte (table handle)
-        spass_digits(x[t], [&](int32_t d) { return L.lut[q][0][d].x; }, [&](int32_t d) { return L.lut[q][1][d]; },
-                     [&](int32_t d) { return L.lut[q][2][d]; });
+        spass_digits(x[t], [&](int32_t d) { return L.pr[q].lut[0][d].x; }, [&](int32_t d) { return L.pr[q].lut[1][d]; },
+                     [&](int32_t d) { return L.pr[q].lut[2][d]; });
     }
     fwd_tail(x, q);
 }
@@ -129,11 +129,11 @@ static void inv(Team x, int q)   // layout C in, layout A out, [-p/4, 5p/4)
     for (int t = 0; t < 64; t++) spass_inv1<1>(x[t], dummy, [&](int i) { return C.iv1[q][i]; }, p);
     track(x, g_maxabs_inv);
     xchg_DC(x);
-    for (int t = 0; t < 64; t++) spass_inv2<1>(x[t], dummy, [&](int v) { return L.i2[q][v][t & 15]; }, p);
+    for (int t = 0; t < 64; t++) spass_inv2<1>(x[t], dummy, [&](int v) { return L.pr[q].i2[v][t & 15]; }, p);
     track(x, g_maxabs_inv);
     xchg_DA(x);
     for (int t = 0; t < 64; t++)
-        spass_inv3<1>(x[t], dummy, [&](int v) { return L.perT[q][kVecI3 + v][t]; }, [&](int v) { return L.perT[q][kVecSc + v][t]; }, p);
+        spass_inv3<1>(x[t], dummy, [&](int v) { return L.pr[q].perT[kVecI3 + v][t]; }, [&](int v) { return L.pr[q].perT[kVecSc + v][t]; }, p);
 }
 
 // key polynomial -> NTT domain, Montgomery form in [0, p), bk16_slot order
@@ -146,7 +146,7 @@ static void key_to_ntt(uint32_t* dst, const uint32_t* src, int q)
     fwd_general(x, q);
     for (int t = 0; t < 64; t++)
         for (int k = 0; k < 16; k++) {
-            int32_t m = smontmul1(x[t][k], (uint32_t)C.r2[q] + (C.r2[q] < 0 ? p : 0), (int32_t)p, q ? Prime<1>::pinv : Prime<0>::pinv);
+            int32_t m = smontmul1(x[t][k], (uint32_t)C.r2[q] + (C.r2[q] < 0 ? p : 0), (int32_t)p, kPinv[q]);
             m %= (int32_t)p;
             dst[bk16_slot(t, k)] = (uint32_t)(m < 0 ? m + (int32_t)p : m);
         }
@@ -166,11 +166,45 @@ static int check_polymul(std::mt19937_64& rng)
         fwd_digits(x[q], q);
         for (int t = 0; t < 64; t++)
             for (int k = 0; k < 16; k++)
-                x[q][t][k] = smontmul1(x[q][t][k], an[q][bk16_slot(t, k)], (int32_t)kP[q], q ? Prime<1>::pinv : Prime<0>::pinv);
+                x[q][t][k] = smontmul1(x[q][t][k], an[q][bk16_slot(t, k)], (int32_t)kP[q], kPinv[q]);
         inv(x[q], q);
     }
     for (int t = 0; t < 64; t++)
         for (int k = 0; k < 16; k++) out[eA(t, k)] = scrt_lift32(x[0][t][k], x[1][t][k], C.crt.w, C.crt.ws);
+    return memcmp(out, ref, sizeof ref) != 0;
+}
+
+// the exact product of the microbenchmark entry point (k_polymul_s<3>): a = any u32, b = any int32
+static int check_polymul3(std::mt19937_64& rng, int mode)
+{
+    static uint32_t a[kN], b[kN], ref[kN], out[kN];
+    for (int i = 0; i < kN; i++) {
+        a[i] = mode == 2 ? 0xFFFFFFFFu : (uint32_t)rng();
+        b[i] = mode == 0 ? (uint32_t)(rng() & 0x3FFFF) : mode == 2 ? 0x80000000u : (uint32_t)rng();      // 18-bit (the reference test's domain) / any
+    }
+    orc_polymul_schoolbook(ref, a, b);
+    static Team x[3], y[3];
+    for (int q = 0; q < 3; q++) {
+        const int32_t p = (int32_t)kP[q];
+        for (int t = 0; t < 64; t++)
+            for (int k = 0; k < 16; k++) {
+                const uint32_t v = a[eA(t, k)];
+                const int32_t w = (int32_t)b[eA(t, k)];
+                x[q][t][k] = (int32_t)(v - (v >> 27) * kP[q]);                                  // lazy_u32: [0, 2p)
+                y[q][t][k] = (int32_t)((uint32_t)w - (uint32_t)(w >> 27) * kP[q]);              // lazy_s32
+            }
+        fwd_general(x[q], q);
+        fwd_general(y[q], q);
+        for (int t = 0; t < 64; t++)
+            for (int k = 0; k < 16; k++) {
+                const int32_t z = smontmul1(x[q][t][k], (uint32_t)sreduce(y[q][t][k], p), p, kPinv[q]);
+                x[q][t][k] = smontmul1(z, (uint32_t)C.r2[q], p, kPinv[q]);
+            }
+        track(x[q], g_maxabs_inv);
+        inv(x[q], q);
+    }
+    for (int t = 0; t < 64; t++)
+        for (int k = 0; k < 16; k++) out[eA(t, k)] = scrt3_lift32(x[0][t][k], x[1][t][k], x[2][t][k], C.crt, C.crt02, C.crt12, C.p01);
     return memcmp(out, ref, sizeof ref) != 0;
 }
 
@@ -202,7 +236,7 @@ static int check_cmux(std::mt19937_64& rng, int worst)
                 for (int k = 0; k < 16; k++) { x0[t][k] = dig[0][eA(t, k)]; x1[t][k] = dig[1][eA(t, k)]; }
             fwd_digits(x0, q);
             fwd_digits(x1, q);
-            const uint32_t pinv = q ? Prime<1>::pinv : Prime<0>::pinv;
+            const uint32_t pinv = kPinv[q];
             for (int o = 0; o < 2; o++)
                 for (int t = 0; t < 64; t++)
                     for (int k = 0; k < 16; k++) {
@@ -244,7 +278,7 @@ static double bound_forward()
 }
 static double bound_inverse(double b0, int q)
 {
-    const double rho = (67108864.0 + 16.0 * ((1 << kSolK[q]) - 1)) / (double)kP[q];   // |sreduce|
+    const double rho = (67108864.0 + 16.0 * std::fabs(134217728.0 - (double)kP[q])) / (double)kP[q];   // |sreduce|
     std::vector<Iv> x(kN, Iv{-b0, b0});
     double m = b0;
     for (int st = 0; st < 10; st++) {
@@ -280,7 +314,7 @@ static int check_primitives(std::mt19937_64& rng)
         // pair product: |a| < 2^31, 0 <= b < p
         const int32_t a0 = (int32_t)rng(), a1 = (int32_t)rng();
         const uint32_t b0 = (uint32_t)(rng() % kP[q]), b1 = (uint32_t)(rng() % kP[q]);
-        const int32_t m2 = smontmul2(a0, b0, a1, b1, p, q ? Prime<1>::pinv : Prime<0>::pinv);
+        const int32_t m2 = smontmul2(a0, b0, a1, b1, p, kPinv[q]);
         const __int128 sum = (__int128)a0 * b0 + (__int128)a1 * b1;
         // m2 * 2^32 == sum (mod p)
         if ((int64_t)((((__int128)m2 << 32) - sum) % p) != 0) bad++;
@@ -299,16 +333,20 @@ int main(int argc, char** argv)
     int bad_m = 0, bad_c = 0;
     for (int i = 0; i < trials; i++) bad_m += check_polymul(rng);
     printf("polymul mismatches: %d / %d\n", bad_m, trials);
+    int bad_3 = 0;
+    for (int i = 0; i < trials; i++) bad_3 += check_polymul3(rng, i % 3);
+    printf("three-prime exact polymul mismatches: %d / %d\n", bad_3, trials);
     for (int i = 0; i < trials; i++) bad_c += check_cmux(rng, i % 4 == 3);
     printf("cmux mismatches: %d / %d\n", bad_c, trials);
     printf("bank conflicts: %d\n", g_conflicts);
     const double bf = bound_forward();
     // key products: two pair reductions, each |x0 b0 + x1 b1| / 2^32 + p/2 with |x| < bf p, b < p < 2^27
     const double b0 = 2.0 * (2.0 * bf / 32.0 + 0.5);
-    const double bi0 = bound_inverse(b0, 0), bi1 = bound_inverse(b0, 1);
-    const double lim0 = 2147483648.0 / kP[0], lim1 = 2147483648.0 / kP[1];
-    printf("bounds (units of p): forward %.3f, key products %.3f, inverse %.3f / %.3f, int32 limit %.4f / %.4f\n", bf, b0, bi0, bi1, lim0, lim1);
+    const double bi0 = bound_inverse(b0, 0), bi1 = bound_inverse(b0, 1), bi2 = bound_inverse(b0, 2);
+    const double lim0 = 2147483648.0 / kP[0], lim1 = 2147483648.0 / kP[1], lim2 = 2147483648.0 / kP[2];
+    const double bg = 2.0 + 10 * 1.25;       // general inputs (stand-alone transforms): [0, 2p) + ten stages
+    printf("bounds (units of p): forward %.3f (general inputs %.3f), key products %.3f, inverse %.3f / %.3f / %.3f, int32 limit %.4f / %.4f / %.4f\n", bf, bg, b0, bi0, bi1, bi2, lim0, lim1, lim2);
     printf("observed max |x| / p: forward %.3f, inverse %.3f\n", (double)g_maxabs_fwd / kP[1], (double)g_maxabs_inv / kP[1]);
-    const bool bounds_ok = bf + 0.01 < lim0 && bi0 + 0.01 < lim0 && bi1 + 0.01 < lim1;
-    return (bad_p || bad_m || bad_c || g_conflicts || !bounds_ok) ? 1 : 0;
+    const bool bounds_ok = bf + 0.01 < lim0 && bi0 + 0.01 < lim0 && bi1 + 0.01 < lim1 && bi2 + 0.01 < lim2 && bg + 0.01 < lim2;
+    return (bad_p || bad_m || bad_3 || bad_c || g_conflicts || !bounds_ok) ? 1 : 0;
 }

@@ -112,21 +112,27 @@ def test_adder_netlist_gate_count():
 
 
 # ------------------------------------- CUDA arithmetic, emulated on the CPU ---
-def test_warp_emulation_of_cuda_ntt_and_cmux(tmp_path):
-    """Compiles the SAME host+device headers the kernels use and runs the warp-level
-    dataflow (radix-32 passes, swizzled exchange, Montgomery MAC, CRT) lane by lane."""
+def test_team_emulation_of_signed_ntt_cmux_and_exact_product(tmp_path):
+    """Compiles the SAME host+device headers the throughput kernels use (csrc/ntt16s.cuh: signed lazy
+    residues, 128-bit exchanges) and runs the 64-thread team dataflow of k_blind_rotate_s /
+    k_polymul_s thread by thread against the oracle: CMUX steps, two-prime and exact three-prime
+    products, bank-conflict freedom of every exchange, interval bounds of the lazy residues."""
     orc.build()
-    exe = str(tmp_path / "emul_ntt")
-    subprocess.check_call(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "emul", "emul_ntt.cpp"),
+    exe = str(tmp_path / "emul_ntt16s")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "emul", "emul_ntt16s.cpp"),
                            "-L" + os.path.join(ROOT, "oracle"), "-lorc", "-Wl,-rpath," + os.path.join(ROOT, "oracle"),
                            "-fopenmp"])
-    out = subprocess.check_output([exe, "6"]).decode()
-    assert "polymul mismatches: 0 / 6" in out and "cmux mismatches: 0 / 6" in out
+    r = subprocess.run([exe, "6"], capture_output=True, text=True)
+    out = r.stdout
+    assert r.returncode == 0, out
+    assert "primitive mismatches (SOL == IMAD form, residues, ranges): 0" in out
+    assert "polymul mismatches: 0 / 6" in out and "three-prime exact polymul mismatches: 0 / 6" in out
+    assert "cmux mismatches: 0 / 6" in out and "bank conflicts: 0" in out
 
 
 def test_team_emulation_of_16_coefficient_ntt_and_cmux(tmp_path):
     """Same for the 64-thread x 16-coefficient team formulation (csrc/ntt16.cuh) behind
-    k_blind_rotate16: three passes, two padded exchanges; also checks that every exchange
+    the latency kernels (k_blind_rotate_cl4 / _lat) and k_cmux16: three passes, two padded exchanges; also checks that every exchange
     access pattern is shared-memory bank-conflict free."""
     orc.build()
     exe = str(tmp_path / "emul_ntt16")
@@ -134,7 +140,6 @@ def test_team_emulation_of_16_coefficient_ntt_and_cmux(tmp_path):
                            "-L" + os.path.join(ROOT, "oracle"), "-lorc", "-Wl,-rpath," + os.path.join(ROOT, "oracle"),
                            "-fopenmp"])
     out = subprocess.check_output([exe, "6"]).decode()
-    assert "position mismatches vs 32-coefficient transform: 0" in out
     assert "digit look-up pass mismatches: 0" in out
     assert "polymul mismatches: 0 / 6" in out and "cmux mismatches: 0 / 6" in out
     assert "pair / four-row multiply mismatches: 0" in out        # umontmul2_p / umontmul4_p of the paired kernels

@@ -89,6 +89,43 @@ def test_polymul_edge_cases(engine):
         assert np.array_equal(got[i], orc.polymul(a[i], b[i], schoolbook=True)), i
 
 
+def test_polymul_exact_reference_domain_batch_2e16(engine):
+    """BASELINE config 2 on the reference test's own input domain (test/test_polynomial_mult_1024.cu:38-39,
+    161-163): a = any u32, b < 2^18, batch 2^16 -- the three-prime product must equal the schoolbook
+    truth (test_polynomial_mult_1024.cu:51-73) with tolerance 0 (the reference allows 2) on a 256-polynomial
+    subsample, plus full-range / extreme operands."""
+    cf = engine
+    L = cf._lib.lib()
+    rng = np.random.default_rng(2)
+    cnt = 1 << 16
+    a = rng.integers(0, 2**32, size=(cnt, N), dtype=np.uint64).astype(np.uint32)
+    b = rng.integers(0, 1 << 18, size=(cnt, N), dtype=np.uint64).astype(np.uint32)
+    b[1] = rng.integers(0, 2**32, size=N, dtype=np.uint64).astype(np.uint32)        # any int32
+    a[2], b[2] = 0xFFFFFFFF, 0x80000000                                              # extreme magnitudes
+    a[3], b[3] = 0, 0x3FFFF
+    da, db = dev_u32(a), dev_u32(b)
+    dout = torch.empty((cnt, N), dtype=torch.int32, device="cuda")
+    cf._lib.check(L.b2fhe_polymul1024_exact_batch(0, None, dout.data_ptr(), da.data_ptr(), db.data_ptr(), cnt))
+    torch.cuda.synchronize()
+    got = to_np(dout, np.uint32)
+    idx = list(range(8)) + list(range(8, cnt, cnt // 248))[:248]
+    for i in idx:
+        assert np.array_equal(got[i], orc.polymul(a[i], b[i], schoolbook=True)), f"poly {i}"
+    # the two-prime product is exact inside its documented bound |sum| < 2^52 (b2fhe.h) ...
+    b9 = rng.integers(-512, 512, size=(64, N)).astype(np.int32).view(np.uint32)
+    d9 = dev_u32(b9)
+    o2 = torch.empty((64, N), dtype=torch.int32, device="cuda")
+    o3 = torch.empty_like(o2)
+    cf._lib.check(L.b2fhe_polymul1024_batch(0, None, o2.data_ptr(), da.data_ptr(), d9.data_ptr(), 64))
+    cf._lib.check(L.b2fhe_polymul1024_exact_batch(0, None, o3.data_ptr(), da.data_ptr(), d9.data_ptr(), 64))
+    torch.cuda.synchronize()
+    assert torch.equal(o2, o3)
+    # ... and NOT beyond it (which is why the exact entry point exists): 18-bit b overflows P ~ 2^53
+    cf._lib.check(L.b2fhe_polymul1024_batch(0, None, o2.data_ptr(), da.data_ptr(), db.data_ptr(), 64))
+    torch.cuda.synchronize()
+    assert not np.array_equal(to_np(o2, np.uint32)[0], got[0])
+
+
 # ------------------------------------------------------------------ stages ---
 def test_blind_rotate_and_keyswitch_stages(engine, keys):
     cf = engine
@@ -101,12 +138,10 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     d0 = torch.from_numpy(c0.view(np.int16)).cuda()
     d1 = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
     refs = [orc.blind_rotate_extract(keys, c0[i]) for i in range(cnt)]
-    # all blind-rotation kernels (5 / 4 = 4-CTA cluster kernel with st.async + mbarrier / with cluster barriers, 2 = 8-CTA cluster kernel, 1 = latency kernel, 16 = 128 threads/gate, 32 = 64 threads/gate),
+    # all blind-rotation kernels (5 = 4-CTA cluster kernel with st.async + mbarrier, 1 = latency kernel, 40 = the
+    # throughput kernel k_blind_rotate_s, 0 = by batch size),
     # every gates-per-CTA instantiation
-    for variant, gs in ((5, (0,)), (4, (0,)), (2, (0,)), (1, (0,)), (16, (0, 1, 2, 3, 4, 5, 6)),
-                        (17, (0, 3, 5)), (18, (0, 3, 5)), (19, (0, 1, 2, 3, 4, 5)), (20, (0, 3)), (21, (0, 1, 2, 3, 4)),
-                        (40, (0, 1, 2, 3, 4)),
-                        (32, (0, 1, 2, 4, 6, 8))):
+    for variant, gs in ((5, (0,)), (1, (0,)), (40, (0, 1, 2, 3, 4)), (0, (0,))):
         cf._lib.check(L.b2fhe_set_br_variant(variant))
         for g in gs:
             cf._lib.check(L.b2fhe_set_gates_per_cta(g))
@@ -351,9 +386,9 @@ def test_cluster_kernel_stress_against_throughput_kernel(engine):
         for cnt in (33, 70, 7):
             x = torch.from_numpy(rng.integers(0, 2**16, (cnt, 637), dtype=np.uint64).astype(np.uint16).view(np.int16)).cuda()
             want = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
-            cf._lib.check(L.b2fhe_set_br_variant(16))
+            cf._lib.check(L.b2fhe_set_br_variant(40))
             cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, want.data_ptr(), x.data_ptr(), 1 << 29, cnt))
-            for variant in (5, 4, 2):
+            for variant in (5, 1):
                 cf._lib.check(L.b2fhe_set_br_variant(variant))
                 for rep in range(6 if variant == 5 else 2):
                     got = torch.zeros_like(want)
@@ -366,11 +401,11 @@ def test_cluster_kernel_stress_against_throughput_kernel(engine):
 
 @pytest.mark.gpu
 def test_default_large_batch_paths_against_single_row_kernel(engine):
-    """The default large-batch path = paired k_blind_rotate16<4, 3> in full waves + a separate launch
-    (fewer gates per CTA) for a last partial wave, then k_keyswitch_step<32, 4>.  Batch sizes around
-    the wave boundaries (one gate over, one SM over, just below the no-split threshold, idle warps in
-    the last key-switch CTA) must reproduce the bits of the first-generation kernels
-    (k_blind_rotate16<4, 0>, k_keyswitch), with and without the split."""
+    """The default large-batch path = k_blind_rotate_s<4> in full waves + a separate launch (fewer gates
+    per CTA) for a last partial wave, then the key switch.  Batch sizes around the wave boundaries (one
+    gate over, one SM over, just below the no-split threshold, idle warps in the last key-switch CTA)
+    must reproduce the bits of the one-gate-per-CTA launch and of k_keyswitch, with and without the
+    split (the oracle pins the kernels themselves in test_blind_rotate_and_keyswitch_stages)."""
     cf = engine
     L = cf._lib.lib()
     rng = np.random.default_rng(99)
@@ -381,11 +416,13 @@ def test_default_large_batch_paths_against_single_row_kernel(engine):
             x = torch.from_numpy(rng.integers(0, 2**16, (cnt, 637), dtype=np.uint64).astype(np.uint16).view(np.int16)).cuda()
             want = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
             wks = torch.empty((cnt, 637), dtype=torch.int16, device="cuda")
-            cf._lib.check(L.b2fhe_set_br_variant(16))
+            cf._lib.check(L.b2fhe_set_br_variant(40))
+            cf._lib.check(L.b2fhe_set_gates_per_cta(1))              # same kernel, one gate per CTA, one launch
             cf._lib.check(L.b2fhe_set_ks_variant(2))
             cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, want.data_ptr(), x.data_ptr(), 1 << 29, cnt))
             cf._lib.check(L.b2fhe_keyswitch_batch(0, None, wks.data_ptr(), want.data_ptr(), cnt))
             cf._lib.check(L.b2fhe_set_br_variant(0))
+            cf._lib.check(L.b2fhe_set_gates_per_cta(0))
             cf._lib.check(L.b2fhe_set_ks_variant(0))
             for split in (-2, -1):
                 cf._lib.check(L.b2fhe_set_br_variant(split))
@@ -399,6 +436,7 @@ def test_default_large_batch_paths_against_single_row_kernel(engine):
     finally:
         cf._lib.check(L.b2fhe_set_br_variant(-2))
         cf._lib.check(L.b2fhe_set_br_variant(0))
+        cf._lib.check(L.b2fhe_set_gates_per_cta(0))
         cf._lib.check(L.b2fhe_set_ks_variant(0))
 
 
