@@ -114,9 +114,9 @@ int setup_device(int device)
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
-    CK(cudaFuncSetAttribute(k_ntt_fwd_s<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, kNttTeams>()));
-    CK(cudaFuncSetAttribute(k_ntt_fwd_s<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, kNttTeams>()));
-    CK(cudaFuncSetAttribute(k_ntt_inv_s, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, kNttTeams>()));
+    CK(cudaFuncSetAttribute(k_ntt_fwd_s<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_fwd_smem_bytes<kNttTeams>()));
+    CK(cudaFuncSetAttribute(k_ntt_fwd_s<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_fwd_smem_bytes<kNttTeams>()));
+    CK(cudaFuncSetAttribute(k_ntt_inv_s, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_inv_smem_bytes<kNttTeams>()));
     CK(cudaFuncSetAttribute(k_polymul_s<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, 4>()));
     CK(cudaFuncSetAttribute(k_polymul_s<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<3, 6>()));
     return noalloc_setup(device);
@@ -146,7 +146,7 @@ int convert_keys(int device, const uint32_t* bk_raw, const uint16_t* ksk_raw)
     CK(cudaMemcpy(d_raw, bk_raw, B2FHE_BK_RAW_WORDS * 4, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_kraw, ksk_raw, B2FHE_KSK_RAW_WORDS * 2, cudaMemcpyHostToDevice));
     const int npoly = kLwe * kRows * 2;
-    k_ntt_fwd_s<1><<<ntt_grid(c, npoly, kNttTeams / 2, 1), kNttThreadsS, ntt_s_smem_bytes<2, kNttTeams>()>>>(d_raw, c.bk, npoly, c.tabs->pr);
+    k_ntt_fwd_s<1><<<ntt_grid(c, npoly, kNttTeams / 2, 2), kNttThreadsS, ntt_fwd_smem_bytes<kNttTeams>()>>>(d_raw, c.bk, npoly, c.tabs->pr);
     LAUNCHED();
     k_ksk_layout<<<c.sm_count * 8, 256>>>(d_kraw, c.ksk);
     LAUNCHED();

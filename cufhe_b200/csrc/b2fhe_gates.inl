@@ -460,7 +460,7 @@ int b2fhe_trgsw2ntt_batch(int device, b2fhe_stream_t stream, uint32_t* out_ntt, 
     if (count == 0) return 0;
     REQUIRE(out_ntt && in_raw, B2FHE_E_BAD_ARGUMENT);
     const int npoly = (int)count * kRows * 2;
-    k_ntt_fwd_s<1><<<ntt_grid(*c, npoly, kNttTeams / 2, 1), kNttThreadsS, ntt_s_smem_bytes<2, kNttTeams>(), (cudaStream_t)stream>>>(
+    k_ntt_fwd_s<1><<<ntt_grid(*c, npoly, kNttTeams / 2, 2), kNttThreadsS, ntt_fwd_smem_bytes<kNttTeams>(), (cudaStream_t)stream>>>(
         in_raw, out_ntt, npoly, c->tabs->pr);
     LAUNCHED();
     return 0;
@@ -500,7 +500,7 @@ int b2fhe_ntt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const 
     if (int r = get_ctx(device, c)) return r;
     if (count == 0) return 0;
     REQUIRE(out && in && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    k_ntt_fwd_s<0><<<ntt_grid(*c, count, kNttTeams / 2, 1), kNttThreadsS, ntt_s_smem_bytes<2, kNttTeams>(), (cudaStream_t)stream>>>(
+    k_ntt_fwd_s<0><<<ntt_grid(*c, count, kNttTeams / 2, 2), kNttThreadsS, ntt_fwd_smem_bytes<kNttTeams>(), (cudaStream_t)stream>>>(
         in, out, (int)count, c->tabs->pr);
     LAUNCHED();
     return 0;
@@ -511,7 +511,7 @@ int b2fhe_intt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const
     if (int r = get_ctx(device, c)) return r;
     if (count == 0) return 0;
     REQUIRE(out && in && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    k_ntt_inv_s<<<ntt_grid(*c, count, kNttTeams / 2, 1), kNttThreadsS, ntt_s_smem_bytes<2, kNttTeams>(), (cudaStream_t)stream>>>(
+    k_ntt_inv_s<<<ntt_grid(*c, count, kNttTeams / 2, 2), kNttThreadsS, ntt_inv_smem_bytes<kNttTeams>(), (cudaStream_t)stream>>>(
         in, out, (int)count, c->tabs->pr);
     LAUNCHED();
     return 0;

@@ -43,12 +43,56 @@ __device__ __forceinline__ SAddr team_addr(uint32_t* smem, int nprimes, int team
     a.lut = smem_u32(&tab->lut[0][0]);
     return a;
 }
+// Compact shared-memory images for the one-direction kernels (the full 30 KB per prime would cap them at one
+// CTA per SM; they are memory-bound and want warps in flight):
+//   forward: per prime [perT rows F3 (8 KB)][f2 (512 B)]                      = 8704 B
+//   inverse: per prime [perT rows I3 + scale (14 KB)][i2 (2 KB)]              = 16384 B
+constexpr int kFwdImgBytes = 8 * 1024 + 512, kInvImgBytes = 14 * 1024 + 2048;
+__device__ __forceinline__ void stage_fwd_image(uint32_t* smem, const PrimeSTables* g)
+{
+    for (int q = 0; q < 2; q++) {
+        uint4* dst = reinterpret_cast<uint4*>(smem + q * (kFwdImgBytes / 4));
+        const uint4* rows = reinterpret_cast<const uint4*>(&g[q].perT[kVecF3][0]);
+        const uint4* f2 = reinterpret_cast<const uint4*>(&g[q].f2[0][0]);
+        for (int i = threadIdx.x; i < 512; i += blockDim.x) dst[i] = __ldg(rows + i);
+        for (int i = threadIdx.x; i < 32; i += blockDim.x) dst[512 + i] = __ldg(f2 + i);
+    }
+}
+__device__ __forceinline__ void stage_inv_image(uint32_t* smem, const PrimeSTables* g)
+{
+    for (int q = 0; q < 2; q++) {
+        uint4* dst = reinterpret_cast<uint4*>(smem + q * (kInvImgBytes / 4));
+        const uint4* rows = reinterpret_cast<const uint4*>(&g[q].perT[kVecI3][0]);
+        const uint4* i2 = reinterpret_cast<const uint4*>(&g[q].i2[0][0]);
+        for (int i = threadIdx.x; i < 14 * 64; i += blockDim.x) dst[i] = __ldg(rows + i);
+        for (int i = threadIdx.x; i < 128; i += blockDim.x) dst[14 * 64 + i] = __ldg(i2 + i);
+    }
+}
+// addresses of one team with ONE exchange array, over a compact image
+__device__ __forceinline__ SAddr team_addr_compact(uint32_t* smem, int img_bytes, int team, int q, int T, bool inverse)
+{
+    uint32_t* img = smem + q * (img_bytes / 4);
+    uint32_t* xs = smem + 2 * (img_bytes / 4) + team * kXsWords;
+    SAddr a;
+    a.own = smem_u32(xs + chunk_of(T));
+    a.vw = smem_u32(xs + 20 * (T & 15) + 4 * (T >> 4));
+    a.sw = smem_u32(xs + 336 * (T >> 4) + (T & 15));
+    a.oth = 0;
+    a.tT = smem_u32(img) + 16 * T;                                   // row r of the image at + 1024 r
+    a.tLo = inverse ? smem_u32(img) + 14 * 1024 + 16 * (T & 15) : 0;
+    a.tHi = inverse ? 0 : smem_u32(img) + 8 * 1024 + 128 * (T >> 4);
+    a.lut = 0;
+    return a;
+}
+template <int TEAMS> __host__ __device__ constexpr int ntt_fwd_smem_bytes() { return 2 * kFwdImgBytes + TEAMS * kXsBytes; }
+template <int TEAMS> __host__ __device__ constexpr int ntt_inv_smem_bytes() { return 2 * kInvImgBytes + TEAMS * kXsBytes; }
+
 __device__ __forceinline__ int32_t prime_of(int q) { return (int32_t)(q == 0 ? Prime<0>::p : q == 1 ? Prime<1>::p : Prime<2>::p); }
 __device__ __forceinline__ uint32_t pinv_of(int q) { return q == 0 ? Prime<0>::pinv : q == 1 ? Prime<1>::pinv : Prime<2>::pinv; }
 
 // NP general polynomials (lazy residues, |x| < 2p, layout A) -> NTT domain (layout C).  `lead`: a
 // team barrier first (the arrays were read by their owners since the last barrier).
-template <int NP>
+template <int NP, int ROWBASE = 0>
 __device__ __forceinline__ void sfwd_general_dev(int32_t (&x0)[16], int32_t (&x1)[16], const SAddr& a, const int q, const int32_t p,
                                                  const int tbar, const bool lead, const int T)
 {
@@ -68,9 +112,10 @@ __device__ __forceinline__ void sfwd_general_dev(int32_t (&x0)[16], int32_t (&x1
     __syncwarp();
     ld_own<0>(x0, a.own);
     if (NP == 2) ld_own<1>(x1, a.own);
-    spass_fwd<NP>(x0, x1, TwLd<1024, 1024 * kVecF3, false>{a.tT, p, T}, p);
+    spass_fwd<NP>(x0, x1, TwLd<1024, 1024 * (kVecF3 - ROWBASE), false>{a.tT, p, T}, p);
 }
 // one inverse transform incl. n^-1 psi^-e: layout C in, layout A out, values in [-p/4, 5p/4)
+template <int ROWBASE = 0>
 __device__ __forceinline__ void sinv1_dev(int32_t (&x0)[16], const SAddr& a, const int q, const int32_t p, const int tbar, const int T)
 {
     int32_t dummy[16];
@@ -85,7 +130,7 @@ __device__ __forceinline__ void sinv1_dev(int32_t (&x0)[16], const SAddr& a, con
     st_vec_strided<0>(x0, a.vw);
     named_bar_sync(tbar, 64);
     ld_own<0>(x0, a.own);
-    spass_inv3<1>(x0, dummy, TwLd<1024, 1024 * kVecI3, false>{a.tT, p, T}, TwLd<1024, 1024 * kVecSc, false>{a.tT, p, T}, p);
+    spass_inv3<1>(x0, dummy, TwLd<1024, 1024 * (kVecI3 - ROWBASE), false>{a.tT, p, T}, TwLd<1024, 1024 * (kVecSc - ROWBASE), false>{a.tT, p, T}, p);
 }
 // any u32 -> lazy residue in [0, 2p);  any int32 -> lazy residue with |r| < 1.3 p
 __device__ __forceinline__ int32_t lazy_u32(uint32_t v, int32_t p) { return (int32_t)(v - (v >> 27) * (uint32_t)p); }
@@ -101,11 +146,11 @@ __global__ void __launch_bounds__(kNttThreadsS) k_ntt_fwd_s(const uint32_t* __re
                                                             const PrimeSTables* __restrict__ g_tab)
 {
     extern __shared__ __align__(16) uint32_t smem[];
-    stage_prime_tables<2>(smem, g_tab);
+    stage_fwd_image(smem, g_tab);
     __syncthreads();
     const int team = threadIdx.x >> 6, T = threadIdx.x & 63;
     const int q = team & 1;
-    const SAddr a = team_addr(smem, 2, team, q, T);
+    const SAddr a = team_addr_compact(smem, kFwdImgBytes, team, q, T, false);
     const int32_t p = prime_of(q);
     const uint32_t pinv = pinv_of(q);
     const int tbar = 1 + team;
@@ -115,7 +160,7 @@ __global__ void __launch_bounds__(kNttThreadsS) k_ntt_fwd_s(const uint32_t* __re
         const uint32_t* src = in + (size_t)pl * kN + T;
 #pragma unroll
         for (int k = 0; k < 16; k++) x[k] = lazy_u32(__ldg(src + 64 * k), p);
-        sfwd_general_dev<1>(x, dummy, a, q, p, tbar, lead, T);
+        sfwd_general_dev<1, kVecF3>(x, dummy, a, q, p, tbar, lead, T);
         lead = true;
         uint4* dst = reinterpret_cast<uint4*>(MODE == 1 ? out + ((size_t)((pl >> 1) * 2 + q) * 2 + (pl & 1)) * kN
                                                         : out + ((size_t)pl * 2 + q) * kN) + T;
@@ -139,12 +184,12 @@ __global__ void __launch_bounds__(kNttThreadsS) k_ntt_inv_s(const uint32_t* __re
                                                             const PrimeSTables* __restrict__ g_tab)
 {
     extern __shared__ __align__(16) uint32_t smem[];
-    stage_prime_tables<2>(smem, g_tab);
+    stage_inv_image(smem, g_tab);
     __syncthreads();
     const int team = threadIdx.x >> 6, T = threadIdx.x & 63;
     const int q = team & 1;
-    SAddr a = team_addr(smem, 2, team, q, T);
-    a.oth = team_addr(smem, 2, team ^ 1, q ^ 1, T).own;
+    SAddr a = team_addr_compact(smem, kInvImgBytes, team, q, T, true);
+    a.oth = team_addr_compact(smem, kInvImgBytes, team ^ 1, q ^ 1, T, true).own;
     const int32_t p = prime_of(q);
     const int tbar = 1 + team, pbar = 1 + kNttTeams + (team >> 1);
     for (int pl = blockIdx.x * (kNttTeams / 2) + (team >> 1); pl < npoly; pl += gridDim.x * (kNttTeams / 2)) {   // pair-uniform
@@ -156,7 +201,7 @@ __global__ void __launch_bounds__(kNttThreadsS) k_ntt_inv_s(const uint32_t* __re
             x[4 * v] = (int32_t)t.x; x[4 * v + 1] = (int32_t)t.y; x[4 * v + 2] = (int32_t)t.z; x[4 * v + 3] = (int32_t)t.w;
         }
         named_bar_sync(pbar, 128);                      // the partner has read my chunk of the previous polynomial
-        sinv1_dev(x, a, q, p, tbar, T);
+        sinv1_dev<kVecI3>(x, a, q, p, tbar, T);
         // team 0 finishes registers 0..7 (coefficients T + 64 k, k < 8), team 1 registers 8..15
         if (q == 0) { sts128<0>(a.own, x[8], x[9], x[10], x[11]); sts128<16>(a.own, x[12], x[13], x[14], x[15]); }
         else { sts128<0>(a.own, x[0], x[1], x[2], x[3]); sts128<16>(a.own, x[4], x[5], x[6], x[7]); }
