@@ -58,6 +58,12 @@ int gate_ptrs(const DevCtx& c, cudaStream_t st, const uint8_t* ops, int level, v
     std::vector<const void*> tab(4 * (size_t)count);
     for (int g = 0; g < count; g++) {
         REQUIRE(out[g] && in0[g], B2FHE_E_BAD_ARGUMENT);
+        // two-input gates need in1, Mux / NMux also in2 (the rule of b2fhe_defer_gate): a null entry would make
+        // the gather skip the slot and the blind rotation read uninitialised staging memory
+        const int op = ops[g];
+        REQUIRE(op < B2FHE_NUM_OPS, B2FHE_E_BAD_ARGUMENT);
+        REQUIRE(op >= B2FHE_NOT || (in1 && in1[g]), B2FHE_E_BAD_ARGUMENT);
+        REQUIRE((op != B2FHE_MUX && op != B2FHE_NMUX) || (in2 && in2[g]), B2FHE_E_BAD_ARGUMENT);
         tab[g] = in0[g];
         tab[count + g] = in1 ? in1[g] : nullptr;
         tab[2 * (size_t)count + g] = in2 ? in2[g] : nullptr;

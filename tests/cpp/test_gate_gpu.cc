@@ -210,6 +210,38 @@ static void run_trlwe(const TFHEpp::EvalKey& ek)
     s.Destroy();
 }
 
+// operand uploads into buffers with a queued / finished device producer.
+//  (1) g* producer (device only, host copy stale), then a COPYING gate: the reference's stream order uploads
+//      the HOST bytes, so the host value must win;
+//  (2) copying producer, raw cudaDeviceSynchronize (not Synchronize), the caller re-encrypts into the same
+//      Ctxt's host copy, then a copying gate: the fresh host value must be used.
+template <class P> static void run_host_wins()
+{
+    const int level = sizeof(typename P::T) == 2 ? 0 : 1;
+    Stream s;
+    s.Create();
+    Ctxt<P> a, b, c, out;
+    int bad = 0;
+    enc<P>(a.tlwehost, 1, 900001); enc<P>(b.tlwehost, 1, 900002);
+    CtxtCopyH2D(a, s); CtxtCopyH2D(b, s);
+    enc<P>(c.tlwehost, 1, 900003);                 // host copy of c = 1 and stays 1
+    gNand<P>(c, a, b, s);                          // device copy of c = NAND(1, 1) = 0, host untouched
+    Nand<P>(out, c, a, s);                         // copying gate: uploads c's HOST bytes (1): NAND(1, 1) = 0
+    Synchronize();
+    if (dec<P>(out.tlwehost) != 0) bad++;
+    Nand<P>(c, a, b, s);                           // copying producer: c = 0 on device and host
+    StreamQuery(s);                                // starts the queue
+    cudaDeviceSynchronize();                       // raw wait, as test/test_intensive.cc:43
+    if (dec<P>(c.tlwehost) != 0) bad++;
+    enc<P>(c.tlwehost, 1, 900004);                 // caller re-encrypts into the same Ctxt
+    Nand<P>(out, c, a, s);                         // must see the fresh 1: NAND(1, 1) = 0 (stale device 0 would give 1)
+    Synchronize();
+    if (dec<P>(out.tlwehost) != 0) bad++;
+    printf("level %d operand uploads after device producers (host bytes win) : %s\n", level, bad ? "FAIL" : "PASS");
+    failures += bad;
+    s.Destroy();
+}
+
 int main()
 {
     cudaDeviceProp prop;
@@ -227,6 +259,8 @@ int main()
     run_chain<lvl0param>(ek, kNumSMs, true);
     run_chain<lvl1param>(ek, kNumSMs, false);
     run_trlwe(ek);
+    run_host_wins<lvl0param>();
+    run_host_wins<lvl1param>();
     CleanUp();
     printf(failures ? "FAILED (%d)\n" : "ALL PASS\n", failures);
     return failures ? 1 : 0;

@@ -58,6 +58,17 @@ def test_gate_batch_ptrs_errors(engine):
     assert L.b2fhe_gate_batch_ptrs(0, None, ops.ctypes.data, 0, nul, nul, nul, None, 2) != 0     # null operands
     assert L.b2fhe_gate_batch_ptrs(0, None, ops.ctypes.data, 3, nul, nul, nul, None, 2) != 0     # bad level
     assert L.b2fhe_gate_batch_ptrs(0, None, None, 0, None, None, None, None, 0) == 0             # empty batch
+    # a two-input gate with a null second operand / a Mux with a null third operand: rejected per gate
+    d = torch.zeros((2, 637), dtype=torch.int16, device="cuda")
+    ok = (C.c_void_p * 2)(d[0].data_ptr(), d[1].data_ptr())
+    half = (C.c_void_p * 2)(d[0].data_ptr(), None)
+    assert L.b2fhe_gate_batch_ptrs(0, None, ops.ctypes.data, 0, ok, ok, half, None, 2) == cf._lib.E_BAD_ARGUMENT
+    assert L.b2fhe_gate_batch_ptrs(0, None, ops.ctypes.data, 0, ok, ok, None, None, 2) == cf._lib.E_BAD_ARGUMENT
+    mux = np.full(2, orc.OP["MUX"], np.uint8)
+    assert L.b2fhe_gate_batch_ptrs(0, None, mux.ctypes.data, 0, ok, ok, ok, half, 2) == cf._lib.E_BAD_ARGUMENT
+    nots = np.full(2, orc.OP["NOT"], np.uint8)
+    assert L.b2fhe_gate_batch_ptrs(0, None, nots.ctypes.data, 0, ok, ok, None, None, 2) == 0     # unary: in1 not needed
+    torch.cuda.synchronize()
     assert L.b2fhe_defer_gate(0, None, 99, 0, C.c_void_p(8), C.c_void_p(8), None, None) != 0     # bad opcode
     assert L.b2fhe_defer_gate(0, None, orc.OP["MUX"], 0, C.c_void_p(8), C.c_void_p(8), C.c_void_p(8), None) != 0
     assert L.b2fhe_defer_pending(0) == 0
