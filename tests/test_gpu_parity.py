@@ -471,3 +471,39 @@ def test_default_keyswitch_step_above_latency_threshold(engine, keys):
     g = to_np(got, np.uint16)
     for i in (0, 1, 2, 3, cnt - 1):
         assert np.array_equal(g[i], orc.keyswitch(keys, x[i])), i
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("level", [0, 1])
+def test_mixed_batch_many_waves_equals_uniform_paths(engine, keys, level):
+    """BASELINE config 4 at a size where the host-built work lists cross SEVERAL waves of the blind rotation
+    (5 full waves + a partial one; Mux / NMux add two work items each): every gate of the mixed batch must
+    equal the same gate evaluated by the uniform per-op path (which the oracle and the reference GPU build pin
+    byte for byte on smaller batches), and decrypt to the truth table."""
+    cf = engine
+    L = cf._lib.lib()
+    sm = torch.cuda.get_device_properties(0).multi_processor_count
+    cnt = 5 * 4 * sm + 77
+    rng = np.random.default_rng(11 + level)
+    ops = (np.arange(cnt) % 14).astype(np.uint8)
+    b = [rng.integers(0, 2, cnt) for _ in range(3)]
+    x = [orc.encrypt(keys, b[k], level, base_index=2000000 + 100000 * k) for k in range(3)]
+    tdt = torch.int16 if level == 0 else torch.int32
+    dt = np.int16 if level == 0 else np.int32
+    d = [torch.from_numpy(v.view(dt)).cuda() for v in x]
+    out = torch.zeros_like(d[0])
+    cf._lib.check(L.b2fhe_gate_batch_mixed(0, None, ops.ctypes.data, level, out.data_ptr(), d[0].data_ptr(), d[1].data_ptr(),
+                                           d[2].data_ptr(), cnt))
+    torch.cuda.synchronize()
+    got = out.cpu().numpy().view(x[0].dtype)
+    for op in range(14):
+        idx = np.nonzero(ops == op)[0]
+        sub = [torch.from_numpy(np.ascontiguousarray(v[idx]).view(dt)).cuda() for v in x]
+        o = torch.zeros((len(idx), x[0].shape[1]), dtype=tdt, device="cuda")
+        unary, ternary = op >= 12, op in (10, 11)
+        cf._lib.check(L.b2fhe_gate_batch(0, None, op, level, o.data_ptr(), sub[0].data_ptr(), None if unary else sub[1].data_ptr(),
+                                         sub[2].data_ptr() if ternary else None, len(idx)))
+        torch.cuda.synchronize()
+        assert np.array_equal(got[idx], o.cpu().numpy().view(x[0].dtype)), f"op {op} level {level}"
+    dec = orc.decrypt(keys, got, level)
+    assert list(dec) == [orc.truth(int(ops[i]), int(b[0][i]), int(b[1][i]), int(b[2][i])) for i in range(cnt)]
