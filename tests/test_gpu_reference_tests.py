@@ -4,7 +4,11 @@ engine's header-only cufhe:: shim with REAL TFHEpp types (include/cufhe_b200.hpp
 `<include/cufhe_gpu.cuh>` resolves to oracle/shim) and linked with TFHEpp + libb2fhe.so by
 `make -C oracle reftests`.  The binaries are built where /root/reference exists and travel to the GPU
 box under oracle/_ref/reftests/.  This is the drop-in proof: the reference's user code, its harness and
-its truth tables, our engine underneath."""
+its truth tables, our engine underneath.
+
+No retry on a crash: the one intermittent SIGSEGV these programs showed was TFHEpp's own static initialiser
+storing with vmovapd into a 16-byte-aligned stack temporary (profiles/r2_reftest_static_init_crash.log);
+oracle/Makefile's REALIGN flags remove it, and segv_trace.cpp prints a backtrace should anything else die."""
 import os
 import re
 import subprocess
@@ -23,11 +27,6 @@ def _run(name, timeout=900):
     if not os.path.exists(exe):
         pytest.skip(f"{exe} not built (needs /root/reference at build time)")
     r = subprocess.run([exe], capture_output=True, text=True, timeout=timeout, cwd=ROOT)
-    if r.returncode < 0:        # killed by a signal: keep the backtrace (oracle/segv_trace.cpp) and try once more
-        first = f"first attempt died with signal {-r.returncode}\n{r.stderr[-3000:]}"
-        print(first)
-        r = subprocess.run([exe], capture_output=True, text=True, timeout=timeout, cwd=ROOT)
-        r.stderr = first + "\n--- second attempt ---\n" + r.stderr
     os.makedirs(OUT, exist_ok=True)
     with open(os.path.join(OUT, f"r2_reftest_{name}.log"), "w") as f:
         f.write(r.stdout + "\n--- stderr ---\n" + r.stderr)
