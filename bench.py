@@ -31,18 +31,19 @@ METRIC = "gate_bootstraps_per_sec_nand_batched"
 UNIT = "gates/s"
 # algorithmic figures per NAND bootstrap
 KEY_BYTES_PER_GATE = 41_680_896            # NTT-domain bootstrapping key touched per gate
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE k_blind_rotate16<4, 3> launch over 16384 gates
-# (profiles/r1_ncu_traffic_k_blind_rotate16_16384_v7.csv): keys once + ciphertext I/O, far below the
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE blind-rotation launch over 16384 gates (round 1's
+# kernel, profiles/r1_ncu_traffic_k_blind_rotate16_16384_v7.csv; only used when no profiles/*traffic*.csv
+# can be read): keys once + ciphertext I/O, far below the
 # algorithmic key bytes because each key row is served to all gates from L2
 DRAM_TRAFFIC_FALLBACK = 67_176_704 + 47_980_032
 
 
 def dram_traffic_per_launch():
-    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant blind-rotation launch, from the newest
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant blind-rotation launch, from the latest round's
     profiles/*traffic*.csv (an `ncu --csv` of the 16384-gate launch); (bytes, file) or the r1 figure."""
     import csv
     import glob
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*traffic*.csv")), key=os.path.getmtime)
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*traffic*.csv")), key=os.path.basename)     # rNN_ prefix: latest round last
     for path in reversed(files):
         try:
             tot, unit_scale = 0.0, {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
@@ -453,7 +454,7 @@ def run_product(args):
                     "d2h_bytes_per_step": cnt * 1274 * world},
             "single_gate_latency_ms": {"device_resident": lat_dev, "host_buffers": lat_host,
                                        "device_resident_keys_in_l2": lat_dev_warm,
-                                       "note": "one NAND: k_blind_rotate_cl4 (one gate per 4-CTA cluster, DSMEM) + k_keyswitch_lat; L2 is flushed "
+                                       "note": "one NAND: k_blind_rotate_cl4s (one gate per 4-CTA cluster, DSMEM) + k_keyswitch_lat; L2 is flushed "
                                                "before every call for the first two figures (keys come from HBM); the third "
                                                "repeats the call without the flush"},
             "gpu_launches": int(launches),

@@ -11,8 +11,7 @@
 #include "../../include/b2fhe.h"
 #include "k_blindrotate.cuh"
 #include "k_blindrotate_s.cuh"
-#include "k_blindrotate_lat.cuh"
-#include "k_blindrotate_cl4.cuh"
+#include "k_blindrotate_cl4s.cuh"
 #include "k_cmux.cuh"
 #include "k_keyswitch.cuh"
 #include "k_ntt_s.cuh"
@@ -27,8 +26,7 @@ struct DevCtx {
     bool owns_keys = false;
     uint32_t* bk = nullptr;         // NTT-domain key [636][4][2 primes][2][1024], Montgomery residues in [0, p), bk16_slot order
     uint32_t* ksk = nullptr;        // T[1024][7][3][320]
-    Lane16Tables* tab16 = nullptr;  // first-generation team tables (latency kernels, stand-alone CMUX)
-    TeamSTables3* tabs = nullptr;   // second-generation tables, three primes (the blind rotation stages the first two)
+    TeamSTables3* tabs = nullptr;   // team transform tables, three primes (the blind rotation stages the first two)
     int sm_count = 0;
 };
 DevCtx g_ctx[kMaxDev];
@@ -36,10 +34,10 @@ std::mutex g_mu;
 int g_gates_per_cta = 0;
 int g_ks_variant = 0;            // 0 = by batch size, 1 = k_keyswitch_lat, 2 = k_keyswitch
 int g_ks_lat_max_per_sm = 32;    // k_keyswitch_lat up to this many gates per SM (measured faster up to there)
-int g_br_cluster_max = 70;       // k_blind_rotate_cl4 up to this many gates: 33 four-CTA clusters run one CTA per SM (1.63 ms), up to 70 two per SM (2.2 ms); beyond that k_blind_rotate_lat (3.5 ms) wins
+int g_br_cluster_max = 70;       // k_blind_rotate_cl4s up to this many gates: 33 four-CTA clusters run one CTA per SM (1.43 ms), up to 70 two per SM (1.91 ms); beyond that k_blind_rotate_s with one gate per CTA (3.3 ms up to 148 gates) wins
 int g_latency_mode = 1;          // small calls: 1 = latency kernels (one gate over several SMs), 0 = always the throughput kernel (b2fhe_set_latency_mode)
-bool g_br_tail_split = true;     // last partial wave of k_blind_rotate16 as its own launch (b2fhe_set_br_variant(-1) / (-2) = off / on)
-int g_br_variant = 0;            // 0 = by batch size, 1 = k_blind_rotate_lat, 5 = k_blind_rotate_cl4, 40 = k_blind_rotate_s, 48 = its key-row-0 timing experiment
+bool g_br_tail_split = true;     // last partial wave of k_blind_rotate_s as its own launch (b2fhe_set_br_variant(-1) / (-2) = off / on)
+int g_br_variant = 0;            // 0 = by batch size, 5 = k_blind_rotate_cl4s, 40 = k_blind_rotate_s, 48 = its key-row-0 timing experiment
 std::atomic<uint64_t> g_launches{0};
 thread_local std::string t_err;
 
@@ -79,19 +77,11 @@ int setup_device(int device)
     CK(cudaSetDevice(device));
     DevCtx& c = g_ctx[device];
     if (c.tabs) return 0;
-    static NttTables T;
-    static Lane16Tables L16;
     static TeamSTables3 LS;
     static TeamSConst CS;
     static bool made = false;
-    if (!made) { make_tables(T); make_tables16(L16); make_tables16s(LS, CS); made = true; }
-    CK(cudaMemcpyToSymbol(c_fw1, T.fw1, sizeof T.fw1));
-    CK(cudaMemcpyToSymbol(c_iv1, T.iv1, sizeof T.iv1));
-    CK(cudaMemcpyToSymbol(c_r2, T.r2, sizeof T.r2));
-    CK(cudaMemcpyToSymbol(c_crt_p0inv, &T.crt_p0inv, sizeof(Tw)));
+    if (!made) { make_tables16s(LS, CS); made = true; }
     CK(cudaMemcpyToSymbol(c_s, &CS, sizeof CS));
-    CK(cudaMalloc(&c.tab16, sizeof(Lane16Tables)));
-    CK(cudaMemcpy(c.tab16, &L16, sizeof L16, cudaMemcpyHostToDevice));
     CK(cudaMalloc(&c.tabs, sizeof(TeamSTables3)));
     CK(cudaMemcpy(c.tabs, &LS, sizeof LS, cudaMemcpyHostToDevice));
     CK(cudaDeviceGetAttribute(&c.sm_count, cudaDevAttrMultiProcessorCount, device));
@@ -105,10 +95,9 @@ int setup_device(int device)
     if (int r = set_brs_attr<3>()) return r;
     if (int r = set_brs_attr<4>()) return r;
     CK(cudaFuncSetAttribute(k_blind_rotate_s<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(4)));
-    CK(cudaFuncSetAttribute(k_blind_rotate_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, kLatSmemBytes));
-    CK(cudaFuncSetAttribute(k_blind_rotate_cl4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
-    CK(cudaFuncSetAttribute(k_cmux16<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(1)));
-    CK(cudaFuncSetAttribute(k_cmux16<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(4)));
+    CK(cudaFuncSetAttribute(k_blind_rotate_cl4s, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
+    CK(cudaFuncSetAttribute(k_cmux_s<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(1)));
+    CK(cudaFuncSetAttribute(k_cmux_s<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(4)));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
@@ -208,7 +197,7 @@ int b2fhe_set_ks_variant(int variant)
 int b2fhe_set_br_variant(int variant)
 {
     if (variant == -1 || variant == -2) { g_br_tail_split = variant == -2; return 0; }
-    REQUIRE(variant == 0 || variant == 1 || variant == 5 || variant == 40 || variant == 48, B2FHE_E_BAD_ARGUMENT);
+    REQUIRE(variant == 0 || variant == 5 || variant == 40 || variant == 48, B2FHE_E_BAD_ARGUMENT);
     g_br_variant = variant;
     return 0;
 }
@@ -288,7 +277,6 @@ int b2fhe_cleanup(void)
         CK(cudaSetDevice(d));
         CK(cudaDeviceSynchronize());
         if (c.owns_keys) { CK(cudaFree(c.bk)); CK(cudaFree(c.ksk)); }
-        if (c.tab16) CK(cudaFree(c.tab16));
         if (c.tabs) CK(cudaFree(c.tabs));
         c = DevCtx();
     }

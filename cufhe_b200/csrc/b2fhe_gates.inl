@@ -23,14 +23,7 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
     // up to 70 gates: one gate per cluster of 4 CTAs x 128 threads (70 clusters are resident at once, two CTAs
     // per SM); hand-overs by st.async + mbarrier
     if (g_br_variant == 5 || (small_ok && P.count <= g_br_cluster_max)) {
-        k_blind_rotate_cl4<true><<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, c.tab16);
-        LAUNCHED();
-        return 0;
-    }
-    // up to one gate per SM: one gate per 512-thread CTA, 1 + 1 transforms on the critical path of a CMUX
-    // step instead of 4 + 2
-    if (g_br_variant == 1 || (small_ok && per_sm <= 1)) {
-        k_blind_rotate_lat<<<P.count, kLatThreads, kLatSmemBytes, st>>>(P, c.tab16);
+        k_blind_rotate_cl4s<<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, reinterpret_cast<const PrimeSTables*>(c.tabs));
         LAUNCHED();
         return 0;
     }
@@ -476,8 +469,8 @@ int b2fhe_cmux_ntt_batch(int device, b2fhe_stream_t stream, uint32_t* out, const
     REQUIRE(out && cs_ntt && c1 && c0, B2FHE_E_BAD_ARGUMENT);
     CmuxParams P{out, cs_ntt, c1, c0, (int)count, cs_per_item ? 1 : 0};
     cudaStream_t st = (cudaStream_t)stream;
-    if ((int)count >= 4 * c->sm_count) k_cmux16<4><<<((int)count + 3) / 4, 512, cmux_smem_bytes(4), st>>>(P, c->tab16);
-    else k_cmux16<1><<<(int)count, 128, cmux_smem_bytes(1), st>>>(P, c->tab16);
+    if ((int)count >= 4 * c->sm_count) k_cmux_s<4><<<((int)count + 3) / 4, 512, cmux_smem_bytes(4), st>>>(P, reinterpret_cast<const PrimeSTables*>(c->tabs));
+    else k_cmux_s<1><<<(int)count, 128, cmux_smem_bytes(1), st>>>(P, reinterpret_cast<const PrimeSTables*>(c->tabs));
     LAUNCHED();
     return 0;
 }

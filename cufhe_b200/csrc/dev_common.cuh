@@ -1,18 +1,10 @@
-// dev_common.cuh -- device-side plumbing shared by all kernels: warp-uniform twiddles in the
-// constant bank, named barriers, shared-window addresses.
+// dev_common.cuh -- device-side plumbing shared by all kernels: named barriers, shared-window addresses.
 #pragma once
 #include <cuda_runtime.h>
 #include "ntt_core.cuh"
 #include "tfhe_core.cuh"
 
 namespace b2 {
-
-// warp-uniform twiddles of the first-generation team transforms (ntt16.cuh): after unrolling every
-// index is a compile-time constant, so ptxas folds them into c[bank][imm] operands (no load).
-__constant__ Tw c_fw1[2][32];
-__constant__ Tw c_iv1[2][32];
-__constant__ uint32_t c_r2[2];
-__constant__ Tw c_crt_p0inv;
 
 // 32-bit shared-window address of a shared-memory pointer
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }

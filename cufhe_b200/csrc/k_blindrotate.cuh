@@ -1,5 +1,5 @@
 // k_blindrotate.cuh -- work-item and parameter types shared by the blind-rotation kernels
-// (k_blindrotate_s.cuh: throughput; k_blindrotate_cl4.cuh / k_blindrotate_lat.cuh: latency).
+// (k_blindrotate_s.cuh: throughput; k_blindrotate_cl4s.cuh: latency).
 //
 // They replace __BlindRotatePreAdd__/__BlindRotate__/Accumulate
 // (reference include/gatebootstrapping_gpu.cuh:115-345) and __SampleExtractIndex__
@@ -32,7 +32,7 @@ struct BrParams {
     int ca, cb, off;        // uniform coefficients
     uint32_t mu;            // test-vector constant (lvl1param::mu)
     int trlwe;              // 0: out[slot] = SampleExtract(0) (1025 words); 1: out[slot] = the TRLWE (2 x 1024 words)
-    int first;              // k_blind_rotate16 / _s only: this launch covers items first .. count-1
+    int first;              // k_blind_rotate_s only: this launch covers items first .. count-1
     uint32_t dbg;           // always 0 in the product; tools/ablate_brs.cu uses it as an opaque zero
 };
 

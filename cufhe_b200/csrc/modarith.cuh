@@ -57,65 +57,6 @@ template <> struct Prime<2> {
 constexpr uint32_t kP[3] = {Prime<0>::p, Prime<1>::p, Prime<2>::p};
 constexpr uint32_t kPinv[3] = {Prime<0>::pinv, Prime<1>::pinv, Prime<2>::pinv};
 
-// a * b / 2^32 (mod p), result in (-p, p).  |a| < 2^31, 0 <= bt < p.
-// With bt = b * 2^32 mod p (Montgomery form) this is a * b mod p.
-template <int Q>
-B2_HD int32_t montmul(int32_t a, uint32_t bt)
-{
-    const int64_t prod = (int64_t)a * (int64_t)(int32_t)bt;
-    const int32_t m = (int32_t)((uint32_t)prod * Prime<Q>::pinv);
-#ifdef __CUDA_ARCH__
-    const int32_t t = __mulhi(m, (int32_t)Prime<Q>::p);
-#else
-    const int32_t t = (int32_t)(((int64_t)m * (int64_t)Prime<Q>::p) >> 32);
-#endif
-    return (int32_t)(prod >> 32) - t;
-}
-
-// unsigned variant: 0 <= a < 2^32 (lazy residue), 0 <= bt < p; result in (-p, p).
-// Used for the key multiply-accumulate, where only ONE constant per key coefficient
-// is affordable (a Shoup companion would double the 41.7 MB key).
-B2_HD int32_t umontmul_p(uint32_t a, uint32_t bt, uint32_t p, uint32_t pinv)
-{
-    const uint64_t prod = (uint64_t)a * (uint64_t)bt;
-    const uint32_t m = (uint32_t)prod * pinv;
-#ifdef __CUDA_ARCH__
-    const uint32_t t = __umulhi(m, p);
-#else
-    const uint32_t t = (uint32_t)(((uint64_t)m * (uint64_t)p) >> 32);
-#endif
-    return (int32_t)((uint32_t)(prod >> 32) - t);
-}
-// a0 b0 + a1 b1 in one reduction: 0 <= a < 2^32, 0 <= b < p, so the 64-bit sum is < 2^33 p and the
-// result lies in (-p, 2p).  On sm_100a: two IMAD.WIDE (the second accumulates), IMAD, IMAD.HI.
-B2_HD uint32_t umontmul2_p(uint32_t a0, uint32_t b0, uint32_t a1, uint32_t b1, uint32_t p, uint32_t pinv)
-{
-    const uint64_t prod = (uint64_t)a0 * (uint64_t)b0 + (uint64_t)a1 * (uint64_t)b1;
-    const uint32_t m = (uint32_t)prod * pinv;
-#ifdef __CUDA_ARCH__
-    const uint32_t t = __umulhi(m, p);
-#else
-    const uint32_t t = (uint32_t)(((uint64_t)m * (uint64_t)p) >> 32);
-#endif
-    return (uint32_t)(prod >> 32) - t;
-}
-// four products in one reduction: the 64-bit sum is < 2^34 p < 2^61, result in (-p, 4p)
-B2_HD uint32_t umontmul4_p(uint32_t a0, uint32_t b0, uint32_t a1, uint32_t b1, uint32_t a2, uint32_t b2, uint32_t a3,
-                           uint32_t b3, uint32_t p, uint32_t pinv)
-{
-    const uint64_t prod = (uint64_t)a0 * (uint64_t)b0 + (uint64_t)a1 * (uint64_t)b1 + (uint64_t)a2 * (uint64_t)b2 +
-                          (uint64_t)a3 * (uint64_t)b3;
-    const uint32_t m = (uint32_t)prod * pinv;
-#ifdef __CUDA_ARCH__
-    const uint32_t t = __umulhi(m, p);
-#else
-    const uint32_t t = (uint32_t)(((uint64_t)m * (uint64_t)p) >> 32);
-#endif
-    return (uint32_t)(prod >> 32) - t;
-}
-template <int Q>
-B2_HD int32_t umontmul(uint32_t a, uint32_t bt) { return umontmul_p(a, bt, Prime<Q>::p, Prime<Q>::pinv); }
-
 // Shoup multiplication by a constant w < p with companion ws = floor(w * 2^32 / p):
 // v * w mod p in [0, 2p) for ANY 32-bit v.  One IMAD.HI + two IMAD on sm_100a, which
 // measures 1.7x faster than the Montgomery form (profiles/r1_ubench_butterfly_mix.log)
@@ -129,15 +70,6 @@ B2_HD uint32_t shoup_mul_p(uint32_t v, uint32_t w, uint32_t ws, uint32_t p)
 #endif
     return v * w - q * p;
 }
-template <int Q>
-B2_HD uint32_t shoup_mul(uint32_t v, uint32_t w, uint32_t ws) { return shoup_mul_p(v, w, ws, Prime<Q>::p); }
-
-// canonical representative in [0, p) of a value in (-p, p)
-template <int Q>
-B2_HD uint32_t canon(int32_t a)
-{
-    return (uint32_t)(a + ((a >> 31) & (int32_t)Prime<Q>::p));
-}
 
 // ---- host-only helpers for table generation --------------------------------
 inline uint32_t h_mulmod(uint32_t a, uint32_t b, uint32_t p) { return (uint32_t)((uint64_t)a * b % p); }
@@ -147,7 +79,6 @@ inline uint32_t h_powmod(uint32_t b, uint64_t e, uint32_t p)
     while (e) { if (e & 1) r = h_mulmod(r, b, p); b = h_mulmod(b, b, p); e >>= 1; }
     return r;
 }
-inline uint32_t h_to_mont(uint32_t a, uint32_t p) { return (uint32_t)((((uint64_t)a) << 32) % p); }
 inline uint32_t h_shoup(uint32_t w, uint32_t p) { return (uint32_t)((((uint64_t)w) << 32) / p); }
 // primitive 2N-th root of unity (smallest generator candidate g with (g^((p-1)/2N))^N == -1)
 inline uint32_t h_psi(uint32_t p)

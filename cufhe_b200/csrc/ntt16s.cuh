@@ -1,9 +1,10 @@
-// ntt16s.cuh -- second-generation 1024-point negacyclic NTT for a TEAM of 64 threads x 16
+// ntt16s.cuh -- 1024-point negacyclic NTT for a TEAM of 64 threads x 16
 // coefficients: SIGNED lazy residues, 128-bit exchanges, just-in-time twiddle vectors.
 //
-// Same transform as ntt16.cuh / ntt_core.cuh (merged-psi Cooley-Tukey forward, natural ->
-// bit-reversed; cyclic DIT inverse with w^-1 followed by n^-1 psi^-e), same NTT-domain
-// positions, so the bootstrapping key (bk16_slot order, Montgomery form in [0, p)) is shared.
+// The transform: merged-psi Cooley-Tukey forward, natural -> bit-reversed (stage s, 2^s groups: group i
+// of element e is e >> (10 - s), twiddle psi^brv(2^s + i)); cyclic DIT inverse with w^-1 (half-size t
+// uses w^-(j 512 / t), j = e mod t) followed by n^-1 psi^-e.  NTT-domain positions are stored in
+// bk16_slot order (ntt_core.cuh), Montgomery form in [0, p): the layout of the bootstrapping key.
 // Replaces SmallForwardNTT_1024 / SmallInverseNTT_1024 (reference
 // include/ntt_gpu/ntt_gpuntt.cuh:232-276,342-392).
 //
@@ -38,7 +39,7 @@
 // with four LDS.128; writers scatter vectors or words into other threads' chunks.  All accesses are
 // bank-conflict free (checked in tests/emul/emul_ntt16s.cpp).
 #pragma once
-#include "ntt16.cuh"
+#include "ntt_core.cuh"
 
 namespace b2 {
 
@@ -146,8 +147,8 @@ B2_HD uint32_t scrt3_lift32(int32_t s0, int32_t s1, int32_t s2, const Tws c01, c
 }
 
 // ---- tables ---------------------------------------------------------------------------------
-// Sixteen Tws per pass and thread = eight V4 vectors {w, ws, w', ws'}; index (2^s - 1) + g as in
-// ntt16.cuh.  [vec][T] order: a warp's LDS.128 is 512 contiguous bytes.  The three per-thread
+// Sixteen Tws per pass and thread = eight V4 vectors {w, ws, w', ws'}; index (2^s - 1) + g.
+// [vec][T] order: a warp's LDS.128 is 512 contiguous bytes.  The three per-thread
 // sets share one base pointer.
 constexpr int kVecF3 = 0, kVecI3 = 8, kVecSc = 14, kVecPerT = 22;
 struct PrimeSTables {           // one prime; the shared-memory image a team works from

@@ -46,19 +46,6 @@ constexpr uint32_t kDecompAdd = 0x80808000u;
 // digit d (0 = most significant) in [-128, 127] (gatebootstrapping_gpu.cuh:172-179)
 B2_HD int32_t digit(uint32_t t, int d) { return (int32_t)((t >> (24 - 8 * d)) & 0xFFu) - 128; }
 
-// centred CRT of lazy residues s0 in [0, 2 p0), s1 in [0, 2 p1): returns the integer S
-// (|S| < P/2) truncated to 32 bits == lift rule of the reference
-// (v > p/2 ? v - p : v, include/gatebootstrapping_gpu.cuh:258,270-281).
-B2_HD uint32_t crt_lift32(uint32_t s0, uint32_t s1, uint32_t c, uint32_t cs)
-{
-    constexpr uint32_t p1 = Prime<1>::p;
-    const uint32_t d = s1 + 3u * p1 - s0;               // == s1 - s0 (mod p1), positive: 2 p0 < 3 p1
-    uint32_t u = shoup_mul<1>(d, c, cs);                // (s1 - s0) / p0 mod p1, in [0, 2 p1)
-    u = u >= p1 ? u - p1 : u;
-    const int32_t uc = u > (p1 - 1) / 2 ? (int32_t)u - (int32_t)p1 : (int32_t)u;
-    return s0 + (uint32_t)uc * Prime<0>::p;
-}
-
 // identity key switch constants (include/keyswitch_gpu.cuh:13-23,92-95)
 constexpr uint32_t kIksAdd = 0xAAA80000u + (1u << 17);
 // digit d (0 = most significant) of the key-switch decomposition, in {0,1,2,3};

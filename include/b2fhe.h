@@ -211,12 +211,11 @@ int b2fhe_init_from_key_cache(int ngpu, const void* blob, size_t len);
 
 /* tuning / introspection */
 int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
-/* blind-rotation kernel: 0 = by batch size (k_blind_rotate_cl4 up to 70 gates, k_blind_rotate_lat up to
- * one gate per SM -- both only while latency mode is on -- else k_blind_rotate_s), 1 = k_blind_rotate_lat
- * (one gate per 512-thread CTA), 5 = k_blind_rotate_cl4 (one gate per cluster of 4 CTAs x 128 threads,
- * hand-overs by st.async + mbarrier), 40 = k_blind_rotate_s (128 threads x 16 coefficients per gate, signed
- * lazy residues, four gates per CTA), 48 = its timing experiment that reads key row 0 at every step (WRONG
- * results, tools only).  0 / 1 / 5 / 40 produce identical bits.  -1 / -2 switch off / on the separate launch
+/* blind-rotation kernel: 0 = by batch size (k_blind_rotate_cl4s up to 70 gates while latency mode is on,
+ * else k_blind_rotate_s), 5 = k_blind_rotate_cl4s (one gate per cluster of 4 CTAs x 128 threads, hand-overs
+ * by st.async + mbarrier), 40 = k_blind_rotate_s (128 threads x 16 coefficients per gate, signed lazy
+ * residues, four gates per CTA), 48 = its timing experiment that reads key row 0 at every step (WRONG
+ * results, tools only).  0 / 5 / 40 produce identical bits.  -1 / -2 switch off / on the separate launch
  * of a last partial wave (on by default; does not change the variant). */
 int b2fhe_set_br_variant(int variant);
 /* 1 (default): small batches use the latency kernels; 0: every batch uses the throughput kernel (right for

@@ -130,22 +130,6 @@ def test_team_emulation_of_signed_ntt_cmux_and_exact_product(tmp_path):
     assert "cmux mismatches: 0 / 6" in out and "bank conflicts: 0" in out
 
 
-def test_team_emulation_of_16_coefficient_ntt_and_cmux(tmp_path):
-    """Same for the 64-thread x 16-coefficient team formulation (csrc/ntt16.cuh) behind
-    the latency kernels (k_blind_rotate_cl4 / _lat) and k_cmux16: three passes, two padded exchanges; also checks that every exchange
-    access pattern is shared-memory bank-conflict free."""
-    orc.build()
-    exe = str(tmp_path / "emul_ntt16")
-    subprocess.check_call(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "emul", "emul_ntt16.cpp"),
-                           "-L" + os.path.join(ROOT, "oracle"), "-lorc", "-Wl,-rpath," + os.path.join(ROOT, "oracle"),
-                           "-fopenmp"])
-    out = subprocess.check_output([exe, "6"]).decode()
-    assert "digit look-up pass mismatches: 0" in out
-    assert "polymul mismatches: 0 / 6" in out and "cmux mismatches: 0 / 6" in out
-    assert "pair / four-row multiply mismatches: 0" in out        # umontmul2_p / umontmul4_p of the paired kernels
-    assert "bank conflicts: 0" in out
-
-
 # -------------------------------------------------------------- host logic ---
 def test_partition_covers_batch():
     from cufhe_b200.api import partition

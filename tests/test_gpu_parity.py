@@ -138,10 +138,10 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     d0 = torch.from_numpy(c0.view(np.int16)).cuda()
     d1 = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
     refs = [orc.blind_rotate_extract(keys, c0[i]) for i in range(cnt)]
-    # all blind-rotation kernels (5 = 4-CTA cluster kernel with st.async + mbarrier, 1 = latency kernel, 40 = the
+    # all blind-rotation kernels (5 = 4-CTA cluster kernel with st.async + mbarrier, 40 = the
     # throughput kernel k_blind_rotate_s, 0 = by batch size),
     # every gates-per-CTA instantiation
-    for variant, gs in ((5, (0,)), (1, (0,)), (40, (0, 1, 2, 3, 4)), (0, (0,))):
+    for variant, gs in ((5, (0,)), (40, (0, 1, 2, 3, 4)), (0, (0,))):
         cf._lib.check(L.b2fhe_set_br_variant(variant))
         for g in gs:
             cf._lib.check(L.b2fhe_set_gates_per_cta(g))
@@ -375,8 +375,8 @@ def test_full_batch_16384_nand(engine, keys):
 
 
 def test_cluster_kernel_stress_against_throughput_kernel(engine):
-    """The cluster kernels hand data between CTAs with st.async / mbarrier (or cluster barriers) and
-    reuse double-buffered receive areas every other step: a protocol slip would show up as sporadic
+    """The cluster kernel hands data between CTAs with 128-bit st.async stores / mbarriers and
+    reuses double-buffered receive areas every other step: a protocol slip would show up as sporadic
     corruption.  One CTA per SM (33 clusters), two per SM (70 clusters) and repeated launches on random
     inputs must reproduce the throughput kernel's bits every time."""
     cf = engine
@@ -388,13 +388,12 @@ def test_cluster_kernel_stress_against_throughput_kernel(engine):
             want = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
             cf._lib.check(L.b2fhe_set_br_variant(40))
             cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, want.data_ptr(), x.data_ptr(), 1 << 29, cnt))
-            for variant in (5, 1):
-                cf._lib.check(L.b2fhe_set_br_variant(variant))
-                for rep in range(6 if variant == 5 else 2):
-                    got = torch.zeros_like(want)
-                    cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, got.data_ptr(), x.data_ptr(), 1 << 29, cnt))
-                    torch.cuda.synchronize()
-                    assert torch.equal(got, want), (cnt, variant, rep)
+            cf._lib.check(L.b2fhe_set_br_variant(5))
+            for rep in range(6):
+                got = torch.zeros_like(want)
+                cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, got.data_ptr(), x.data_ptr(), 1 << 29, cnt))
+                torch.cuda.synchronize()
+                assert torch.equal(got, want), (cnt, rep)
     finally:
         cf._lib.check(L.b2fhe_set_br_variant(0))
 
@@ -443,7 +442,7 @@ def test_default_large_batch_paths_against_single_row_kernel(engine):
 @pytest.mark.gpu
 def test_default_keyswitch_step_above_latency_threshold(engine, keys):
     """Above 32 gates per SM the default key switch is k_keyswitch_step<16, 8> (below: k_keyswitch_lat).
-    A batch just over the threshold with a PARTIAL last CTA: every gate compared with the first-generation
+    A batch just over the threshold with a PARTIAL last CTA: every gate compared with the one-warp-per-gate
     k_keyswitch (variant 2), the first ones and the extreme rows with the oracle."""
     cf = engine
     L = cf._lib.lib()
