@@ -96,7 +96,7 @@ struct SAddr {              // per-thread shared-window byte addresses
     uint32_t tT;            // &tab.pr[q].perT[0][T]   (+ 1024 bytes per vector)
     uint32_t tLo;           // &tab.pr[q].i2[0][T&15]   (+ 256 bytes per vector)
     uint32_t tHi;           // &tab.pr[q].f2[T>>4][0]   (+ 16 bytes per vector)
-    uint32_t lut;           // &tab.pr[q].lut[0][0]   (+ 2048 bytes per table, 8 bytes per entry)
+    uint32_t lut;           // &tab.pr[q].lut0[0]   (4-byte entries; lut12[0], lut12[1] at + kLut1Off, + kLut2Off, 8-byte entries)
 };
 constexpr int kXsBytes = kXsWords * 4;
 
@@ -182,8 +182,8 @@ __device__ __forceinline__ void sfwd2_dev(int32_t (&x0)[16], int32_t (&x1)[16], 
 {
     {
         auto l0 = [](int32_t h) { return lds32<0>((uint32_t)h); };
-        auto l1 = [](int32_t h) { return lds64<2048>((uint32_t)h); };
-        auto l2 = [](int32_t h) { return lds64<4096>((uint32_t)h); };
+        auto l1 = [](int32_t h) { return lds64<kLut1Off>((uint32_t)h); };
+        auto l2 = [](int32_t h) { return lds64<kLut2Off>((uint32_t)h); };
         spass_digits(x0, l0, l1, l2);
         spass_digits(x1, l0, l1, l2);
     }
@@ -233,6 +233,9 @@ __device__ __forceinline__ void digits_dev(int32_t (&x0)[16], int32_t (&x1)[16],
         if (K < 4) {
             x0[K] = (int32_t)(t >> 24) - 128;
             x1[K] = (int32_t)((t >> 16) & 0xFFu) - 128;
+        } else if (K >= 8 && K < 12) {          // table 0: 4-byte entries
+            x0[K] = (int32_t)(lut + ((t >> 24) << 2));
+            x1[K] = (int32_t)(lut + (__byte_perm(t, 0, 0x4442) << 2));
         } else {
             x0[K] = (int32_t)(lut + ((t >> 24) << 3));
             x1[K] = (int32_t)(lut + (__byte_perm(t, 0, 0x4442) << 3));
@@ -277,8 +280,8 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, c
 #pragma unroll
             for (int k = 0; k < 16; k++) {
                 const uint32_t t = ((uint32_t)lds32<0>(own0 + 256 * k) & dbg) + (uint32_t)(T + 5 * k);
-                y0[k] = k < 4 ? (int32_t)(t & 0xFFu) - 128 : (int32_t)(a.lut + ((t & 0xFFu) << 3));
-                y1[k] = k < 4 ? (int32_t)((t + 7u) & 0xFFu) - 128 : (int32_t)(a.lut + (((t + 7u) & 0xFFu) << 3));
+                y0[k] = k < 4 ? (int32_t)(t & 0xFFu) - 128 : (int32_t)(a.lut + ((t & 0xFFu) << ((k >> 2) == 2 ? 2 : 3)));
+                y1[k] = k < 4 ? (int32_t)((t + 7u) & 0xFFu) - 128 : (int32_t)(a.lut + (((t + 7u) & 0xFFu) << ((k >> 2) == 2 ? 2 : 3)));
             }
         } else if (flip) digits_dev<true>(y0, y1, own0, rot0, a.lut);
         else digits_dev<false>(y0, y1, own0, rot0, a.lut);
@@ -294,8 +297,8 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, c
 #pragma unroll
             for (int k = 0; k < 16; k++) {
                 const uint32_t t = ((uint32_t)lds32<8192>(own0 + 256 * k) & dbg) + (uint32_t)(T + 3 * k);
-                x0[k] = k < 4 ? (int32_t)(t & 0xFFu) - 128 : (int32_t)(a.lut + ((t & 0xFFu) << 3));
-                x1[k] = k < 4 ? (int32_t)((t + 7u) & 0xFFu) - 128 : (int32_t)(a.lut + (((t + 7u) & 0xFFu) << 3));
+                x0[k] = k < 4 ? (int32_t)(t & 0xFFu) - 128 : (int32_t)(a.lut + ((t & 0xFFu) << ((k >> 2) == 2 ? 2 : 3)));
+                x1[k] = k < 4 ? (int32_t)((t + 7u) & 0xFFu) - 128 : (int32_t)(a.lut + (((t + 7u) & 0xFFu) << ((k >> 2) == 2 ? 2 : 3)));
             }
         } else if (flip) digits_dev<true>(x0, x1, own0 + 8192, rot0 + 8192, a.lut);
         else digits_dev<false>(x0, x1, own0 + 8192, rot0 + 8192, a.lut);
@@ -378,7 +381,7 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P,
     a.tT = smem_u32(&tab->pr[q].perT[0][T]);
     a.tLo = smem_u32(&tab->pr[q].i2[0][T & 15]);
     a.tHi = smem_u32(&tab->pr[q].f2[T >> 4][0]);
-    a.lut = smem_u32(&tab->pr[q].lut[0][0]);
+    a.lut = smem_u32(&tab->pr[q].lut0[0]);
 
     // ---- pre-add + modulus switch (gatebootstrapping_gpu.cuh:316-345) ----
     BrItem it;

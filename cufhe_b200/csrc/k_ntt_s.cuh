@@ -40,7 +40,7 @@ __device__ __forceinline__ SAddr team_addr(uint32_t* smem, int nprimes, int team
     a.tT = smem_u32(&tab->perT[0][T]);
     a.tLo = smem_u32(&tab->i2[0][T & 15]);
     a.tHi = smem_u32(&tab->f2[T >> 4][0]);
-    a.lut = smem_u32(&tab->lut[0][0]);
+    a.lut = smem_u32(&tab->lut0[0]);
     return a;
 }
 // Compact shared-memory images for the one-direction kernels (the full 30 KB per prime would cap them at one

@@ -39,6 +39,7 @@
 // with four LDS.128; writers scatter vectors or words into other threads' chunks.  All accesses are
 // bank-conflict free (checked in tests/emul/emul_ntt16s.cpp).
 #pragma once
+#include <cstddef>
 #include "ntt_core.cuh"
 
 namespace b2 {
@@ -155,11 +156,17 @@ struct PrimeSTables {           // one prime; the shared-memory image a team wor
     V4 perT[kVecPerT][64];      // [vec][T]: forward strides 8..1 (layout C) | inverse t = 256 (slots 0..3), 512 (4..11) | n^-1 psi^-(T + 64 k)
     V4 i2[8][16];               // [vec][lo]      inverse t = 16..128     (layout D)
     V4 f2[4][8];                // [hi][vec]      forward strides 128..16 (layout D); half-warp broadcast
-    // gadget-digit tables, 8-byte entries indexed by the RAW digit byte d (standing for d - 128), centred
-    // residues:  0: { W1 (d-128), - };  1: { W2a (d-128), W2b (d-128) };  2: { W2a W1 (d-128), W2b W1 (d-128) }
-    I2 lut[3][256];
+    // gadget-digit tables indexed by the RAW digit byte d (standing for d - 128), centred residues:
+    //   lut0 (4-byte entries: a warp's random look-ups spread over all 32 banks, measured 0.9 % of a blind
+    //         rotation against 8-byte entries with an unused half, profiles/r2_ablate_v5_rejected_experiments.log):
+    //         W1 (d-128)
+    //   lut12[0]: { W2a (d-128), W2b (d-128) };  lut12[1]: { W2a W1 (d-128), W2b W1 (d-128) }
+    int32_t lut0[256];
+    I2 lut12[2][256];
 };
-static_assert(sizeof(PrimeSTables) == 22528 + 2048 + 512 + 6144, "table layout");
+constexpr int kLut1Off = 1024, kLut2Off = 1024 + 2048;    // byte offsets of lut12[0], lut12[1] from lut0
+static_assert(sizeof(PrimeSTables) == 22528 + 2048 + 512 + 1024 + 4096, "table layout");
+static_assert(offsetof(PrimeSTables, lut12) - offsetof(PrimeSTables, lut0) == kLut1Off, "table layout");
 struct TeamSTables { PrimeSTables pr[2]; };          // the bootstrapping path: two primes
 struct TeamSTables3 { PrimeSTables pr[3]; };         // the exact polynomial product: three
 constexpr int kTeamSTableWords = sizeof(TeamSTables) / 4;
@@ -229,9 +236,9 @@ inline void make_prime_tables16s(PrimeSTables& L, TeamSConst& C, int q)
     C.r2[q] = h_centre((uint32_t)((((unsigned __int128)1) << 64) % p), p);
     for (int d = 0; d < 256; d++) {
         const uint32_t v = d >= 128 ? (uint32_t)(d - 128) : p - (uint32_t)(128 - d);     // d - 128 mod p
-        L.lut[0][d] = I2{h_centre(h_mulmod(w1, v, p), p), 0};
-        L.lut[1][d] = I2{h_centre(h_mulmod(w2a, v, p), p), h_centre(h_mulmod(w2b, v, p), p)};
-        L.lut[2][d] = I2{h_centre(h_mulmod(h_mulmod(w2a, w1, p), v, p), p), h_centre(h_mulmod(h_mulmod(w2b, w1, p), v, p), p)};
+        L.lut0[d] = h_centre(h_mulmod(w1, v, p), p);
+        L.lut12[0][d] = I2{h_centre(h_mulmod(w2a, v, p), p), h_centre(h_mulmod(w2b, v, p), p)};
+        L.lut12[1][d] = I2{h_centre(h_mulmod(h_mulmod(w2a, w1, p), v, p), p), h_centre(h_mulmod(h_mulmod(w2b, w1, p), v, p), p)};
     }
 }
 inline void make_tables16s(TeamSTables3& L, TeamSConst& C)

@@ -112,8 +112,8 @@ static void fwd_digits(Team x, int q)   // raw digits in [0, 256), layout A
 {
     for (int t = 0; t < 64; t++) {
         for (int k = 0; k < 4; k++) x[t][k] -= 128;          // slot k holds the signed digit, the others the raw byte (table handle)
-        spass_digits(x[t], [&](int32_t d) { return L.pr[q].lut[0][d].x; }, [&](int32_t d) { return L.pr[q].lut[1][d]; },
-                     [&](int32_t d) { return L.pr[q].lut[2][d]; });
+        spass_digits(x[t], [&](int32_t d) { return L.pr[q].lut0[d]; }, [&](int32_t d) { return L.pr[q].lut12[0][d]; },
+                     [&](int32_t d) { return L.pr[q].lut12[1][d]; });
     }
     fwd_tail(x, q);
 }
