@@ -37,7 +37,8 @@ int g_ks_lat_max_per_sm = 32;    // k_keyswitch_lat up to this many gates per SM
 int g_br_cluster_max = 70;       // k_blind_rotate_cl4s up to this many gates: 33 four-CTA clusters run one CTA per SM (1.43 ms), up to 70 two per SM (1.91 ms); beyond that k_blind_rotate_s with one gate per CTA (3.3 ms up to 148 gates) wins
 int g_latency_mode = 1;          // small calls: 1 = latency kernels (one gate over several SMs), 0 = always the throughput kernel (b2fhe_set_latency_mode)
 bool g_br_tail_split = true;     // last partial wave of k_blind_rotate_s as its own launch (b2fhe_set_br_variant(-1) / (-2) = off / on)
-int g_br_variant = 0;            // 0 = by batch size, 5 = k_blind_rotate_cl4s, 40 = k_blind_rotate_s, 48 = its key-row-0 timing experiment
+bool g_ntt_prefetch = true;     // stand-alone NTT / INTT: inputs prefetched by bulk copies (b2fhe_set_br_variant(-3) / (-4) = off / on)
+int g_br_variant = 0;            // 0 = by batch size, 5 = k_blind_rotate_cl4s, 40 = k_blind_rotate_s, 6 / 41 = their schedule-fuzzing builds, 48 = the key-row-0 timing experiment
 std::atomic<uint64_t> g_launches{0};
 thread_local std::string t_err;
 
@@ -95,7 +96,10 @@ int setup_device(int device)
     if (int r = set_brs_attr<3>()) return r;
     if (int r = set_brs_attr<4>()) return r;
     CK(cudaFuncSetAttribute(k_blind_rotate_s<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(4)));
-    CK(cudaFuncSetAttribute(k_blind_rotate_cl4s, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
+    CK(cudaFuncSetAttribute(k_blind_rotate_cl4s<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
+    CK(cudaFuncSetAttribute(k_blind_rotate_cl4s<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCl4SmemBytes));
+    CK(cudaFuncSetAttribute(k_blind_rotate_s<1, false, ABL_JIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(1)));
+    CK(cudaFuncSetAttribute(k_blind_rotate_s<4, false, ABL_JIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, brs_smem_bytes(4)));
     CK(cudaFuncSetAttribute(k_cmux_s<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(1)));
     CK(cudaFuncSetAttribute(k_cmux_s<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, cmux_smem_bytes(4)));
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
@@ -105,7 +109,9 @@ int setup_device(int device)
     CK(cudaFuncSetAttribute(k_keyswitch_step<32, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * kN * 2));
     CK(cudaFuncSetAttribute(k_ntt_fwd_s<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_fwd_smem_bytes<kNttTeams>()));
     CK(cudaFuncSetAttribute(k_ntt_fwd_s<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_fwd_smem_bytes<kNttTeams>()));
-    CK(cudaFuncSetAttribute(k_ntt_inv_s, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_inv_smem_bytes<kNttTeams>()));
+    CK(cudaFuncSetAttribute(k_ntt_fwd_s<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_fwd_pf_smem_bytes<kNttTeams>()));
+    CK(cudaFuncSetAttribute(k_ntt_inv_s<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_inv_smem_bytes<kNttTeams>()));
+    CK(cudaFuncSetAttribute(k_ntt_inv_s<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_inv_pf_smem_bytes<kNttTeams>()));
     CK(cudaFuncSetAttribute(k_polymul_s<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, 4>()));
     CK(cudaFuncSetAttribute(k_polymul_s<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<3, 6>()));
     return noalloc_setup(device);
@@ -197,7 +203,8 @@ int b2fhe_set_ks_variant(int variant)
 int b2fhe_set_br_variant(int variant)
 {
     if (variant == -1 || variant == -2) { g_br_tail_split = variant == -2; return 0; }
-    REQUIRE(variant == 0 || variant == 5 || variant == 40 || variant == 48, B2FHE_E_BAD_ARGUMENT);
+    if (variant == -3 || variant == -4) { g_ntt_prefetch = variant == -4; return 0; }
+    REQUIRE(variant == 0 || variant == 5 || variant == 6 || variant == 40 || variant == 41 || variant == 48, B2FHE_E_BAD_ARGUMENT);
     g_br_variant = variant;
     return 0;
 }

@@ -23,7 +23,19 @@ int launch_br(const DevCtx& c, BrParams P, cudaStream_t st)
     // up to 70 gates: one gate per cluster of 4 CTAs x 128 threads (70 clusters are resident at once, two CTAs
     // per SM); hand-overs by st.async + mbarrier
     if (g_br_variant == 5 || (small_ok && P.count <= g_br_cluster_max)) {
-        k_blind_rotate_cl4s<<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, reinterpret_cast<const PrimeSTables*>(c.tabs));
+        k_blind_rotate_cl4s<false><<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, reinterpret_cast<const PrimeSTables*>(c.tabs));
+        LAUNCHED();
+        return 0;
+    }
+    // schedule fuzzing builds (random sleeps around every synchronisation; same bits): 6 = cluster kernel, 41 = throughput kernel
+    if (g_br_variant == 6) {
+        k_blind_rotate_cl4s<true><<<P.count * kCl4Ctas, kCl4Threads, kCl4SmemBytes, st>>>(P, reinterpret_cast<const PrimeSTables*>(c.tabs));
+        LAUNCHED();
+        return 0;
+    }
+    if (g_br_variant == 41) {
+        if (g == 1) k_blind_rotate_s<1, false, ABL_JIT><<<P.count - P.first, 128, brs_smem_bytes(1), st>>>(P, reinterpret_cast<const TeamSTables*>(c.tabs));
+        else k_blind_rotate_s<4, false, ABL_JIT><<<(P.count - P.first + 3) / 4, 512, brs_smem_bytes(4), st>>>(P, reinterpret_cast<const TeamSTables*>(c.tabs));
         LAUNCHED();
         return 0;
     }
@@ -493,8 +505,13 @@ int b2fhe_ntt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const 
     if (int r = get_ctx(device, c)) return r;
     if (count == 0) return 0;
     REQUIRE(out && in && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    k_ntt_fwd_s<0><<<ntt_grid(*c, count, kNttTeams / 2, 2), kNttThreadsS, ntt_fwd_smem_bytes<kNttTeams>(), (cudaStream_t)stream>>>(
-        in, out, (int)count, c->tabs->pr);
+    // inputs prefetched by bulk copies (16-byte aligned sources only; any other 4-byte aligned pointer takes the plain loads)
+    if ((reinterpret_cast<uintptr_t>(in) & 15) == 0 && g_ntt_prefetch)
+        k_ntt_fwd_s<0, true><<<ntt_grid(*c, count, kNttTeams / 2, 2), kNttThreadsS, ntt_fwd_pf_smem_bytes<kNttTeams>(), (cudaStream_t)stream>>>(
+            in, out, (int)count, c->tabs->pr);
+    else
+        k_ntt_fwd_s<0><<<ntt_grid(*c, count, kNttTeams / 2, 2), kNttThreadsS, ntt_fwd_smem_bytes<kNttTeams>(), (cudaStream_t)stream>>>(
+            in, out, (int)count, c->tabs->pr);
     LAUNCHED();
     return 0;
 }
@@ -504,8 +521,12 @@ int b2fhe_intt1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, const
     if (int r = get_ctx(device, c)) return r;
     if (count == 0) return 0;
     REQUIRE(out && in && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    k_ntt_inv_s<<<ntt_grid(*c, count, kNttTeams / 2, 2), kNttThreadsS, ntt_inv_smem_bytes<kNttTeams>(), (cudaStream_t)stream>>>(
-        in, out, (int)count, c->tabs->pr);
+    if (g_ntt_prefetch)      // `in` is read as 128-bit vectors either way
+        k_ntt_inv_s<true><<<ntt_grid(*c, count, kNttTeams / 2, 2), kNttThreadsS, ntt_inv_pf_smem_bytes<kNttTeams>(), (cudaStream_t)stream>>>(
+            in, out, (int)count, c->tabs->pr);
+    else
+        k_ntt_inv_s<false><<<ntt_grid(*c, count, kNttTeams / 2, 2), kNttThreadsS, ntt_inv_smem_bytes<kNttTeams>(), (cudaStream_t)stream>>>(
+            in, out, (int)count, c->tabs->pr);
     LAUNCHED();
     return 0;
 }

@@ -34,28 +34,6 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, int rank)
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
     return r;
 }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-// default (.acquire.cta) wait, as for TMA-written shared memory: the st.async data is in shared memory
-// when the transaction count completes; an .acquire.cluster wait would add an L1 invalidate (CCTL.IVALL)
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "MBAR_WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra MBAR_DONE_%=;\n"
-        "bra MBAR_WAIT_%=;\n"
-        "MBAR_DONE_%=:\n"
-        "}\n" ::"r"(bar), "r"(parity) : "memory");
-}
 // 128-bit store into another CTA's shared memory that signals `bytes written` on that CTA's mbarrier
 __device__ __forceinline__ void st_async_v4(uint32_t remote_addr, int32_t a, int32_t b, int32_t c, int32_t d, uint32_t remote_bar)
 {
@@ -72,6 +50,9 @@ constexpr int kCl4SmemWords = kCl4TabWords + 4 * kXsWords + kN + 2 * kN + 2 * kN
 // 74 KB: three CTAs (of different gates, or of one gate when few are in flight) fit one SM
 constexpr int kCl4SmemBytes = kCl4SmemWords * 4;
 
+// JIT: schedule fuzzing (b2fhe_set_br_variant(6)): random sleeps around every hand-over, barrier and
+// mbarrier wait; results must not change
+template <bool JIT = false>
 __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 2)
     k_blind_rotate_cl4s(const BrParams P, const PrimeSTables* __restrict__ g_tab)
 {
@@ -128,7 +109,7 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
     const int32_t cw = c_s.crt.w, cws = c_s.crt.ws;
     if (threadIdx.x == 0) {
         for (int b = 0; b < 4; b++) mbar_init(smem_u32(mbar + b), 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_fence_init();
     }
     cluster.sync();                                            // every CTA's shared memory (and mbarriers) are live
 
@@ -148,6 +129,7 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
             mbar_arrive_expect_tx(smem_u32(mbar + 2 + par), kN * 4);
         }
         // ---- A: digit polynomial, forward transform, pair products ------------------------------
+        if (JIT) jitter_sleep(rank * 4 + (threadIdx.x >> 5));
         int32_t x[16], y[16];
 #pragma unroll
         for (int k = 0; k < 16; k++) {
@@ -162,7 +144,9 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
         sts128<1024>(tx_own, x[4], x[5], x[6], x[7]);
         sts128<2048>(tx_own, x[8], x[9], x[10], x[11]);
         sts128<3072>(tx_own, x[12], x[13], x[14], x[15]);
+        if (JIT) jitter_sleep(0x11u + rank * 4 + (threadIdx.x >> 5));
         __syncthreads();
+        if (JIT) jitter_sleep(0x22u + rank * 4 + (threadIdx.x >> 5));
         {
             const V4 o0 = lds128<0>(tx_oth), o1 = lds128<1024>(tx_oth), o2 = lds128<2048>(tx_oth), o3 = lds128<3072>(tx_oth);
             const int32_t ox[16] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w, o2.x, o2.y, o2.z, o2.w, o3.x, o3.y, o3.z, o3.w};
@@ -180,13 +164,15 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
 #pragma unroll
             for (int v = 0; v < 4; v++) { kb[v] = __ldg(bk_own + nxt + v * 64); kb[4 + v] = __ldg(bk_oth + nxt + v * 64); }
         }
+        if (JIT) jitter_sleep(0x33u + rank * 4 + (threadIdx.x >> 5));
         if (d != j) {                                          // output 1-j is finished by CTA (q, 1-j)
 #pragma unroll
             for (int v = 0; v < 4; v++)
                 st_async_v4(ra_part + (par * kN + v * 256) * 4, y[4 * v], y[4 * v + 1], y[4 * v + 2], y[4 * v + 3], rb_part + 8 * par);
         } else {
             // ---- B: team j adds the other accumulator polynomial's contribution, inverse transform ----
-            mbar_wait_cluster(smem_u32(mbar + par), phase);
+            mbar_wait(smem_u32(mbar + par), phase);
+            if (JIT) jitter_sleep(0x44u + rank * 4 + (threadIdx.x >> 5));
             const uint32_t rc = smem_u32(recv + par * kN + 4 * T);
             const V4 r0 = lds128<0>(rc), r1 = lds128<1024>(rc), r2 = lds128<2048>(rc), r3 = lds128<3072>(rc);
             const int32_t rv[16] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
@@ -202,8 +188,10 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
                 if (v == 3) sts128<3072>(zl, y[12], y[13], y[14], y[15]);
             }
         }
+        if (JIT) jitter_sleep(0x55u + rank * 4 + (threadIdx.x >> 5));
         __syncthreads();                                       // zloc
-        mbar_wait_cluster(smem_u32(mbar + 2 + par), phase);
+        mbar_wait(smem_u32(mbar + 2 + par), phase);
+        if (JIT) jitter_sleep(0x66u + rank * 4 + (threadIdx.x >> 5));
         // ---- C: CRT of output j, local accumulator update (two 128-bit slots per thread) ----------
 #pragma unroll
         for (int h = 0; h < 2; h++) {
@@ -215,6 +203,7 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
 #pragma unroll
             for (int e = 0; e < 4; e++) ap[64 * e] += q ? scrt_lift32(o[e], m[e], cw, cws) : scrt_lift32(m[e], o[e], cw, cws);
         }
+        if (JIT) jitter_sleep(0x77u + rank * 4 + (threadIdx.x >> 5));
         __syncthreads();                                       // rotated reads of the next step cross threads
     }
 

@@ -44,7 +44,11 @@ enum : int { ABL_LUT = 1,      // table look-ups at conflict-free (lane) indices
              ABL_KEY = 4,      // no key loads (register constants)
              ABL_BAR = 8,      // no named barriers / __syncwarp
              ABL_XCH = 16,     // no shared-memory exchanges
-             ABL_TWD = 64 };   // twiddles from registers (no table loads)
+             ABL_TWD = 64,     // twiddles from registers (no table loads)
+             // schedule fuzzing (RIGHT results, b2fhe_set_br_variant(41)): every warp sleeps a random 0..1 us before and
+             // after every barrier / __syncwarp, so a missing or misplaced synchronisation shows up as wrong bits
+             // (tests/test_gpu_parity.py::test_schedule_jitter_is_bit_exact; compute-sanitizer is closed on this pool)
+             ABL_JIT = 32 };
 
 // ---- shared memory through explicit 32-bit window addresses ------------------------------------
 template <int OFF> __device__ __forceinline__ int32_t lds32(uint32_t a)
@@ -107,8 +111,35 @@ __device__ __forceinline__ void stage_tables_s(uint32_t* s_tab, const TeamSTable
     for (int i = threadIdx.x; i < kTeamSTableWords / 4; i += blockDim.x) dst[i] = __ldg(src + i);
 }
 
-template <int ABL> __device__ __forceinline__ void tbar_sync(int id, int n) { if (!(ABL & ABL_BAR)) named_bar_sync(id, n); }
-template <int ABL> __device__ __forceinline__ void warp_sync() { if (!(ABL & ABL_BAR)) __syncwarp(); }
+// warp-uniform random sleep of 0..1023 ns (clock-seeded: different in every launch).  It moves WARPS against each
+// other: tools/fuzz_mutants.cu shows that dropping any of the six cross-warp barriers of a step is caught (all gates
+// wrong under fuzzing; the 'lead' barrier alone corrupts only ~5 of 1184 gates without it).  The four __syncwarp()
+// of the half-warp exchanges order LANES of one warp; a converged warp issues its shared-memory instructions in
+// program order, so no timing perturbation can make their absence visible (per-lane sleeps were tried: a single
+// NANOSLEEP does not split a warp) -- they are kept because the PTX memory model requires them.
+__device__ __forceinline__ void jitter_sleep(uint32_t salt)
+{
+    uint32_t h = ((uint32_t)clock() ^ salt) * 0x9E3779B9u;
+    h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13;
+    h = __shfl_sync(0xFFFFFFFFu, h, 0);
+    __nanosleep(h & 1023u);
+}
+// SITE numbers the ten synchronisation points of a step; a MUTANT build (tools/fuzz_mutants.cu) drops one of them
+// to show that the fuzzing notices: ABL = ABL_JIT | site << kMutShift
+constexpr int kMutShift = 8;
+template <int ABL, int SITE> __host__ __device__ constexpr bool sync_kept() { return !(ABL & ABL_BAR) && ((ABL >> kMutShift) & 15) != SITE; }
+template <int ABL, int SITE = 0> __device__ __forceinline__ void tbar_sync(int id, int n)
+{
+    if (ABL & ABL_JIT) jitter_sleep(threadIdx.x >> 5);
+    if (sync_kept<ABL, SITE>()) named_bar_sync(id, n);
+    if (ABL & ABL_JIT) jitter_sleep(0x55u + (threadIdx.x >> 5));
+}
+template <int ABL, int SITE = 0> __device__ __forceinline__ void warp_sync()
+{
+    if (ABL & ABL_JIT) jitter_sleep(0xAAu + (threadIdx.x >> 5));
+    if (sync_kept<ABL, SITE>()) __syncwarp();
+    if (ABL & ABL_JIT) jitter_sleep(0x33u + (threadIdx.x >> 5));
+}
 
 // owner's four LDS.128 of its chunk in array ARR: vector v -> x[4 v .. 4 v + 3]
 template <int ARR> __device__ __forceinline__ void ld_own(int32_t (&x)[16], const uint32_t own)
@@ -187,14 +218,14 @@ __device__ __forceinline__ void sfwd2_dev(int32_t (&x0)[16], int32_t (&x1)[16], 
         spass_digits(x0, l0, l1, l2);
         spass_digits(x1, l0, l1, l2);
     }
-    if (lead) tbar_sync<ABL>(tbar, 64);          // owners have read their chunks (previous D->C)
+    if (lead) tbar_sync<ABL, 1>(tbar, 64);          // owners have read their chunks (previous D->C)
     if (!(ABL & ABL_XCH)) { st_vec_contig<0>(x0, a.vw); st_vec_contig<1>(x1, a.vw); }
-    tbar_sync<ABL>(tbar, 64);
+    tbar_sync<ABL, 2>(tbar, 64);
     if (!(ABL & ABL_XCH)) { ld_own_strided<0>(x0, a.own); ld_own_strided<1>(x1, a.own); }
     spass_fwd<2>(x0, x1, TwLd<16, 0, (ABL & ABL_TWD) != 0>{a.tHi, p, T}, p);
-    warp_sync<ABL>();                            // group mates have read their chunks
+    warp_sync<ABL, 3>();                            // group mates have read their chunks
     if (!(ABL & ABL_XCH)) { st_words<0>(x0, a.sw); st_words<1>(x1, a.sw); }
-    warp_sync<ABL>();
+    warp_sync<ABL, 4>();
     if (!(ABL & ABL_XCH)) { ld_own<0>(x0, a.own); ld_own<1>(x1, a.own); }
     spass_fwd<2>(x0, x1, TwLd<1024, 1024 * kVecF3, (ABL & ABL_TWD) != 0>{a.tT, p, T}, p);
 }
@@ -208,14 +239,14 @@ __device__ __forceinline__ void sinv2_dev(int32_t (&x0)[16], int32_t (&x1)[16], 
         const Tws* c1 = c_s.iv1[q];
         spass_inv1<2>(x0, x1, [&](int i) { return c1[i]; }, p);
     }
-    warp_sync<ABL>();                            // group mates' last loads of their chunks (forward D->C)
+    warp_sync<ABL, 5>();                            // group mates' last loads of their chunks (forward D->C)
     if (!(ABL & ABL_XCH)) { st_words<0>(x0, a.sw); st_words<1>(x1, a.sw); }
-    warp_sync<ABL>();
+    warp_sync<ABL, 6>();
     if (!(ABL & ABL_XCH)) { ld_own<0>(x0, a.own); ld_own<1>(x1, a.own); }
     spass_inv2<2>(x0, x1, TwLd<256, 0, (ABL & ABL_TWD) != 0>{a.tLo, p, T}, p);
-    tbar_sync<ABL>(tbar, 64);                    // every owner has read its chunk
+    tbar_sync<ABL, 7>(tbar, 64);                    // every owner has read its chunk
     if (!(ABL & ABL_XCH)) { st_vec_strided<0>(x0, a.vw); st_vec_strided<1>(x1, a.vw); }
-    tbar_sync<ABL>(tbar, 64);
+    tbar_sync<ABL, 8>(tbar, 64);
     if (!(ABL & ABL_XCH)) { ld_own<0>(x0, a.own); ld_own<1>(x1, a.own); }
     spass_inv3<2>(x0, x1, TwLd<1024, 1024 * kVecI3, (ABL & ABL_TWD) != 0>{a.tT, p, T},
                   TwLd<1024, 1024 * kVecSc, (ABL & ABL_TWD) != 0>{a.tT, p, T}, p);
@@ -343,13 +374,13 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, c
         sts128<16>(a.own, sb[4], sb[5], sb[6], sb[7]);
         sts128<32>(a.own, sb[8], sb[9], sb[10], sb[11]);
         sts128<48>(a.own, sb[12], sb[13], sb[14], sb[15]);
-        tbar_sync<ABL>(gbar, 128);
+        tbar_sync<ABL, 9>(gbar, 128);
         int32_t t[16];
         ld_own<0>(t, a.oth);                             // other team's residue of out q
         const int32_t cw = c_s.crt.w, cws = c_s.crt.ws;
         if (q) acc_update(mine, t, sa, cw, cws);
         else acc_update(mine, sa, t, cw, cws);
-        tbar_sync<ABL>(gbar, 128);
+        tbar_sync<ABL, 10>(gbar, 128);
     }
 }
 

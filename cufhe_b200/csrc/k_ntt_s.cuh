@@ -86,6 +86,10 @@ __device__ __forceinline__ SAddr team_addr_compact(uint32_t* smem, int img_bytes
 }
 template <int TEAMS> __host__ __device__ constexpr int ntt_fwd_smem_bytes() { return 2 * kFwdImgBytes + TEAMS * kXsBytes; }
 template <int TEAMS> __host__ __device__ constexpr int ntt_inv_smem_bytes() { return 2 * kInvImgBytes + TEAMS * kXsBytes; }
+// with input prefetch (PF): one 4 KB staging buffer + one mbarrier per polynomial slot (forward: the two
+// prime teams of a polynomial share the input) / per team (inverse: each team reads its own prime's residues)
+template <int TEAMS> __host__ __device__ constexpr int ntt_fwd_pf_smem_bytes() { return ntt_fwd_smem_bytes<TEAMS>() + (TEAMS / 2) * (kN * 4 + 8); }
+template <int TEAMS> __host__ __device__ constexpr int ntt_inv_pf_smem_bytes() { return ntt_inv_smem_bytes<TEAMS>() + TEAMS * (kN * 4 + 8); }
 
 __device__ __forceinline__ int32_t prime_of(int q) { return (int32_t)(q == 0 ? Prime<0>::p : q == 1 ? Prime<1>::p : Prime<2>::p); }
 __device__ __forceinline__ uint32_t pinv_of(int q) { return q == 0 ? Prime<0>::pinv : q == 1 ? Prime<1>::pinv : Prime<2>::pinv; }
@@ -137,29 +141,56 @@ __device__ __forceinline__ int32_t lazy_u32(uint32_t v, int32_t p) { return (int
 __device__ __forceinline__ int32_t lazy_s32(int32_t v, int32_t p) { return (int32_t)((uint32_t)v - (uint32_t)(v >> 27) * (uint32_t)p); }
 __device__ __forceinline__ uint32_t canon_s(int32_t r, int32_t p) { return (uint32_t)(r < 0 ? r + p : r); }
 
+// layout A from a staged natural-order polynomial: x[k] = lazy(buf[T + 64 k]); base = &buf[T]
+template <int K = 0> __device__ __forceinline__ void ld_stage_a(int32_t (&x)[16], const uint32_t base, const int32_t p)
+{
+    if constexpr (K < 16) {
+        x[K] = lazy_u32((uint32_t)lds32<256 * K>(base), p);
+        ld_stage_a<K + 1>(x, base, p);
+    }
+}
+
 // MODE 0: polynomials -> canonical residues, out[poly][2][1024]
 // MODE 1: bootstrapping key / TRGSW rows -> Montgomery-form residues in [0, p), out index
 //         ((pl>>1)*2 + q)*2 + (pl&1), i.e. [i][row][prime][out poly][1024]
 // both in bk16_slot order: thread T writes vector v = positions 16 T + 4 v .. + 3 at word (64 v + T) 4
-template <int MODE>
+// PF: the NEXT polynomial of a slot is fetched by one bulk copy (TMA, cp.async.bulk) into a 4 KB staging buffer
+// while the current one is transformed -- the loads of a persistent team are otherwise exposed once per
+// polynomial (0.235 -> see DESIGN.md 4.4).  `in` must then be 16-byte aligned.
+template <int MODE, bool PF = false>
 __global__ void __launch_bounds__(kNttThreadsS) k_ntt_fwd_s(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int npoly,
                                                             const PrimeSTables* __restrict__ g_tab)
 {
     extern __shared__ __align__(16) uint32_t smem[];
     stage_fwd_image(smem, g_tab);
-    __syncthreads();
     const int team = threadIdx.x >> 6, T = threadIdx.x & 63;
-    const int q = team & 1;
+    const int q = team & 1, slot = team >> 1;
+    const uint32_t stg = smem_u32(smem) + ntt_fwd_smem_bytes<kNttTeams>() + slot * (kN * 4);
+    const uint32_t mb = smem_u32(smem) + ntt_fwd_smem_bytes<kNttTeams>() + (kNttTeams / 2) * (kN * 4) + slot * 8;
+    const bool producer = PF && q == 0 && T == 0;
+    if (producer) { mbar_init(mb, 1); mbar_fence_init(); }
+    __syncthreads();
     const SAddr a = team_addr_compact(smem, kFwdImgBytes, team, q, T, false);
     const int32_t p = prime_of(q);
     const uint32_t pinv = pinv_of(q);
-    const int tbar = 1 + team;
+    const int tbar = 1 + team, pbar = 1 + kNttTeams + slot;
     bool lead = false;
-    for (int pl = blockIdx.x * (kNttTeams / 2) + (team >> 1); pl < npoly; pl += gridDim.x * (kNttTeams / 2)) {
+    const int first = blockIdx.x * (kNttTeams / 2) + slot, stride = gridDim.x * (kNttTeams / 2);
+    if (producer && first < npoly) { mbar_arrive_expect_tx(mb, kN * 4); bulk_g2s(stg, in + (size_t)first * kN, kN * 4, mb); }
+    uint32_t phase = 0;
+    for (int pl = first; pl < npoly; pl += stride) {
         int32_t x[16], dummy[16];
-        const uint32_t* src = in + (size_t)pl * kN + T;
+        if (PF) {
+            mbar_wait(mb, phase);
+            phase ^= 1u;
+            ld_stage_a(x, stg + 4 * T, p);
+            named_bar_sync(pbar, 128);              // both prime teams have read the buffer
+            if (producer && pl + stride < npoly) { mbar_arrive_expect_tx(mb, kN * 4); bulk_g2s(stg, in + (size_t)(pl + stride) * kN, kN * 4, mb); }
+        } else {
+            const uint32_t* src = in + (size_t)pl * kN + T;
 #pragma unroll
-        for (int k = 0; k < 16; k++) x[k] = lazy_u32(__ldg(src + 64 * k), p);
+            for (int k = 0; k < 16; k++) x[k] = lazy_u32(__ldg(src + 64 * k), p);
+        }
         sfwd_general_dev<1, kVecF3>(x, dummy, a, q, p, tbar, lead, T);
         lead = true;
         uint4* dst = reinterpret_cast<uint4*>(MODE == 1 ? out + ((size_t)((pl >> 1) * 2 + q) * 2 + (pl & 1)) * kN
@@ -180,25 +211,46 @@ __global__ void __launch_bounds__(kNttThreadsS) k_ntt_fwd_s(const uint32_t* __re
 
 // inverse of MODE 0: in[poly][2][1024] residues -> out[poly][1024] = centred CRT value mod 2^32.
 // The two teams of a polynomial (one per prime) swap halves and each finishes 512 coefficients.
+template <bool PF = false>
 __global__ void __launch_bounds__(kNttThreadsS) k_ntt_inv_s(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int npoly,
                                                             const PrimeSTables* __restrict__ g_tab)
 {
     extern __shared__ __align__(16) uint32_t smem[];
     stage_inv_image(smem, g_tab);
-    __syncthreads();
     const int team = threadIdx.x >> 6, T = threadIdx.x & 63;
     const int q = team & 1;
+    const uint32_t stg = smem_u32(smem) + ntt_inv_smem_bytes<kNttTeams>() + team * (kN * 4);
+    const uint32_t mb = smem_u32(smem) + ntt_inv_smem_bytes<kNttTeams>() + kNttTeams * (kN * 4) + team * 8;
+    const bool producer = PF && T == 0;
+    if (producer) { mbar_init(mb, 1); mbar_fence_init(); }
+    __syncthreads();
     SAddr a = team_addr_compact(smem, kInvImgBytes, team, q, T, true);
     a.oth = team_addr_compact(smem, kInvImgBytes, team ^ 1, q ^ 1, T, true).own;
     const int32_t p = prime_of(q);
     const int tbar = 1 + team, pbar = 1 + kNttTeams + (team >> 1);
-    for (int pl = blockIdx.x * (kNttTeams / 2) + (team >> 1); pl < npoly; pl += gridDim.x * (kNttTeams / 2)) {   // pair-uniform
+    const int first = blockIdx.x * (kNttTeams / 2) + (team >> 1), stride = gridDim.x * (kNttTeams / 2);
+    if (producer && first < npoly) { mbar_arrive_expect_tx(mb, kN * 4); bulk_g2s(stg, in + ((size_t)first * 2 + q) * kN, kN * 4, mb); }
+    uint32_t phase = 0;
+    for (int pl = first; pl < npoly; pl += stride) {   // pair-uniform
         int32_t x[16];
-        const uint4* src = reinterpret_cast<const uint4*>(in + ((size_t)pl * 2 + q) * kN) + T;
+        if (PF) {
+            mbar_wait(mb, phase);
+            phase ^= 1u;
+            const V4 t0 = lds128<0>(stg + 16 * T), t1 = lds128<1024>(stg + 16 * T), t2 = lds128<2048>(stg + 16 * T), t3 = lds128<3072>(stg + 16 * T);
+            x[0] = t0.x; x[1] = t0.y; x[2] = t0.z; x[3] = t0.w; x[4] = t1.x; x[5] = t1.y; x[6] = t1.z; x[7] = t1.w;
+            x[8] = t2.x; x[9] = t2.y; x[10] = t2.z; x[11] = t2.w; x[12] = t3.x; x[13] = t3.y; x[14] = t3.z; x[15] = t3.w;
+            named_bar_sync(tbar, 64);                   // the team has read the buffer
+            if (producer && pl + stride < npoly) {
+                mbar_arrive_expect_tx(mb, kN * 4);
+                bulk_g2s(stg, in + ((size_t)(pl + stride) * 2 + q) * kN, kN * 4, mb);
+            }
+        } else {
+            const uint4* src = reinterpret_cast<const uint4*>(in + ((size_t)pl * 2 + q) * kN) + T;
 #pragma unroll
-        for (int v = 0; v < 4; v++) {
-            const uint4 t = __ldg(src + 64 * v);
-            x[4 * v] = (int32_t)t.x; x[4 * v + 1] = (int32_t)t.y; x[4 * v + 2] = (int32_t)t.z; x[4 * v + 3] = (int32_t)t.w;
+            for (int v = 0; v < 4; v++) {
+                const uint4 t = __ldg(src + 64 * v);
+                x[4 * v] = (int32_t)t.x; x[4 * v + 1] = (int32_t)t.y; x[4 * v + 2] = (int32_t)t.z; x[4 * v + 3] = (int32_t)t.w;
+            }
         }
         named_bar_sync(pbar, 128);                      // the partner has read my chunk of the previous polynomial
         sinv1_dev<kVecI3>(x, a, q, p, tbar, T);

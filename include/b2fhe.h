@@ -215,8 +215,10 @@ int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
  * else k_blind_rotate_s), 5 = k_blind_rotate_cl4s (one gate per cluster of 4 CTAs x 128 threads, hand-overs
  * by st.async + mbarrier), 40 = k_blind_rotate_s (128 threads x 16 coefficients per gate, signed lazy
  * residues, four gates per CTA), 48 = its timing experiment that reads key row 0 at every step (WRONG
- * results, tools only).  0 / 5 / 40 produce identical bits.  -1 / -2 switch off / on the separate launch
- * of a last partial wave (on by default; does not change the variant). */
+ * results, tools only), 6 / 41 = schedule-fuzzing builds of 5 / 40 (every warp sleeps a random 0..1 us around
+ * every barrier, __syncwarp, mbarrier wait and hand-over; tests only).  0 / 5 / 6 / 40 / 41 produce identical bits.  -1 / -2 switch off / on the separate launch
+ * of a last partial wave (on by default; does not change the variant).  -3 / -4 switch off / on the
+ * bulk-copy input prefetch of b2fhe_ntt1024_batch / b2fhe_intt1024_batch (on by default; A/B only). */
 int b2fhe_set_br_variant(int variant);
 /* 1 (default): small batches use the latency kernels; 0: every batch uses the throughput kernel (right for
  * many small calls in flight on many streams).  The choice depends on this setting and the batch size only. */

@@ -70,6 +70,39 @@ def test_ntt_roundtrip_and_polymul(engine):
             assert np.array_equal(got[i], orc.polymul(a[i], b[i], schoolbook=True)), f"poly {i}"
 
 
+def test_ntt_input_prefetch_equals_plain_loads(engine):
+    """The bulk-copy (TMA) input prefetch of b2fhe_ntt1024_batch / b2fhe_intt1024_batch against the plain-load
+    kernels (b2fhe_set_br_variant(-3)): same bytes on a ragged batch long enough that every persistent team
+    takes several polynomials (so the prefetched buffers are re-armed and re-used), on a batch of one, and
+    from a source that is only 4-byte aligned (takes the plain loads)."""
+    cf = engine
+    L = cf._lib.lib()
+    rng = np.random.default_rng(11)
+    cnt = 5003
+    a = rng.integers(0, 2**32, size=(cnt + 1, N), dtype=np.uint64).astype(np.uint32)
+    da = dev_u32(a.reshape(-1))
+    outs = {}
+    try:
+        for pf in (-3, -4):
+            cf._lib.check(L.b2fhe_set_br_variant(pf))
+            dn = torch.zeros((cnt, 2, N), dtype=torch.int32, device="cuda")
+            db = torch.zeros((cnt, N), dtype=torch.int32, device="cuda")
+            d1 = torch.zeros((1, 2, N), dtype=torch.int32, device="cuda")
+            dm = torch.zeros((7, 2, N), dtype=torch.int32, device="cuda")
+            cf._lib.check(L.b2fhe_ntt1024_batch(0, None, dn.data_ptr(), da.data_ptr(), cnt))
+            cf._lib.check(L.b2fhe_intt1024_batch(0, None, db.data_ptr(), dn.data_ptr(), cnt))
+            cf._lib.check(L.b2fhe_ntt1024_batch(0, None, d1.data_ptr(), da.data_ptr() + 4096 * 17, 1))
+            cf._lib.check(L.b2fhe_ntt1024_batch(0, None, dm.data_ptr(), da.data_ptr() + 4, 7))      # 4-byte aligned source
+            torch.cuda.synchronize()
+            outs[pf] = (to_np(dn, np.uint32), to_np(db, np.uint32), to_np(d1, np.uint32), to_np(dm, np.uint32))
+    finally:
+        cf._lib.check(L.b2fhe_set_br_variant(-4))
+    for x, y in zip(outs[-3], outs[-4]):
+        assert np.array_equal(x, y)
+    assert np.array_equal(outs[-4][1], a[:cnt])                       # round trip
+    assert np.array_equal(outs[-4][2][0], outs[-4][0][17])
+
+
 def test_polymul_edge_cases(engine):
     cf = engine
     L = cf._lib.lib()
@@ -168,6 +201,36 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
         gk = to_np(dks, np.uint16)
         for i in range(cnt):
             assert np.array_equal(gk[i], want[i]), (ks_variant, i)
+
+
+def test_schedule_jitter_is_bit_exact(engine, keys):
+    """Schedule fuzzing in place of compute-sanitizer's racecheck / synccheck (closed on this pool): variants 41 / 6
+    are k_blind_rotate_s / k_blind_rotate_cl4s compiled with a random 0..1 us sleep of every warp before and
+    after every named barrier, __syncwarp, __syncthreads, mbarrier wait and DSMEM hand-over (clock-seeded, so
+    every launch draws a different schedule).  A missing or misplaced synchronisation would let a warp read
+    an exchange buffer / accumulator / receive buffer too early or overwrite it too late; the outputs must
+    stay byte-identical to the oracle on every repetition."""
+    cf = engine
+    L = cf._lib.lib()
+    cnt = 9
+    c0 = orc.encrypt(keys, np.arange(cnt) & 1, 0, base_index=977)
+    c0[2, :] = 0
+    c0[3, :636] = 0xFFFF
+    d0 = torch.from_numpy(c0.view(np.int16)).cuda()
+    d1 = torch.empty((cnt, 1025), dtype=torch.int32, device="cuda")
+    refs = np.stack([orc.blind_rotate_extract(keys, c0[i]) for i in range(cnt)])
+    try:
+        for variant, g in ((41, 4), (41, 1), (6, 0)):
+            cf._lib.check(L.b2fhe_set_br_variant(variant))
+            cf._lib.check(L.b2fhe_set_gates_per_cta(g))
+            for rep in range(4):
+                d1.zero_()
+                cf._lib.check(L.b2fhe_blind_rotate_batch(0, None, d1.data_ptr(), d0.data_ptr(), 1 << 29, cnt))
+                torch.cuda.synchronize()
+                assert np.array_equal(to_np(d1, np.uint32), refs), f"variant {variant}, gates/cta {g}, repetition {rep}"
+    finally:
+        cf._lib.check(L.b2fhe_set_gates_per_cta(0))
+        cf._lib.check(L.b2fhe_set_br_variant(0))
 
 
 def test_trlwe_level_entry_points(engine, keys):

@@ -18,12 +18,15 @@ def t(fn, reps=5):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); fn(); e1.record(); torch.cuda.synchronize(); best = min(best, e0.elapsed_time(e1))
     return best
-for name, fn in (("ntt", lambda: cf._lib.check(L.b2fhe_ntt1024_batch(0, None, nt.data_ptr(), a.data_ptr(), n))),
-                 ("intt", lambda: cf._lib.check(L.b2fhe_intt1024_batch(0, None, o.data_ptr(), nt.data_ptr(), n))),
-                 ("polymul2", lambda: cf._lib.check(L.b2fhe_polymul1024_batch(0, None, o.data_ptr(), a.data_ptr(), b.data_ptr(), n))),
-                 ("polymul3_exact", lambda: cf._lib.check(L.b2fhe_polymul1024_exact_batch(0, None, o.data_ptr(), a.data_ptr(), b.data_ptr(), n)))):
+for pf in (-3, -4):
+  cf._lib.check(L.b2fhe_set_br_variant(pf))
+  for name, fn in (("ntt", lambda: cf._lib.check(L.b2fhe_ntt1024_batch(0, None, nt.data_ptr(), a.data_ptr(), n))),
+                   ("intt", lambda: cf._lib.check(L.b2fhe_intt1024_batch(0, None, o.data_ptr(), nt.data_ptr(), n))),
+                   ("polymul2", lambda: cf._lib.check(L.b2fhe_polymul1024_batch(0, None, o.data_ptr(), a.data_ptr(), b.data_ptr(), n))),
+                   ("polymul3_exact", lambda: cf._lib.check(L.b2fhe_polymul1024_exact_batch(0, None, o.data_ptr(), a.data_ptr(), b.data_ptr(), n)))):
+    if pf == -4 and name.startswith("polymul"): continue
     ms = t(fn)
-    print(json.dumps({"probe": name, "batch": n, "ms": ms, "gb_per_s": 12288 * n / ms * 1e-6}), flush=True)
+    print(json.dumps({"probe": name, "input_prefetch": pf == -4, "batch": n, "ms": ms, "gb_per_s": 12288 * n / ms * 1e-6}), flush=True)
 cf._lib.check(L.b2fhe_ntt1024_batch(0, None, nt.data_ptr(), a.data_ptr(), n))
 cf._lib.check(L.b2fhe_intt1024_batch(0, None, o.data_ptr(), nt.data_ptr(), n))
 torch.cuda.synchronize()
