@@ -90,8 +90,8 @@ int launch_ks(const DevCtx& c, KsParams P, cudaStream_t st)
         return 0;
     }
     // in-step variants (A/B): 10 + (warps per CTA: 0 = 8, 1 = 16, 2 = 32) * 3 + (barrier every 1 / 2 / 4 coefficients)
-    if (g_ks_variant == 0) {      // measured fastest (profiles/r1_probe_v14_keyswitch_in_step.log): 16 gates per CTA, barrier every 8 coefficients
-        k_keyswitch_step<16, 8><<<(P.count + 15) / 16, 32 * 16, 16 * kN * 2, st>>>(P);
+    if (g_ks_variant == 0) {      // measured fastest with the 16x2 adds (profiles/r2_probe_ks_viadd.log): 16 gates per CTA, barrier every 2 coefficients
+        k_keyswitch_step<16, 2><<<(P.count + 15) / 16, 32 * 16, 16 * kN * 2, st>>>(P);
         LAUNCHED();
         return 0;
     }

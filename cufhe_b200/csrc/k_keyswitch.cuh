@@ -66,6 +66,15 @@ __device__ __forceinline__ uint32_t ks_operand(const uint32_t* x, int j, int trl
     return j == 0 ? x[0] : j == kN ? x[kN] : 0u - x[kN - j];
 }
 
+// two u16 columns per word, each summed mod 2^16: ONE instruction (VIADD.16x2 on sm_100a) instead of a
+// 32-bit add for the low column + a shifted add for the high one
+__device__ __forceinline__ uint32_t add16x2(uint32_t a, uint32_t b)
+{
+    uint32_t r;
+    asm("add.u16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+
 constexpr int kKsGates = 8;                       // warps (= gates) per CTA
 
 __global__ void __launch_bounds__(32 * kKsGates) k_keyswitch(const KsParams P)
@@ -85,9 +94,9 @@ __global__ void __launch_bounds__(32 * kKsGates) k_keyswitch(const KsParams P)
     const uint32_t eb = ca * ks_operand(x0, kN, P.trlwe) + (x1 ? cb * x1[kN] : 0u) + it.off;
     __syncwarp();
 
-    uint32_t accF[10], accH[10];
+    uint32_t acc[10];
 #pragma unroll
-    for (int w = 0; w < 10; w++) accF[w] = accH[w] = 0u;
+    for (int w = 0; w < 10; w++) acc[w] = 0u;
     const uint32_t* Tl = P.T + lane;
     for (int j = 0; j < kN; j++) {
         const uint32_t tj = s_t[warp][j];
@@ -99,8 +108,7 @@ __global__ void __launch_bounds__(32 * kKsGates) k_keyswitch(const KsParams P)
 #pragma unroll
                 for (int w = 0; w < 10; w++) {
                     const uint32_t v = __ldg(row + 32 * w);
-                    accF[w] += v;
-                    accH[w] += v >> 16;
+                    acc[w] = add16x2(acc[w], v);
                 }
             }
         }
@@ -109,10 +117,10 @@ __global__ void __launch_bounds__(32 * kKsGates) k_keyswitch(const KsParams P)
 #pragma unroll
     for (int w = 0; w < 10; w++) {
         const int c0 = 2 * (lane + 32 * w);
-        if (c0 < kLwe) out[c0] = (uint16_t)accF[w];
-        else if (c0 == kLwe) out[c0] = (uint16_t)(accF[w] + iks_round_b(eb));
-        if (c0 + 1 < kLwe) out[c0 + 1] = (uint16_t)accH[w];
-        else if (c0 + 1 == kLwe) out[c0 + 1] = (uint16_t)(accH[w] + iks_round_b(eb));
+        if (c0 < kLwe) out[c0] = (uint16_t)acc[w];
+        else if (c0 == kLwe) out[c0] = (uint16_t)(acc[w] + iks_round_b(eb));
+        if (c0 + 1 < kLwe) out[c0 + 1] = (uint16_t)(acc[w] >> 16);
+        else if (c0 + 1 == kLwe) out[c0 + 1] = (uint16_t)((acc[w] >> 16) + iks_round_b(eb));
     }
 }
 
@@ -141,9 +149,9 @@ __global__ void __launch_bounds__(32 * W) k_keyswitch_step(const KsParams P)
     const uint32_t eb = ca * ks_operand(x0, kN, P.trlwe) + (x1 ? cb * x1[kN] : 0u) + it.off;
     __syncthreads();
 
-    uint32_t accF[10], accH[10];
+    uint32_t acc[10];
 #pragma unroll
-    for (int w = 0; w < 10; w++) accF[w] = accH[w] = 0u;
+    for (int w = 0; w < 10; w++) acc[w] = 0u;
     const uint32_t* Tl = P.T + lane;
     for (int j0 = 0; j0 < kN; j0 += SYNCJ) {
         if (active) {
@@ -159,8 +167,7 @@ __global__ void __launch_bounds__(32 * W) k_keyswitch_step(const KsParams P)
 #pragma unroll
                         for (int w = 0; w < 10; w++) {
                             const uint32_t v = __ldg(row + 32 * w);
-                            accF[w] += v;
-                            accH[w] += v >> 16;
+                            acc[w] = add16x2(acc[w], v);
                         }
                     }
                 }
@@ -173,10 +180,10 @@ __global__ void __launch_bounds__(32 * W) k_keyswitch_step(const KsParams P)
 #pragma unroll
     for (int w = 0; w < 10; w++) {
         const int c0 = 2 * (lane + 32 * w);
-        if (c0 < kLwe) out[c0] = (uint16_t)accF[w];
-        else if (c0 == kLwe) out[c0] = (uint16_t)(accF[w] + iks_round_b(eb));
-        if (c0 + 1 < kLwe) out[c0 + 1] = (uint16_t)accH[w];
-        else if (c0 + 1 == kLwe) out[c0 + 1] = (uint16_t)(accH[w] + iks_round_b(eb));
+        if (c0 < kLwe) out[c0] = (uint16_t)acc[w];
+        else if (c0 == kLwe) out[c0] = (uint16_t)(acc[w] + iks_round_b(eb));
+        if (c0 + 1 < kLwe) out[c0 + 1] = (uint16_t)(acc[w] >> 16);
+        else if (c0 + 1 == kLwe) out[c0 + 1] = (uint16_t)((acc[w] >> 16) + iks_round_b(eb));
     }
 }
 
@@ -200,9 +207,9 @@ __global__ void __launch_bounds__(32 * kKsLatWarps) k_keyswitch_lat(const KsPara
     const uint32_t eb = ca * ks_operand(x0, kN, P.trlwe) + (x1 ? cb * x1[kN] : 0u) + it.off;
     __syncthreads();
 
-    uint32_t accF[10], accH[10];
+    uint32_t acc[10];
 #pragma unroll
-    for (int w = 0; w < 10; w++) accF[w] = accH[w] = 0u;
+    for (int w = 0; w < 10; w++) acc[w] = 0u;
     const uint32_t* Tl = P.T + lane;
     constexpr int per = kN / kKsLatWarps;
     for (int j = warp * per; j < (warp + 1) * per; j++) {
@@ -215,20 +222,20 @@ __global__ void __launch_bounds__(32 * kKsLatWarps) k_keyswitch_lat(const KsPara
 #pragma unroll
                 for (int w = 0; w < 10; w++) {
                     const uint32_t v = __ldg(row + 32 * w);
-                    accF[w] += v;
-                    accH[w] += v >> 16;
+                    acc[w] = add16x2(acc[w], v);
                 }
             }
         }
     }
 #pragma unroll
-    for (int w = 0; w < 10; w++) s_red[warp][lane + 32 * w] = (accF[w] & 0xFFFFu) | (accH[w] << 16);
+    for (int w = 0; w < 10; w++) s_red[warp][lane + 32 * w] = acc[w];
     __syncthreads();
     uint16_t* out = P.out + (size_t)it.slot * kLvl0Words;
     for (int c = threadIdx.x; c < kKsRowWords; c += blockDim.x) {
-        uint32_t lo = 0u, hi = 0u;
+        uint32_t sum = 0u;
 #pragma unroll
-        for (int w = 0; w < kKsLatWarps; w++) { const uint32_t v = s_red[w][c]; lo += v; hi += v >> 16; }
+        for (int w = 0; w < kKsLatWarps; w++) sum = add16x2(sum, s_red[w][c]);
+        const uint32_t lo = sum, hi = sum >> 16;
         const int c0 = 2 * c;
         if (c0 < kLwe) out[c0] = (uint16_t)lo;
         else if (c0 == kLwe) out[c0] = (uint16_t)(lo + iks_round_b(eb));

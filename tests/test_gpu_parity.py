@@ -504,7 +504,7 @@ def test_default_large_batch_paths_against_single_row_kernel(engine):
 
 @pytest.mark.gpu
 def test_default_keyswitch_step_above_latency_threshold(engine, keys):
-    """Above 32 gates per SM the default key switch is k_keyswitch_step<16, 8> (below: k_keyswitch_lat).
+    """Above 32 gates per SM the default key switch is k_keyswitch_step<16, 2> (below: k_keyswitch_lat).
     A batch just over the threshold with a PARTIAL last CTA: every gate compared with the one-warp-per-gate
     k_keyswitch (variant 2), the first ones and the extreme rows with the oracle."""
     cf = engine
