@@ -196,7 +196,7 @@ int b2fhe_set_gates_per_cta(int gates)
 }
 int b2fhe_set_ks_variant(int variant)
 {
-    REQUIRE((variant >= 0 && variant <= 2) || (variant >= 10 && variant <= 21), B2FHE_E_BAD_ARGUMENT);
+    REQUIRE((variant >= 0 && variant <= 3) || (variant >= 10 && variant <= 21), B2FHE_E_BAD_ARGUMENT);
     g_ks_variant = variant;
     return 0;
 }

@@ -84,8 +84,15 @@ int launch_ks(const DevCtx& c, KsParams P, cudaStream_t st)
     if (P.count <= 0) return 0;
     P.T = c.ksk;
     if (g_ks_variant == 1 || (g_ks_variant == 0 && P.count <= g_ks_lat_max_per_sm * c.sm_count)) {
-        // small batch: 16 warps per gate instead of one
-        k_keyswitch_lat<<<P.count, 32 * kKsLatWarps, 0, st>>>(P);
+        // small batch: 16 warps per gate instead of one; 32 warps up to 4 gates per SM (half the chain of
+        // L2 round trips: single NAND 1.51 -> 1.49 ms warm, 1.60 -> 1.53 ms from a flushed L2, profiles/r2_probe_lat_ks.log)
+        if (P.count <= 4 * c.sm_count) k_keyswitch_lat<7, 32><<<P.count, 1024, 0, st>>>(P);
+        else k_keyswitch_lat<7><<<P.count, 32 * kKsLatWarps, 0, st>>>(P);
+        LAUNCHED();
+        return 0;
+    }
+    if (g_ks_variant == 3) {      // A/B of the latency kernel: a branch per digit (10 key words per thread in flight), 16 warps
+        k_keyswitch_lat<0><<<P.count, 32 * kKsLatWarps, 0, st>>>(P);
         LAUNCHED();
         return 0;
     }

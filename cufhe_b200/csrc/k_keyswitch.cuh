@@ -189,12 +189,23 @@ __global__ void __launch_bounds__(32 * W) k_keyswitch_step(const KsParams P)
 
 // Small-batch variant: one CTA of 16 warps per gate; warp w walks j in [64 w, 64 w + 64),
 // then the 16 partial sums are added through shared memory.  Same arithmetic (mod 2^16
-// per column), ~16x shorter critical path: 1.9 ms -> ~0.15 ms for a single gate.
-constexpr int kKsLatWarps = 16;
-__global__ void __launch_bounds__(32 * kKsLatWarps) k_keyswitch_lat(const KsParams P)
+// per column), ~16x shorter critical path than one warp per gate.
+// The walk is a chain of L2 round trips, so what matters is how many rows are in flight: the
+// digit test is a PREDICATE on the loads (zero digits load nothing and add 0), not a branch, and
+// the rows of DG digits (DG = 7: a whole coefficient, 70 words per thread) are requested before the
+// first is added.  DG = 0 keeps the branch per digit (round-1 form, 10 loads in flight; A/B).
+__device__ __forceinline__ uint32_t ldg_if(const uint32_t* p, uint32_t on)
+{
+    uint32_t v;
+    asm("{ .reg .pred q; setp.ne.u32 q, %2, 0; mov.u32 %0, 0; @q ld.global.nc.u32 %0, [%1]; }" : "=r"(v) : "l"(p), "r"(on));
+    return v;
+}
+constexpr int kKsLatWarps = 16;      // default; 32 for the smallest batches (half the chain of L2 round trips)
+template <int DG, int WARPS = kKsLatWarps>
+__global__ void __launch_bounds__(32 * WARPS) k_keyswitch_lat(const KsParams P)
 {
     __shared__ uint32_t s_t[kN];
-    __shared__ uint32_t s_red[kKsLatWarps][kKsRowWords];
+    __shared__ uint32_t s_red[WARPS][kKsRowWords];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int item = blockIdx.x;
     KsItem it;
@@ -211,19 +222,39 @@ __global__ void __launch_bounds__(32 * kKsLatWarps) k_keyswitch_lat(const KsPara
 #pragma unroll
     for (int w = 0; w < 10; w++) acc[w] = 0u;
     const uint32_t* Tl = P.T + lane;
-    constexpr int per = kN / kKsLatWarps;
+    constexpr int per = kN / WARPS;
     for (int j = warp * per; j < (warp + 1) * per; j++) {
         const uint32_t tj = s_t[j];
+        if (DG == 0) {
 #pragma unroll
-        for (int d = 0; d < kIksT; d++) {
-            const uint32_t dg = iks_digit(tj, d);
-            if (dg != 2u) {
-                const uint32_t* row = Tl + ((size_t)(j * kIksT + d) * 3 + min(dg, 2u)) * kKsRowWords;
+            for (int d = 0; d < kIksT; d++) {
+                const uint32_t dg = iks_digit(tj, d);
+                if (dg != 2u) {
+                    const uint32_t* row = Tl + ((size_t)(j * kIksT + d) * 3 + min(dg, 2u)) * kKsRowWords;
 #pragma unroll
-                for (int w = 0; w < 10; w++) {
-                    const uint32_t v = __ldg(row + 32 * w);
-                    acc[w] = add16x2(acc[w], v);
+                    for (int w = 0; w < 10; w++) acc[w] = add16x2(acc[w], __ldg(row + 32 * w));
                 }
+            }
+        } else {
+#pragma unroll
+            for (int d0 = 0; d0 < kIksT; d0 += DG) {
+                uint32_t v[DG ? DG : 1][10];
+#pragma unroll
+                for (int dd = 0; dd < DG; dd++) {
+                    const int d = d0 + dd;
+                    if (d < kIksT) {
+                        const uint32_t dg = iks_digit(tj, d);
+                        const uint32_t* row = Tl + ((size_t)(j * kIksT + d) * 3 + min(dg, 2u)) * kKsRowWords;
+#pragma unroll
+                        for (int w = 0; w < 10; w++) v[dd][w] = ldg_if(row + 32 * w, dg ^ 2u);
+                    }
+                }
+#pragma unroll
+                for (int dd = 0; dd < DG; dd++)
+                    if (d0 + dd < kIksT) {
+#pragma unroll
+                        for (int w = 0; w < 10; w++) acc[w] = add16x2(acc[w], v[dd][w]);
+                    }
             }
         }
     }
@@ -234,7 +265,7 @@ __global__ void __launch_bounds__(32 * kKsLatWarps) k_keyswitch_lat(const KsPara
     for (int c = threadIdx.x; c < kKsRowWords; c += blockDim.x) {
         uint32_t sum = 0u;
 #pragma unroll
-        for (int w = 0; w < kKsLatWarps; w++) sum = add16x2(sum, s_red[w][c]);
+        for (int w = 0; w < WARPS; w++) sum = add16x2(sum, s_red[w][c]);
         const uint32_t lo = sum, hi = sum >> 16;
         const int c0 = 2 * c;
         if (c0 < kLwe) out[c0] = (uint16_t)lo;

@@ -224,7 +224,7 @@ int b2fhe_set_br_variant(int variant);
  * many small calls in flight on many streams).  The choice depends on this setting and the batch size only. */
 int b2fhe_set_latency_mode(int on);
 /* key-switch kernel: 0 = by batch size (k_keyswitch_lat up to 32 gates per SM, else
- * k_keyswitch_step<16, 2>), 1 = k_keyswitch_lat (16 warps per gate), 2 = k_keyswitch (one
+ * k_keyswitch_step<16, 2>), 1 = k_keyswitch_lat (16 or 32 warps per gate), 3 = its round-1 form (A/B), 2 = k_keyswitch (one
  * free-running warp per gate), 10..18 = k_keyswitch_step<W, SYNCJ> with W = 8 / 16 / 32 gates per
  * CTA walking the mask in step, a barrier every SYNCJ = 1 / 2 / 4 coefficients (10 + 3 iW + iS),
  * 19 / 20 / 21 = <32, 8> / <32, 16> / <16, 8>.  All produce identical bits. */

@@ -193,7 +193,7 @@ def test_blind_rotate_and_keyswitch_stages(engine, keys):
     dx = dev_u32(x)
     dks = torch.empty((cnt, 637), dtype=torch.int16, device="cuda")
     want = [orc.keyswitch(keys, x[i]) for i in range(cnt)]
-    for ks_variant in (1, 2, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 0):   # 16 warps per gate / one warp per gate / in-step CTAs (W x SYNCJ) / by batch size
+    for ks_variant in (1, 2, 3, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 0):   # 16 warps per gate / one warp per gate / in-step CTAs (W x SYNCJ) / by batch size
         cf._lib.check(L.b2fhe_set_ks_variant(ks_variant))
         dks.zero_()
         cf._lib.check(L.b2fhe_keyswitch_batch(0, None, dks.data_ptr(), dx.data_ptr(), cnt))
@@ -528,6 +528,17 @@ def test_default_keyswitch_step_above_latency_threshold(engine, keys):
             cf._lib.check(L.b2fhe_keyswitch_batch(0, None, got.data_ptr(), dx.data_ptr(), cnt))
             torch.cuda.synchronize()
             assert torch.equal(got, want), variant
+        # k_keyswitch_lat on both sides of ITS 32-warp / 16-warp switch (4 gates per SM), default and round-1 form
+        for variant, n in ((0, 4 * sm), (0, 4 * sm + 3), (1, 4 * sm + 3), (3, 4 * sm + 3), (3, 9)):
+            cf._lib.check(L.b2fhe_set_ks_variant(variant))
+            got.zero_()
+            cf._lib.check(L.b2fhe_keyswitch_batch(0, None, got.data_ptr(), dx.data_ptr(), n))
+            torch.cuda.synchronize()
+            assert torch.equal(got[:n], want[:n]), (variant, n)
+        cf._lib.check(L.b2fhe_set_ks_variant(0))
+        got.zero_()
+        cf._lib.check(L.b2fhe_keyswitch_batch(0, None, got.data_ptr(), dx.data_ptr(), cnt))
+        torch.cuda.synchronize()
     finally:
         cf._lib.check(L.b2fhe_set_ks_variant(0))
     g = to_np(got, np.uint16)
