@@ -52,7 +52,8 @@ constexpr int kCl4SmemBytes = kCl4SmemWords * 4;
 
 // JIT: schedule fuzzing (b2fhe_set_br_variant(6)): random sleeps around every hand-over, barrier and
 // mbarrier wait; results must not change
-template <bool JIT = false>
+// MUT: mutation test of that fuzzing (tools/fuzz_mutants.cu): the in-loop synchronisation point number MUT (1..5) is dropped
+template <bool JIT = false, int MUT = 0>
 __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 2)
     k_blind_rotate_cl4s(const BrParams P, const PrimeSTables* __restrict__ g_tab)
 {
@@ -145,7 +146,7 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
         sts128<2048>(tx_own, x[8], x[9], x[10], x[11]);
         sts128<3072>(tx_own, x[12], x[13], x[14], x[15]);
         if (JIT) jitter_sleep(0x11u + rank * 4 + (threadIdx.x >> 5));
-        __syncthreads();
+        if (MUT != 1) __syncthreads();
         if (JIT) jitter_sleep(0x22u + rank * 4 + (threadIdx.x >> 5));
         {
             const V4 o0 = lds128<0>(tx_oth), o1 = lds128<1024>(tx_oth), o2 = lds128<2048>(tx_oth), o3 = lds128<3072>(tx_oth);
@@ -171,7 +172,7 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
                 st_async_v4(ra_part + (par * kN + v * 256) * 4, y[4 * v], y[4 * v + 1], y[4 * v + 2], y[4 * v + 3], rb_part + 8 * par);
         } else {
             // ---- B: team j adds the other accumulator polynomial's contribution, inverse transform ----
-            mbar_wait(smem_u32(mbar + par), phase);
+            if (MUT != 2) mbar_wait(smem_u32(mbar + par), phase);
             if (JIT) jitter_sleep(0x44u + rank * 4 + (threadIdx.x >> 5));
             const uint32_t rc = smem_u32(recv + par * kN + 4 * T);
             const V4 r0 = lds128<0>(rc), r1 = lds128<1024>(rc), r2 = lds128<2048>(rc), r3 = lds128<3072>(rc);
@@ -189,8 +190,8 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
             }
         }
         if (JIT) jitter_sleep(0x55u + rank * 4 + (threadIdx.x >> 5));
-        __syncthreads();                                       // zloc
-        mbar_wait(smem_u32(mbar + 2 + par), phase);
+        if (MUT != 3) __syncthreads();                         // zloc
+        if (MUT != 4) mbar_wait(smem_u32(mbar + 2 + par), phase);
         if (JIT) jitter_sleep(0x66u + rank * 4 + (threadIdx.x >> 5));
         // ---- C: CRT of output j, local accumulator update (two 128-bit slots per thread) ----------
 #pragma unroll
@@ -204,7 +205,7 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
             for (int e = 0; e < 4; e++) ap[64 * e] += q ? scrt_lift32(o[e], m[e], cw, cws) : scrt_lift32(m[e], o[e], cw, cws);
         }
         if (JIT) jitter_sleep(0x77u + rank * 4 + (threadIdx.x >> 5));
-        __syncthreads();                                       // rotated reads of the next step cross threads
+        if (MUT != 5) __syncthreads();                         // rotated reads of the next step cross threads
     }
 
     cluster.sync();                                            // no CTA leaves while a peer may still address it
