@@ -187,11 +187,10 @@ int uniform_gate(const DevCtx& c, cudaStream_t st, int op, int level, void* out,
     REQUIRE(in1 != nullptr && in2 != nullptr, B2FHE_E_BAD_ARGUMENT);
     const int sg = op == B2FHE_NMUX ? -1 : 1;
     if (level == 0) {           // src/bootstrap_gpu.cu:515-588
-        uint32_t *ta, *tb = nullptr;
+        uint32_t* ta;
         if (int r = S.get((void**)&ta, 2 * (size_t)count * kLvl1Words * 4)) return r;
         // both branches as ONE blind-rotation launch of 2 * count work items (one wave quantisation, not two):
-        // item g = inc AND in1 -> ta[g], item count + g = (NOT inc) AND in0 -> tb[g] = ta[count + g]
-        (void)tb;
+        // item g = inc AND in1 -> ta[g], item count + g = (NOT inc) AND in0 -> ta[count + g]
         BrItem* d_items;
         if (int r = S.get((void**)&d_items, 2 * (size_t)count * sizeof(BrItem))) return r;
         k_mux_items<<<(2 * count + 255) / 256, 256, 0, st>>>(d_items, count, -(int)kMu0);
