@@ -1,5 +1,30 @@
 // dev_common.cuh -- device-side plumbing shared by all kernels: named barriers, shared-window addresses.
 #pragma once
+#ifdef B2_HOST_TRACE
+// Host build of the step schedule for tests/emul/emul_sched.cpp (a CPU race detector that runs the REAL
+// brs_gate_loop source, one host thread per CUDA thread): no CUDA headers, the device qualifiers vanish, shared
+// memory and every synchronisation go through the tracer the emulator defines.
+#include <cstdint>
+#define __device__
+#define __host__
+#define __forceinline__ inline
+#define __constant__
+#define __restrict__
+struct uint4 { uint32_t x, y, z, w; };
+inline uint4 make_uint4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) { return uint4{x, y, z, w}; }
+#include "ntt_core.cuh"
+#include "tfhe_core.cuh"
+namespace b2 {
+uint32_t trace_smem_u32(const void* p);                   // byte offset inside the emulated shared memory
+void trace_bar(int id, int nthreads);                     // bar.sync id, nthreads
+void trace_warpsync();                                    // __syncwarp()
+uint32_t trace_ld(uint32_t addr, int word);               // one 32-bit word of a 4 / 8 / 16-byte access at addr
+void trace_st(uint32_t addr, int word, uint32_t v);
+bool trace_sync_kept(int site);                           // false: the emulator drops synchronisation point `site`
+inline uint32_t smem_u32(const void* p) { return trace_smem_u32(p); }
+inline void named_bar_sync(int id, int nthreads) { trace_bar(id, nthreads); }
+}  // namespace b2
+#else
 #include <cuda_runtime.h>
 #include "ntt_core.cuh"
 #include "tfhe_core.cuh"
@@ -49,3 +74,4 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 }
 
 }  // namespace b2
+#endif  // B2_HOST_TRACE

@@ -51,6 +51,28 @@ enum : int { ABL_LUT = 1,      // table look-ups at conflict-free (lane) indices
              ABL_JIT = 32 };
 
 // ---- shared memory through explicit 32-bit window addresses ------------------------------------
+#ifdef B2_HOST_TRACE
+template <int OFF> inline int32_t lds32(uint32_t a) { return (int32_t)trace_ld(a + OFF, 0); }
+template <int OFF> inline I2 lds64(uint32_t a) { I2 r; r.x = (int32_t)trace_ld(a + OFF, 0); r.y = (int32_t)trace_ld(a + OFF, 1); return r; }
+template <int OFF> inline V4 lds128(uint32_t a)
+{
+    V4 r;
+    r.x = (int32_t)trace_ld(a + OFF, 0); r.y = (int32_t)trace_ld(a + OFF, 1); r.z = (int32_t)trace_ld(a + OFF, 2); r.w = (int32_t)trace_ld(a + OFF, 3);
+    return r;
+}
+template <int OFF> inline void sts32(uint32_t a, int32_t v) { trace_st(a + OFF, 0, (uint32_t)v); }
+template <int OFF> inline void sts128(uint32_t a, int32_t x, int32_t y, int32_t z, int32_t w)
+{
+    trace_st(a + OFF, 0, (uint32_t)x); trace_st(a + OFF, 1, (uint32_t)y); trace_st(a + OFF, 2, (uint32_t)z); trace_st(a + OFF, 3, (uint32_t)w);
+}
+inline uint32_t __byte_perm(uint32_t x, uint32_t y, uint32_t s)
+{
+    const uint64_t v = ((uint64_t)y << 32) | x;
+    uint32_t r = 0;
+    for (int i = 0; i < 4; i++) r |= (uint32_t)((v >> (8 * ((s >> (4 * i)) & 7))) & 0xFF) << (8 * i);
+    return r;
+}
+#else
 template <int OFF> __device__ __forceinline__ int32_t lds32(uint32_t a)
 {
     int32_t r;
@@ -78,10 +100,15 @@ template <int OFF> __device__ __forceinline__ void sts128(uint32_t a, int32_t x,
     asm volatile("st.shared.v4.s32 [%0 + %1], {%2, %3, %4, %5};" ::"r"(a), "n"(OFF), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
 
+#endif
+
 // key vector load flavours (A/B in tools/ablate_brs.cu): 0 = ld.global.nc (through L1), 1 = ld.global.cg (L2 only),
 // 2 = ld.global.cs (streaming), 3 = ld.global.nc.L1::no_allocate
 template <int KEYLD> __device__ __forceinline__ uint4 ld_key(const uint4* p)
 {
+#ifdef B2_HOST_TRACE
+    return *p;
+#else
     if (KEYLD == 1) return __ldcg(p);
     if (KEYLD == 2) return __ldcs(p);
     if (KEYLD == 3) {
@@ -90,6 +117,7 @@ template <int KEYLD> __device__ __forceinline__ uint4 ld_key(const uint4* p)
         return r;
     }
     return __ldg(p);
+#endif
 }
 
 struct SAddr {              // per-thread shared-window byte addresses
@@ -104,6 +132,7 @@ struct SAddr {              // per-thread shared-window byte addresses
 };
 constexpr int kXsBytes = kXsWords * 4;
 
+#ifndef B2_HOST_TRACE
 __device__ __forceinline__ void stage_tables_s(uint32_t* s_tab, const TeamSTables* g_tab)
 {
     const uint4* src = reinterpret_cast<const uint4*>(g_tab);
@@ -124,10 +153,19 @@ __device__ __forceinline__ void jitter_sleep(uint32_t salt)
     h = __shfl_sync(0xFFFFFFFFu, h, 0);
     __nanosleep(h & 1023u);
 }
+#else
+inline void jitter_sleep(uint32_t) {}
+inline void __syncwarp() { trace_warpsync(); }
+struct { unsigned x; } static const threadIdx{0};      // only named by the (disabled) fuzzing sleeps
+#endif
 // SITE numbers the ten synchronisation points of a step; a MUTANT build (tools/fuzz_mutants.cu) drops one of them
 // to show that the fuzzing notices: ABL = ABL_JIT | site << kMutShift
 constexpr int kMutShift = 8;
+#ifdef B2_HOST_TRACE
+template <int ABL, int SITE> inline bool sync_kept() { return trace_sync_kept(SITE); }
+#else
 template <int ABL, int SITE> __host__ __device__ constexpr bool sync_kept() { return !(ABL & ABL_BAR) && ((ABL >> kMutShift) & 15) != SITE; }
+#endif
 template <int ABL, int SITE = 0> __device__ __forceinline__ void tbar_sync(int id, int n)
 {
     if (ABL & ABL_JIT) jitter_sleep(threadIdx.x >> 5);
@@ -291,7 +329,7 @@ __device__ __forceinline__ void acc_update(const uint32_t mine, const int32_t (&
 template <bool ROW0, int ABL, int KEYLD>
 __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, const uint32_t accb, const SAddr& a,
                                               const uint16_t* s_abar, const int T, const int q, const int tbar, const int gbar,
-                                              const uint32_t dbg)
+                                              const uint32_t dbg, const int nsteps = kLwe)
 {
     const int32_t p = (int32_t)(q ? Prime<1>::p : Prime<0>::p);
     const uint32_t pinv = q ? Prime<1>::pinv : Prime<0>::pinv;
@@ -301,7 +339,7 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, c
     const uint32_t own0 = accb + 4 * (kN + T);                     // &D_0[1024 + T]; D_1 = + 8192 bytes
     const uint32_t mine = own0 + q * 8192;                         // my output polynomial's +acc copy
     const uint4* row0 = bk4;                                       // rows 2j, 2j + 1 of step i: advances by two rows per j
-    for (int i = 0; i < kLwe; i++) {
+    for (int i = 0; i < nsteps; i++) {
         const uint32_t abar = s_abar[i];
         const uint32_t rot0 = own0 - 4 * (abar & (kN - 1));
         const bool flip = (abar >> kNbit) != 0;
@@ -384,6 +422,22 @@ __device__ __forceinline__ void brs_gate_loop(const uint32_t* __restrict__ bk, c
     }
 }
 
+// the shared-window addresses of thread T of team q (xs / xs_other: the two exchange arrays of my / the other team)
+__device__ __forceinline__ SAddr brs_addr(const TeamSTables* tab, const uint32_t* xs, const uint32_t* xs_other, const int q, const int T)
+{
+    SAddr a;
+    a.own = smem_u32(xs + chunk_of(T));
+    a.vw = smem_u32(xs + 20 * (T & 15) + 4 * (T >> 4));
+    a.sw = smem_u32(xs + 336 * (T >> 4) + (T & 15));
+    a.oth = smem_u32(xs_other + chunk_of(T));
+    a.tT = smem_u32(&tab->pr[q].perT[0][T]);
+    a.tLo = smem_u32(&tab->pr[q].i2[0][T & 15]);
+    a.tHi = smem_u32(&tab->pr[q].f2[T >> 4][0]);
+    a.lut = smem_u32(&tab->pr[q].lut0[0]);
+    return a;
+}
+
+#ifndef B2_HOST_TRACE
 template <int G, bool ROW0 = false, int ABL = 0, int KEYLD = 0>
 __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P, const TeamSTables* __restrict__ tabs)
 {
@@ -404,15 +458,7 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P,
     uint16_t* s_abar = reinterpret_cast<uint16_t*>(gbase + kBrsAccWords + 4 * kXsWords);
     const int gbar = 1 + gs, tbar = 1 + G + 2 * gs + q;      // named barriers (0 = __syncthreads)
 
-    SAddr a;
-    a.own = smem_u32(xs + chunk_of(T));
-    a.vw = smem_u32(xs + 20 * (T & 15) + 4 * (T >> 4));
-    a.sw = smem_u32(xs + 336 * (T >> 4) + (T & 15));
-    a.oth = smem_u32(xs_other + chunk_of(T));
-    a.tT = smem_u32(&tab->pr[q].perT[0][T]);
-    a.tLo = smem_u32(&tab->pr[q].i2[0][T & 15]);
-    a.tHi = smem_u32(&tab->pr[q].f2[T >> 4][0]);
-    a.lut = smem_u32(&tab->pr[q].lut0[0]);
+    const SAddr a = brs_addr(tab, xs, xs_other, q, T);
 
     // ---- pre-add + modulus switch (gatebootstrapping_gpu.cuh:316-345) ----
     BrItem it;
@@ -451,5 +497,7 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P,
     for (int m = t128; m < kN; m += 128) out[m] = m == 0 ? acc0[0] : 0u - acc0[kN - m];
     if (t128 == 0) out[kN] = acc1[0];
 }
+
+#endif  // B2_HOST_TRACE
 
 }  // namespace b2

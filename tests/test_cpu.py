@@ -130,6 +130,25 @@ def test_team_emulation_of_signed_ntt_cmux_and_exact_product(tmp_path):
     assert "cmux mismatches: 0 / 6" in out and "bank conflicts: 0" in out
 
 
+def test_step_schedule_race_detector_on_the_real_kernel_source(tmp_path):
+    """tests/emul/emul_sched.cpp compiles the REAL CMUX step of k_blind_rotate_s (brs_gate_loop and everything
+    below it, B2_HOST_TRACE build of the same headers) for the host and runs it with one host thread per CUDA
+    thread -- every lane independent -- under a vector-clock race detector over the emulated shared memory
+    (compute-sanitizer is closed on the GPU pool, and GPU-side schedule fuzzing cannot see a missing
+    __syncwarp).  The unmodified schedule must be race-free over several steps (one with a >= 1024) and reproduce
+    the oracle's accumulator; with any ONE of its ten synchronisation points removed the detector must fire."""
+    orc.build()
+    exe = str(tmp_path / "emul_sched")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-pthread", "-o", exe, os.path.join(ROOT, "tests", "emul", "emul_sched.cpp"),
+                           "-L" + os.path.join(ROOT, "oracle"), "-lorc", "-Wl,-rpath," + os.path.join(ROOT, "oracle")])
+    out = subprocess.run([exe, "5", "0"], capture_output=True, text=True, timeout=300).stdout
+    assert "races 0, accumulator words differing from the oracle 0" in out, out
+    for site in range(1, 11):
+        out = subprocess.run([exe, "2", str(site)], capture_output=True, text=True, timeout=300).stdout
+        races = int(out.split("races ")[1].split(",")[0])
+        assert races > 0, (site, out)
+
+
 # -------------------------------------------------------------- host logic ---
 def test_partition_covers_batch():
     from cufhe_b200.api import partition
