@@ -5,29 +5,54 @@
 // brs_gate_loop source, one host thread per CUDA thread): no CUDA headers, the device qualifiers vanish, shared
 // memory and every synchronisation go through the tracer the emulator defines.
 #include <cstdint>
+#include <cstddef>
+#include <algorithm>
 #define __device__
 #define __host__
+#define __global__
 #define __forceinline__ inline
 #define __constant__
 #define __restrict__
+#define __launch_bounds__(...)
+#define __cluster_dims__(...)
 struct uint4 { uint32_t x, y, z, w; };
 inline uint4 make_uint4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) { return uint4{x, y, z, w}; }
+struct TraceDim3 { unsigned x, y, z; };
+extern thread_local TraceDim3 threadIdx, blockIdx, blockDim, gridDim;      // set by the emulator per host thread
+template <class T> inline T __ldg(const T* p) { return *p; }
+using std::min;
 #include "ntt_core.cuh"
 #include "tfhe_core.cuh"
 namespace b2 {
-uint32_t trace_smem_u32(const void* p);                   // byte offset inside the emulated shared memory
-void trace_bar(int id, int nthreads);                     // bar.sync id, nthreads
+uint32_t trace_smem_u32(const void* p);                   // byte offset inside the emulated shared memory (all CTAs)
+uint32_t* trace_cta_smem();                               // my CTA's dynamic shared memory
+void trace_bar(int id, int nthreads);                     // bar.sync id, nthreads (of my CTA)
 void trace_warpsync();                                    // __syncwarp()
 uint32_t trace_ld(uint32_t addr, int word);               // one 32-bit word of a 4 / 8 / 16-byte access at addr
 void trace_st(uint32_t addr, int word, uint32_t v);
 bool trace_sync_kept(int site);                           // false: the emulator drops synchronisation point `site`
+void trace_mbar_init(uint32_t bar, uint32_t count);
+void trace_mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes);
+void trace_mbar_wait(uint32_t bar, uint32_t parity);
 inline uint32_t smem_u32(const void* p) { return trace_smem_u32(p); }
 inline void named_bar_sync(int id, int nthreads) { trace_bar(id, nthreads); }
+inline void mbar_init(uint32_t bar, uint32_t count) { trace_mbar_init(bar, count); }
+inline void mbar_fence_init() {}
+inline void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) { trace_mbar_arrive_expect_tx(bar, bytes); }
+inline void mbar_wait(uint32_t bar, uint32_t parity) { trace_mbar_wait(bar, parity); }
 }  // namespace b2
+inline void __syncthreads() { b2::trace_bar(0, (int)blockDim.x); }
+// dynamic shared memory of the kernel / plain-pointer accesses to it (traced on the host, plain on the device)
+#define B2_DYN_SMEM(name) uint32_t* name = b2::trace_cta_smem()
+#define B2_SMEM_RD(p) (b2::trace_ld(b2::trace_smem_u32(p), 0))
+#define B2_SMEM_WR(p, v) (b2::trace_st(b2::trace_smem_u32(p), 0, (v)))
 #else
 #include <cuda_runtime.h>
 #include "ntt_core.cuh"
 #include "tfhe_core.cuh"
+#define B2_DYN_SMEM(name) extern __shared__ __align__(16) uint32_t name[]
+#define B2_SMEM_RD(p) (*(p))
+#define B2_SMEM_WR(p, v) (*(p) = (v))
 
 namespace b2 {
 

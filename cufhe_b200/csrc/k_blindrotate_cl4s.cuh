@@ -23,11 +23,28 @@
 // Replaces (for batches of a few gates) __BlindRotatePreAdd__ + Accumulate
 // (reference include/gatebootstrapping_gpu.cuh:115-345), SampleExtract src/bootstrap_gpu.cu:366-381.
 #pragma once
-#include <cooperative_groups.h>
 #include "k_ntt_s.cuh"
+#ifdef B2_HOST_TRACE
+namespace b2 {
+uint32_t trace_mapa(uint32_t addr, int rank);
+void trace_st_async(uint32_t remote_addr, int32_t a, int32_t b, int32_t c, int32_t d, uint32_t remote_bar);
+int trace_cluster_rank();
+void trace_cluster_sync();
+}
+namespace cooperative_groups {
+struct cluster_group { unsigned block_rank() const { return (unsigned)b2::trace_cluster_rank(); } void sync() const { b2::trace_cluster_sync(); } };
+inline cluster_group this_cluster() { return cluster_group{}; }
+}
+#else
+#include <cooperative_groups.h>
+#endif
 
 namespace b2 {
 
+#ifdef B2_HOST_TRACE
+inline uint32_t mapa_u32(uint32_t addr, int rank) { return trace_mapa(addr, rank); }
+inline void st_async_v4(uint32_t remote_addr, int32_t a, int32_t b, int32_t c, int32_t d, uint32_t remote_bar) { trace_st_async(remote_addr, a, b, c, d, remote_bar); }
+#else
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, int rank)
 {
     uint32_t r;
@@ -40,7 +57,12 @@ __device__ __forceinline__ void st_async_v4(uint32_t remote_addr, int32_t a, int
     asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.s32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(remote_addr),
                  "r"(a), "r"(b), "r"(c), "r"(d), "r"(remote_bar) : "memory");
 }
+#endif
 
+#ifndef B2_CL4_STEPS
+#define B2_CL4_STEPS kLwe
+#endif
+constexpr int kCl4Steps = B2_CL4_STEPS;     // 636; the host trace build (tests/emul/emul_cl4s.cpp) walks a few steps only
 constexpr int kCl4Ctas = 4;
 constexpr int kCl4Threads = 128;
 constexpr int kCl4TabWords = (int)sizeof(PrimeSTables) / 4;
@@ -59,7 +81,7 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
 {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
-    extern __shared__ __align__(16) uint32_t smem[];
+    B2_DYN_SMEM(smem);
     uint32_t* acc = smem + kCl4TabWords + 4 * kXsWords;        // acc_j
     uint32_t* tx = acc + kN;                                   // [team][v * 64 + T] as 128-bit vectors: transformed digit
     uint32_t* recv = tx + 2 * kN;                              // [parity][v * 64 + T]: partial sum of output j from CTA (q, 1-j)
@@ -90,7 +112,7 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
     }
     const int cbody = it.off + ca * (int)a0[kLwe] + (a1 ? cb * (int)a1[kLwe] : 0);
     const uint32_t bbar = modswitch_b((uint32_t)cbody & 0xFFFFu);
-    for (int c = threadIdx.x; c < kN; c += kCl4Threads) acc[c] = j ? testvec_b((uint32_t)c, bbar, P.mu) : 0u;
+    for (int c = threadIdx.x; c < kN; c += kCl4Threads) B2_SMEM_WR(acc + c, j ? testvec_b((uint32_t)c, bbar, P.mu) : 0u);
     __syncthreads();
 
     const int32_t p = prime_of(q);
@@ -117,7 +139,7 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
     uint4 kb[8];                                               // this step's key vectors, fetched ONE STEP AHEAD (L2 latency ~ 1/5 of a step)
 #pragma unroll
     for (int v = 0; v < 4; v++) { kb[v] = __ldg(bk_own + v * 64); kb[4 + v] = __ldg(bk_oth + v * 64); }
-    for (int i = 0; i < kLwe; i++) {
+    for (int i = 0; i < kCl4Steps; i++) {
         const uint32_t abar = s_abar[i];
         const uint32_t am = abar & (kN - 1);
         const bool flip = (abar >> kNbit) != 0;
@@ -134,10 +156,10 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
         int32_t x[16], y[16];
 #pragma unroll
         for (int k = 0; k < 16; k++) {
-            uint32_t rot = acc[(rbase + 64 * k) & (kN - 1)];
+            uint32_t rot = B2_SMEM_RD(acc + ((rbase + 64 * k) & (kN - 1)));
             const bool neg = (k < kth) != flip;
             rot = neg ? 0u - rot : rot;
-            const uint32_t t = rot - acc[T + 64 * k] + kDecompAdd;
+            const uint32_t t = rot - B2_SMEM_RD(acc + T + 64 * k) + kDecompAdd;
             x[k] = (int32_t)((t >> dshift) & 0xFFu) - 128;
         }
         sfwd_general_dev<1>(x, y, a, q, p, bar, true, T);
@@ -202,7 +224,7 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
             const int32_t m[4] = {mine.x, mine.y, mine.z, mine.w}, o[4] = {othr.x, othr.y, othr.z, othr.w};
             uint32_t* ap = acc + (slot & 63) + 256 * (slot >> 6);                // coefficient T' + 64 (4 v + e)
 #pragma unroll
-            for (int e = 0; e < 4; e++) ap[64 * e] += q ? scrt_lift32(o[e], m[e], cw, cws) : scrt_lift32(m[e], o[e], cw, cws);
+            for (int e = 0; e < 4; e++) B2_SMEM_WR(ap + 64 * e, B2_SMEM_RD(ap + 64 * e) + (q ? scrt_lift32(o[e], m[e], cw, cws) : scrt_lift32(m[e], o[e], cw, cws)));
         }
         if (JIT) jitter_sleep(0x77u + rank * 4 + (threadIdx.x >> 5));
         if (MUT != 5) __syncthreads();                         // rotated reads of the next step cross threads
@@ -213,12 +235,12 @@ __global__ void __cluster_dims__(kCl4Ctas, 1, 1) __launch_bounds__(kCl4Threads, 
     if (q != 0) return;
     if (P.trlwe) {
         uint32_t* out = P.out + (size_t)it.slot * 2 * kN + j * kN;
-        for (int m = threadIdx.x; m < kN; m += kCl4Threads) out[m] = acc[m];
+        for (int m = threadIdx.x; m < kN; m += kCl4Threads) out[m] = B2_SMEM_RD(acc + m);
         return;
     }
     uint32_t* out = P.out + (size_t)it.slot * kLvl1Words;      // SampleExtract(0), src/bootstrap_gpu.cu:366-381
-    if (j == 0) { for (int m = threadIdx.x; m < kN; m += kCl4Threads) out[m] = m == 0 ? acc[0] : 0u - acc[kN - m]; }
-    else if (threadIdx.x == 0) out[kN] = acc[0];
+    if (j == 0) { for (int m = threadIdx.x; m < kN; m += kCl4Threads) out[m] = m == 0 ? B2_SMEM_RD(acc) : 0u - B2_SMEM_RD(acc + kN - m); }
+    else if (threadIdx.x == 0) out[kN] = B2_SMEM_RD(acc);
 }
 
 }  // namespace b2

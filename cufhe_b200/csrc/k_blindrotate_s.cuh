@@ -156,7 +156,6 @@ __device__ __forceinline__ void jitter_sleep(uint32_t salt)
 #else
 inline void jitter_sleep(uint32_t) {}
 inline void __syncwarp() { trace_warpsync(); }
-struct { unsigned x; } static const threadIdx{0};      // only named by the (disabled) fuzzing sleeps
 #endif
 // SITE numbers the ten synchronisation points of a step; a MUTANT build (tools/fuzz_mutants.cu) drops one of them
 // to show that the fuzzing notices: ABL = ABL_JIT | site << kMutShift

@@ -154,6 +154,7 @@ template <int K = 0> __device__ __forceinline__ void ld_stage_a(int32_t (&x)[16]
 // MODE 1: bootstrapping key / TRGSW rows -> Montgomery-form residues in [0, p), out index
 //         ((pl>>1)*2 + q)*2 + (pl&1), i.e. [i][row][prime][out poly][1024]
 // both in bk16_slot order: thread T writes vector v = positions 16 T + 4 v .. + 3 at word (64 v + T) 4
+#ifndef B2_HOST_TRACE      // the kernels below are device-only (the host trace build uses the team functions above)
 // PF: the NEXT polynomial of a slot is fetched by one bulk copy (TMA, cp.async.bulk) into a 4 KB staging buffer
 // while the current one is transformed -- the loads of a persistent team are otherwise exposed once per
 // polynomial (0.235 -> see DESIGN.md 4.4).  `in` must then be 16-byte aligned.
@@ -358,5 +359,7 @@ __global__ void __launch_bounds__(256) k_int_peak(uint32_t* out, int iters, int 
     for (int k = 0; k < 16; k++) acc ^= x[k];
     if (acc == 0x12345678u) out[0] = acc;      // keeps the loop alive, practically never taken
 }
+
+#endif  // B2_HOST_TRACE
 
 }  // namespace b2

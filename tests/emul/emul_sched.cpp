@@ -14,100 +14,14 @@
 // usage: emul_sched [steps] [drop_site]   drop_site = 1..10 removes that synchronisation point of the step
 // (the numbering of tbar_sync<ABL, SITE> / warp_sync<ABL, SITE>); the detector must then report races.
 #define B2_HOST_TRACE 1
-#include <algorithm>
-#include <atomic>
-#include <condition_variable>
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
-#include <map>
-#include <mutex>
 #include <random>
-#include <thread>
-#include <vector>
 #include "../../cufhe_b200/csrc/k_blindrotate_s.cuh"
 #include "../../oracle/cufhe_oracle.h"
+#define TRACE_THREADS 128                       // one gate: two teams of 64
+#define TRACE_CTA_THREADS 128
+#include "trace_rt.h"
 
 using namespace b2;
-
-constexpr int kThreads = 128;                     // one gate: two teams of 64
-static std::vector<uint32_t> g_smem;              // emulated shared memory (words)
-static std::mutex g_mu;                           // one lock for the whole tracer
-static std::condition_variable g_cv;
-static int g_drop_site = 0;
-static thread_local int t_tid = -1;
-
-// ---- vector clocks ----------------------------------------------------------------------------------
-struct VC { uint32_t c[kThreads]; };
-static VC g_vc[kThreads];
-struct Access { int tid; uint32_t clk; };
-struct Shadow { Access w{-1, 0}; std::vector<Access> r; };
-static std::vector<Shadow> g_shadow;
-static long g_races = 0, g_events = 0;
-static std::map<std::pair<uint32_t, int>, int> g_race_words;       // (word, kind) -> count, for the report
-
-static bool ordered(const Access& a, int me) { return a.tid < 0 || a.tid == me || g_vc[me].c[a.tid] >= a.clk; }
-static void report(uint32_t word, int kind, const Access& a, int me)
-{
-    g_races++;
-    if (g_race_words.size() < 8) g_race_words[{word, kind}]++;
-    (void)a; (void)me;
-}
-
-namespace b2 {
-uint32_t trace_smem_u32(const void* p) { return (uint32_t)((const char*)p - (const char*)g_smem.data()); }
-bool trace_sync_kept(int site) { return site != g_drop_site; }
-uint32_t trace_ld(uint32_t addr, int word)
-{
-    std::lock_guard<std::mutex> lk(g_mu);
-    const uint32_t w = addr / 4 + word;
-    if (addr % 4 || w >= g_smem.size()) { printf("bad shared address %u\n", addr); exit(2); }
-    Shadow& s = g_shadow[w];
-    g_events++;
-    if (!ordered(s.w, t_tid)) report(w, 0, s.w, t_tid);                 // read after an unordered write
-    bool found = false;
-    for (auto& a : s.r) if (a.tid == t_tid) { a.clk = g_vc[t_tid].c[t_tid]; found = true; }
-    if (!found) s.r.push_back(Access{t_tid, g_vc[t_tid].c[t_tid]});
-    return g_smem[w];
-}
-void trace_st(uint32_t addr, int word, uint32_t v)
-{
-    std::lock_guard<std::mutex> lk(g_mu);
-    const uint32_t w = addr / 4 + word;
-    if (addr % 4 || w >= g_smem.size()) { printf("bad shared address %u\n", addr); exit(2); }
-    Shadow& s = g_shadow[w];
-    g_events++;
-    if (!ordered(s.w, t_tid)) report(w, 1, s.w, t_tid);                 // write after an unordered write
-    for (auto& a : s.r) if (!ordered(a, t_tid)) report(w, 2, a, t_tid); // write after an unordered read
-    s.r.clear();
-    s.w = Access{t_tid, g_vc[t_tid].c[t_tid]};
-    g_smem[w] = v;
-}
-
-// ---- barriers: bar.sync id, n (counted, like the hardware) and __syncwarp (the 32 lanes of my warp) ----
-struct Bar { std::vector<int> arrived; uint64_t gen = 0; };
-static std::map<int, Bar> g_bars;                 // key: id for named barriers, 1000 + warp for __syncwarp
-static void barrier(int key, int n)
-{
-    std::unique_lock<std::mutex> lk(g_mu);
-    Bar& b = g_bars[key];
-    b.arrived.push_back(t_tid);
-    if ((int)b.arrived.size() == n) {
-        VC j{};
-        for (int t : b.arrived)
-            for (int i = 0; i < kThreads; i++) j.c[i] = std::max(j.c[i], g_vc[t].c[i]);
-        for (int t : b.arrived) { g_vc[t] = j; g_vc[t].c[t]++; }
-        b.arrived.clear();
-        b.gen++;
-        g_cv.notify_all();
-    } else {
-        const uint64_t gen = b.gen;
-        g_cv.wait(lk, [&] { return b.gen != gen; });
-    }
-}
-void trace_bar(int id, int nthreads) { barrier(id, nthreads); }
-void trace_warpsync() { barrier(1000 + t_tid / 32, 32); }
-}  // namespace b2
 
 // ---- key conversion on the host: raw TRGSW polynomial -> NTT domain, Montgomery form, bk16_slot order ----
 static TeamSTables3 L;
@@ -137,17 +51,18 @@ static void ntt_host(uint32_t* dst, const uint32_t* src, int q)
 int main(int argc, char** argv)
 {
     const int steps = argc > 1 ? atoi(argv[1]) : 2;
-    g_drop_site = argc > 2 ? atoi(argv[2]) : 0;
+    trace::drop_site = argc > 2 ? atoi(argv[2]) : 0;
     static TeamSConst CS;
     make_tables16s(L, CS);
     c_s = CS;
     std::mt19937_64 rng(20261105);
 
     // shared memory of a one-gate CTA, laid out as the kernel lays it out
-    g_smem.assign((size_t)brs_smem_bytes(1) / 4, 0u);
-    g_shadow.resize(g_smem.size());
-    memcpy(g_smem.data(), &L, sizeof(TeamSTables));                         // the first two primes
-    uint32_t* gbase = g_smem.data() + kTeamSTableWords;
+    trace::cta_words = (size_t)brs_smem_bytes(1) / 4;
+    trace::smem.assign(trace::cta_words, 0u);
+    trace::shadow.resize(trace::smem.size());
+    memcpy(trace::smem.data(), &L, sizeof(TeamSTables));                    // the first two primes
+    uint32_t* gbase = trace::smem.data() + kTeamSTableWords;
     uint32_t* acc = gbase;                                                  // [-acc_0 | +acc_0 | -acc_1 | +acc_1]
     uint16_t* s_abar = reinterpret_cast<uint16_t*>(gbase + kBrsAccWords + 4 * kXsWords);
     static uint32_t ref[2 * kN];
@@ -170,19 +85,15 @@ int main(int argc, char** argv)
         orc_cmux_step(ref, s_abar[i], &bk_raw[(size_t)i * 8 * kN], 0);
     }
 
-    const TeamSTables* tab = reinterpret_cast<const TeamSTables*>(g_smem.data());
-    std::vector<std::thread> th;
-    for (int t = 0; t < kThreads; t++)
-        th.emplace_back([&, t] {
-            t_tid = t;
-            const int q = t >> 6, T = t & 63;
-            uint32_t* xs = gbase + kBrsAccWords + q * 2 * kXsWords;
-            uint32_t* xs_other = gbase + kBrsAccWords + (q ^ 1) * 2 * kXsWords;
-            const SAddr a = brs_addr(tab, xs, xs_other, q, T);
-            const int gbar = 1, tbar = 2 + q;
-            brs_gate_loop<false, 0, 0>(bk_dev.data(), smem_u32(acc), a, s_abar, T, q, tbar, gbar, 0u, steps);
-        });
-    for (auto& x : th) x.join();
+    const TeamSTables* tab = reinterpret_cast<const TeamSTables*>(trace::smem.data());
+    trace::launch(1, [&](int, int t) {
+        const int q = t >> 6, T = t & 63;
+        uint32_t* xs = gbase + kBrsAccWords + q * 2 * kXsWords;
+        uint32_t* xs_other = gbase + kBrsAccWords + (q ^ 1) * 2 * kXsWords;
+        const SAddr a = brs_addr(tab, xs, xs_other, q, T);
+        const int gbar = 1, tbar = 2 + q;
+        brs_gate_loop<false, 0, 0>(bk_dev.data(), smem_u32(acc), a, s_abar, T, q, tbar, gbar, 0u, steps);
+    });
 
     int bad = 0;
     for (int j = 0; j < 2; j++)
@@ -191,8 +102,7 @@ int main(int argc, char** argv)
             bad += acc[2 * j * kN + c] != 0u - ref[j * kN + c];
         }
     printf("steps %d, dropped synchronisation point %d: %ld shared-memory accesses traced, races %ld, accumulator words differing from the oracle %d\n",
-           steps, g_drop_site, g_events, g_races, bad);
-    for (auto& kv : g_race_words)
-        printf("  e.g. word %u (%s)\n", kv.first.first, kv.first.second == 0 ? "read after unordered write" : kv.first.second == 1 ? "write after unordered write" : "write after unordered read");
+           steps, trace::drop_site, trace::events, trace::races, bad);
+    trace::print_races();
     return 0;
 }

@@ -149,6 +149,25 @@ def test_step_schedule_race_detector_on_the_real_kernel_source(tmp_path):
         assert races > 0, (site, out)
 
 
+def test_cluster_kernel_race_detector_on_the_real_kernel_source(tmp_path):
+    """tests/emul/emul_cl4s.cpp runs the REAL k_blind_rotate_cl4s (4 CTAs x 128 threads, B2_HOST_TRACE build) on
+    512 host threads: distributed shared memory (mapa, st.async with mbarrier complete_tx), the mbarrier waits,
+    __syncthreads, team barriers and cluster.sync are modelled by tests/emul/trace_rt.h with vector clocks.  Five
+    CMUX steps (the double-buffered receive buffers are re-used twice) must be race-free and give the oracle's
+    TRLWE; without any ONE of the five in-loop synchronisation points -- the two mbarrier waits included, which
+    are not run as mutants on the GPU because they may hang it -- the detector must fire."""
+    orc.build()
+    exe = str(tmp_path / "emul_cl4s")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-pthread", "-o", exe, os.path.join(ROOT, "tests", "emul", "emul_cl4s.cpp"),
+                           "-L" + os.path.join(ROOT, "oracle"), "-lorc", "-Wl,-rpath," + os.path.join(ROOT, "oracle")])
+    out = subprocess.run([exe, "0"], capture_output=True, text=True, timeout=600).stdout
+    assert "races 0, TRLWE words differing from the oracle 0" in out, out
+    for site in range(1, 6):
+        out = subprocess.run([exe, str(site)], capture_output=True, text=True, timeout=600).stdout
+        races = int(out.split("races ")[1].split(",")[0])
+        assert races > 0, (site, out)
+
+
 # -------------------------------------------------------------- host logic ---
 def test_partition_covers_batch():
     from cufhe_b200.api import partition
