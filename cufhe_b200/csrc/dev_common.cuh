@@ -34,12 +34,14 @@ bool trace_sync_kept(int site);                           // false: the emulator
 void trace_mbar_init(uint32_t bar, uint32_t count);
 void trace_mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes);
 void trace_mbar_wait(uint32_t bar, uint32_t parity);
+void trace_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar);
 inline uint32_t smem_u32(const void* p) { return trace_smem_u32(p); }
 inline void named_bar_sync(int id, int nthreads) { trace_bar(id, nthreads); }
 inline void mbar_init(uint32_t bar, uint32_t count) { trace_mbar_init(bar, count); }
 inline void mbar_fence_init() {}
 inline void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) { trace_mbar_arrive_expect_tx(bar, bytes); }
 inline void mbar_wait(uint32_t bar, uint32_t parity) { trace_mbar_wait(bar, parity); }
+inline void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) { trace_bulk_g2s(dst, src, bytes, bar); }
 }  // namespace b2
 inline void __syncthreads() { b2::trace_bar(0, (int)blockDim.x); }
 // dynamic shared memory of the kernel / plain-pointer accesses to it (traced on the host, plain on the device)

@@ -154,7 +154,6 @@ template <int K = 0> __device__ __forceinline__ void ld_stage_a(int32_t (&x)[16]
 // MODE 1: bootstrapping key / TRGSW rows -> Montgomery-form residues in [0, p), out index
 //         ((pl>>1)*2 + q)*2 + (pl&1), i.e. [i][row][prime][out poly][1024]
 // both in bk16_slot order: thread T writes vector v = positions 16 T + 4 v .. + 3 at word (64 v + T) 4
-#ifndef B2_HOST_TRACE      // the kernels below are device-only (the host trace build uses the team functions above)
 // PF: the NEXT polynomial of a slot is fetched by one bulk copy (TMA, cp.async.bulk) into a 4 KB staging buffer
 // while the current one is transformed -- the loads of a persistent team are otherwise exposed once per
 // polynomial (0.235 -> see DESIGN.md 4.4).  `in` must then be 16-byte aligned.
@@ -162,7 +161,7 @@ template <int MODE, bool PF = false>
 __global__ void __launch_bounds__(kNttThreadsS) k_ntt_fwd_s(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int npoly,
                                                             const PrimeSTables* __restrict__ g_tab)
 {
-    extern __shared__ __align__(16) uint32_t smem[];
+    B2_DYN_SMEM(smem);
     stage_fwd_image(smem, g_tab);
     const int team = threadIdx.x >> 6, T = threadIdx.x & 63;
     const int q = team & 1, slot = team >> 1;
@@ -185,7 +184,7 @@ __global__ void __launch_bounds__(kNttThreadsS) k_ntt_fwd_s(const uint32_t* __re
             mbar_wait(mb, phase);
             phase ^= 1u;
             ld_stage_a(x, stg + 4 * T, p);
-            named_bar_sync(pbar, 128);              // both prime teams have read the buffer
+            if (sync_kept<0, 11>()) named_bar_sync(pbar, 128);      // both prime teams have read the buffer (site 11 of the host race detector's mutants)
             if (producer && pl + stride < npoly) { mbar_arrive_expect_tx(mb, kN * 4); bulk_g2s(stg, in + (size_t)(pl + stride) * kN, kN * 4, mb); }
         } else {
             const uint32_t* src = in + (size_t)pl * kN + T;
@@ -216,7 +215,7 @@ template <bool PF = false>
 __global__ void __launch_bounds__(kNttThreadsS) k_ntt_inv_s(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int npoly,
                                                             const PrimeSTables* __restrict__ g_tab)
 {
-    extern __shared__ __align__(16) uint32_t smem[];
+    B2_DYN_SMEM(smem);
     stage_inv_image(smem, g_tab);
     const int team = threadIdx.x >> 6, T = threadIdx.x & 63;
     const int q = team & 1;
@@ -240,7 +239,7 @@ __global__ void __launch_bounds__(kNttThreadsS) k_ntt_inv_s(const uint32_t* __re
             const V4 t0 = lds128<0>(stg + 16 * T), t1 = lds128<1024>(stg + 16 * T), t2 = lds128<2048>(stg + 16 * T), t3 = lds128<3072>(stg + 16 * T);
             x[0] = t0.x; x[1] = t0.y; x[2] = t0.z; x[3] = t0.w; x[4] = t1.x; x[5] = t1.y; x[6] = t1.z; x[7] = t1.w;
             x[8] = t2.x; x[9] = t2.y; x[10] = t2.z; x[11] = t2.w; x[12] = t3.x; x[13] = t3.y; x[14] = t3.z; x[15] = t3.w;
-            named_bar_sync(tbar, 64);                   // the team has read the buffer
+            if (sync_kept<0, 12>()) named_bar_sync(tbar, 64);       // the team has read the buffer (site 12)
             if (producer && pl + stride < npoly) {
                 mbar_arrive_expect_tx(mb, kN * 4);
                 bulk_g2s(stg, in + ((size_t)(pl + stride) * 2 + q) * kN, kN * 4, mb);
@@ -279,7 +278,7 @@ template <int NPR>
 __global__ void __launch_bounds__(64 * NPR * 2) k_polymul_s(const uint32_t* __restrict__ a_in, const uint32_t* __restrict__ b_in,
                                                             uint32_t* __restrict__ out, int npoly, const PrimeSTables* __restrict__ g_tab)
 {
-    extern __shared__ __align__(16) uint32_t smem[];
+    B2_DYN_SMEM(smem);
     stage_prime_tables<NPR>(smem, g_tab);
     __syncthreads();
     const int team = threadIdx.x >> 6, T = threadIdx.x & 63;
@@ -333,6 +332,7 @@ __global__ void __launch_bounds__(64 * NPR * 2) k_polymul_s(const uint32_t* __re
     }
 }
 
+#ifndef B2_HOST_TRACE      // device-only
 // ---- integer-pipe peak probe (roofline denominator) -------------------
 // mode 0: independent IMAD (lo) chains; mode 1: the butterfly actually used
 // (IMAD.HI + 2 IMAD + IADD3 + IADD), 16 independent chains per thread, registers only.

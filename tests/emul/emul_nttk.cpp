@@ -1,0 +1,91 @@
+// CPU race detector for the stand-alone transform kernels -- test infrastructure.
+//
+// Runs the REAL kernels of cufhe_b200/csrc/k_ntt_s.cuh (B2_HOST_TRACE build, one persistent CTA, one host thread
+// per CUDA thread): k_ntt_fwd_s<0, true> and k_ntt_inv_s<true> with their bulk-copy (TMA) input prefetch -- a
+// staging buffer that is re-armed and overwritten while other threads may still read it, an mbarrier with a
+// transaction count -- and k_polymul_s<2> / <3>.  tests/emul/trace_rt.h reports every pair of unordered
+// conflicting shared-memory accesses; the results are checked as well: INTT(NTT(x)) == x and the products
+// against the oracle's schoolbook product.
+// usage: emul_nttk [polys] [drop] [deadlock seconds]   drop = 11 / 12 removes the barrier that protects the staging buffer of the
+// forward / inverse kernel from being refilled while it is read; the detector must then report (races, and the
+// deadlock that follows when the mbarrier's phase runs ahead of a waiting thread).
+#define B2_HOST_TRACE 1
+#include <random>
+#include "../../cufhe_b200/csrc/k_ntt_s.cuh"
+#include "../../oracle/cufhe_oracle.h"
+#define TRACE_THREADS 512
+#define TRACE_CTA_THREADS 512
+#include "trace_rt.h"
+
+using namespace b2;
+static TeamSTables3 L;
+
+static void reset(size_t bytes)
+{
+    trace::cta_words = bytes / 4;
+    trace::smem.assign(trace::cta_words, 0u);
+    trace::shadow.assign(trace::smem.size(), trace::Shadow{});
+    trace::bars.clear();
+    trace::mbars.clear();
+    for (auto& v : trace::vc) v = trace::VC{};
+}
+
+int main(int argc, char** argv)
+{
+    const int n = argc > 1 ? atoi(argv[1]) : 13;          // ragged: the four polynomial slots of the CTA take 4, 3, 3, 3
+    trace::drop_site = argc > 2 ? atoi(argv[2]) : 0;
+    if (argc > 3) trace::deadlock_s = atoi(argv[3]);
+    static TeamSConst CS;
+    make_tables16s(L, CS);
+    c_s = CS;
+    std::mt19937_64 rng(20261107);
+    std::vector<uint32_t> a((size_t)n * kN), b((size_t)n * kN), res((size_t)n * 2 * kN), back((size_t)n * kN), prod((size_t)n * kN);
+    for (auto& v : a) v = (uint32_t)rng();
+    for (auto& v : b) v = (uint32_t)(rng() % (1u << 18));
+
+    long races = 0, events = 0;
+    // forward, inputs prefetched by bulk copies
+    reset((size_t)ntt_fwd_pf_smem_bytes<kNttTeams>());
+    trace::launch(1, [&](int, int) { k_ntt_fwd_s<0, true>(a.data(), res.data(), n, L.pr); });
+    printf("k_ntt_fwd_s<0, true>: %ld accesses, races %ld\n", trace::events, trace::races);
+    races += trace::races; events += trace::events; trace::races = trace::events = 0;
+    // inverse, inputs prefetched by bulk copies
+    reset((size_t)ntt_inv_pf_smem_bytes<kNttTeams>());
+    trace::launch(1, [&](int, int) { k_ntt_inv_s<true>(res.data(), back.data(), n, L.pr); });
+    printf("k_ntt_inv_s<true>:    %ld accesses, races %ld\n", trace::events, trace::races);
+    races += trace::races; events += trace::events; trace::races = trace::events = 0;
+    int bad_rt = 0;
+    for (size_t i = 0; i < a.size(); i++) bad_rt += back[i] != a[i];
+    int bad_range = 0;
+    for (int p = 0; p < n; p++)
+        for (int q = 0; q < 2; q++)
+            for (int i = 0; i < kN; i++) bad_range += res[((size_t)p * 2 + q) * kN + i] >= kP[q];
+
+    // products: two primes (b small enough for P ~ 2^53: 8-bit), three primes (b < 2^18, the reference test's domain)
+    int bad_prod = 0;
+    {
+        std::vector<uint32_t> b8((size_t)n * kN);
+        for (auto& v : b8) v = (uint32_t)(int32_t)((int)(rng() % 256) - 128);
+        reset((size_t)ntt_s_smem_bytes<2, 4>());
+        trace::launch(1, [&](int, int) { k_polymul_s<2>(a.data(), b8.data(), prod.data(), n, L.pr); }, 256);
+        printf("k_polymul_s<2>:       %ld accesses, races %ld\n", trace::events, trace::races);
+        races += trace::races; events += trace::events; trace::races = trace::events = 0;
+        static uint32_t ref[kN];
+        for (int p = 0; p < n; p++) {
+            orc_polymul_schoolbook(ref, &a[(size_t)p * kN], &b8[(size_t)p * kN]);
+            bad_prod += memcmp(ref, &prod[(size_t)p * kN], sizeof ref) != 0;
+        }
+        reset((size_t)ntt_s_smem_bytes<3, 6>());
+        trace::launch(1, [&](int, int) { k_polymul_s<3>(a.data(), b.data(), prod.data(), n, L.pr); }, 384);
+        printf("k_polymul_s<3>:       %ld accesses, races %ld\n", trace::events, trace::races);
+        races += trace::races; events += trace::events;
+        for (int p = 0; p < n; p++) {
+            orc_polymul_schoolbook(ref, &a[(size_t)p * kN], &b[(size_t)p * kN]);
+            bad_prod += memcmp(ref, &prod[(size_t)p * kN], sizeof ref) != 0;
+        }
+    }
+    printf("polynomials %d: %ld shared-memory accesses traced, races %ld, round-trip words wrong %d, residues out of range %d, products wrong %d\n",
+           n, events, races, bad_rt, bad_range, bad_prod);
+    trace::print_races();
+    return 0;
+}

@@ -18,6 +18,8 @@
 #include <mutex>
 #include <thread>
 #include <vector>
+#include <chrono>
+#include <unistd.h>
 
 thread_local TraceDim3 threadIdx{0, 0, 0}, blockIdx{0, 0, 0}, blockDim{1, 1, 1}, gridDim{1, 1, 1};
 
@@ -29,6 +31,7 @@ static size_t cta_words = 0;                      // words per CTA
 static std::mutex mu;                             // one lock for the whole tracer
 static std::condition_variable cv;
 static int drop_site = 0;
+static int deadlock_s = 20;                       // a wait longer than this is reported as a deadlock
 static thread_local int tid = -1;                 // global thread id = cta * kCtaThreads + threadIdx.x
 static inline int my_cta() { return tid / kCtaThreads; }
 
@@ -91,7 +94,11 @@ static void barrier(long key, int n)
         cv.notify_all();
     } else {
         const uint64_t gen = b.gen;
-        cv.wait(lk, [&] { return b.gen != gen; });
+        if (!cv.wait_for(lk, std::chrono::seconds(deadlock_s), [&] { return b.gen != gen; })) {
+            printf("DEADLOCK: thread %d waits at barrier %ld (%zu of %d arrived); races so far %ld\n", tid, key, b.arrived.size(), n, races);
+            fflush(stdout);
+            _exit(3);
+        }
     }
 }
 
@@ -167,28 +174,45 @@ void trace_st_async(uint32_t remote_addr, int32_t a, int32_t b, int32_t c, int32
     trace::mbar_contribute(m);
     trace::mbar_check_complete(m);
 }
+// cp.async.bulk global -> shared with mbarrier::complete_tx::bytes: the words are written on behalf of the issuing
+// thread (the async proxy starts after the issue), then the bytes complete on the mbarrier
+void trace_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
+{
+    std::lock_guard<std::mutex> lk(trace::mu);
+    const uint32_t* s = (const uint32_t*)src;
+    for (uint32_t i = 0; i < bytes / 4; i++) trace::st_word_locked(dst / 4 + i, s[i]);
+    trace::MBar& m = trace::mbars[bar];
+    m.tx -= bytes;
+    trace::mbar_contribute(m);
+    trace::mbar_check_complete(m);
+}
 // try_wait.parity P: returns once the phase with parity P has completed
 void trace_mbar_wait(uint32_t bar, uint32_t parity)
 {
     std::unique_lock<std::mutex> lk(trace::mu);
     trace::MBar& m = trace::mbars[bar];
-    trace::cv.wait(lk, [&] { return (m.phase & 1u) != (parity & 1u); });
+    if (!trace::cv.wait_for(lk, std::chrono::seconds(trace::deadlock_s), [&] { return (m.phase & 1u) != (parity & 1u); })) {
+        printf("DEADLOCK: thread %d waits for parity %u of the mbarrier at %u (phase %u, %d arrivals and %ld bytes pending); races so far %ld\n",
+               trace::tid, parity, bar, m.phase, m.pending, m.tx, trace::races);
+        fflush(stdout);
+        _exit(3);
+    }
     trace::join_into(trace::vc[trace::tid], m.done[parity & 1u]);
 }
 }  // namespace b2
 
 namespace trace {
 // run `ctas` CTAs of `kCtaThreads` threads concurrently (one cluster); fn(cta, thread) is the kernel body
-template <class F> static void launch(int ctas, F fn)
+template <class F> static void launch(int ctas, F fn, int nthreads = kCtaThreads)
 {
     std::vector<std::thread> th;
     for (int c = 0; c < ctas; c++)
-        for (int t = 0; t < kCtaThreads; t++)
+        for (int t = 0; t < nthreads; t++)
             th.emplace_back([=] {
                 tid = c * kCtaThreads + t;
                 threadIdx = TraceDim3{(unsigned)t, 0, 0};
                 blockIdx = TraceDim3{(unsigned)c, 0, 0};
-                blockDim = TraceDim3{(unsigned)kCtaThreads, 1, 1};
+                blockDim = TraceDim3{(unsigned)nthreads, 1, 1};
                 gridDim = TraceDim3{(unsigned)ctas, 1, 1};
                 fn(c, t);
             });
