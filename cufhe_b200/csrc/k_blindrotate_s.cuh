@@ -132,7 +132,6 @@ struct SAddr {              // per-thread shared-window byte addresses
 };
 constexpr int kXsBytes = kXsWords * 4;
 
-#ifndef B2_HOST_TRACE
 __device__ __forceinline__ void stage_tables_s(uint32_t* s_tab, const TeamSTables* g_tab)
 {
     const uint4* src = reinterpret_cast<const uint4*>(g_tab);
@@ -140,6 +139,7 @@ __device__ __forceinline__ void stage_tables_s(uint32_t* s_tab, const TeamSTable
     for (int i = threadIdx.x; i < kTeamSTableWords / 4; i += blockDim.x) dst[i] = __ldg(src + i);
 }
 
+#ifndef B2_HOST_TRACE
 // warp-uniform random sleep of 0..1023 ns (clock-seeded: different in every launch).  It moves WARPS against each
 // other: tools/fuzz_mutants.cu shows that dropping any of the six cross-warp barriers of a step is caught (all gates
 // wrong under fuzzing; the 'lead' barrier alone corrupts only ~5 of 1184 gates without it).  The four __syncwarp()
@@ -436,11 +436,13 @@ __device__ __forceinline__ SAddr brs_addr(const TeamSTables* tab, const uint32_t
     return a;
 }
 
-#ifndef B2_HOST_TRACE
+#ifndef B2_BRS_STEPS
+#define B2_BRS_STEPS kLwe          // 636; the host trace build (tests/emul/emul_brs.cpp) walks a few steps only
+#endif
 template <int G, bool ROW0 = false, int ABL = 0, int KEYLD = 0>
 __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P, const TeamSTables* __restrict__ tabs)
 {
-    extern __shared__ __align__(16) uint32_t smem[];
+    B2_DYN_SMEM(smem);
     stage_tables_s(smem, tabs);
     __syncthreads();
 
@@ -475,28 +477,27 @@ __global__ void __launch_bounds__(128 * G, 1) k_blind_rotate_s(const BrParams P,
     const uint32_t bbar = modswitch_b((uint32_t)cbody & 0xFFFFu);
     for (int c = t128; c < kN; c += 128) {
         const uint32_t tv = testvec_b((uint32_t)c, bbar, P.mu);
-        acc[c] = 0u;
-        acc[kN + c] = 0u;
-        acc[2 * kN + c] = 0u - tv;
-        acc[3 * kN + c] = tv;
+        B2_SMEM_WR(acc + c, 0u);
+        B2_SMEM_WR(acc + kN + c, 0u);
+        B2_SMEM_WR(acc + 2 * kN + c, 0u - tv);
+        B2_SMEM_WR(acc + 3 * kN + c, tv);
     }
     named_bar_sync(gbar, 128);
 
-    brs_gate_loop<ROW0, ABL, KEYLD>(P.bk, smem_u32(acc), a, s_abar, T, q, tbar, gbar, P.dbg);
+    brs_gate_loop<ROW0, ABL, KEYLD>(P.bk, smem_u32(acc), a, s_abar, T, q, tbar, gbar, P.dbg, B2_BRS_STEPS);
 
     // ---- SampleExtract(0) (src/bootstrap_gpu.cu:366-381) ----
     const uint32_t* acc0 = acc + kN;                         // +acc_0
     const uint32_t* acc1 = acc + 3 * kN;                     // +acc_1
     if (P.trlwe) {          // BootstrapTLWE2TRLWE (src/bootstrap_gpu.cu:316-322): no extraction
         uint32_t* out = P.out + (size_t)it.slot * 2 * kN;
-        for (int m = t128; m < kN; m += 128) { out[m] = acc0[m]; out[kN + m] = acc1[m]; }
+        for (int m = t128; m < kN; m += 128) { out[m] = B2_SMEM_RD(acc0 + m); out[kN + m] = B2_SMEM_RD(acc1 + m); }
         return;
     }
     uint32_t* out = P.out + (size_t)it.slot * kLvl1Words;
-    for (int m = t128; m < kN; m += 128) out[m] = m == 0 ? acc0[0] : 0u - acc0[kN - m];
-    if (t128 == 0) out[kN] = acc1[0];
+    for (int m = t128; m < kN; m += 128) out[m] = m == 0 ? B2_SMEM_RD(acc0) : 0u - B2_SMEM_RD(acc0 + kN - m);
+    if (t128 == 0) out[kN] = B2_SMEM_RD(acc1);
 }
 
-#endif  // B2_HOST_TRACE
 
 }  // namespace b2

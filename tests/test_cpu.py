@@ -188,6 +188,21 @@ def test_transform_kernels_race_detector_on_the_real_kernel_source(tmp_path):
         assert "DEADLOCK" in out or "races 0," not in out.splitlines()[-1], (site, out)
 
 
+def test_whole_throughput_kernel_race_detector(tmp_path):
+    """tests/emul/emul_brs.cpp: the REAL k_blind_rotate_s<4> as one CTA of 512 host threads -- four gate slots side by
+    side, three of them occupied -- from table staging and pre-add / modulus switch / test vector through three
+    CMUX steps to SampleExtract(0): no race (the gates' named barriers do not interfere, head and tail are ordered
+    against the loop), lvl1 outputs equal to the oracle's; a dropped hand-over barrier is reported."""
+    orc.build()
+    exe = str(tmp_path / "emul_brs")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-pthread", "-o", exe, os.path.join(ROOT, "tests", "emul", "emul_brs.cpp"),
+                           "-L" + os.path.join(ROOT, "oracle"), "-lorc", "-Wl,-rpath," + os.path.join(ROOT, "oracle")])
+    out = subprocess.run([exe, "0"], capture_output=True, text=True, timeout=900).stdout
+    assert "races 0, output words differing from the oracle 0" in out, out
+    out = subprocess.run([exe, "9"], capture_output=True, text=True, timeout=900).stdout
+    assert int(out.split("races ")[1].split(",")[0]) > 0, out
+
+
 # -------------------------------------------------------------- host logic ---
 def test_partition_covers_batch():
     from cufhe_b200.api import partition
