@@ -31,7 +31,7 @@ static_assert(cmux_smem_bytes(4) <= 227 * 1024, "shared memory");
 template <int G>
 __global__ void __launch_bounds__(128 * G, 1) k_cmux_s(const CmuxParams P, const PrimeSTables* __restrict__ g_tab)
 {
-    extern __shared__ __align__(16) uint32_t smem[];
+    B2_DYN_SMEM(smem);
     stage_prime_tables<2>(smem, g_tab);
     __syncthreads();
     const int gs = threadIdx.x >> 7, t128 = threadIdx.x & 127;

@@ -3,7 +3,7 @@
 // Runs the REAL kernels of cufhe_b200/csrc/k_ntt_s.cuh (B2_HOST_TRACE build, one persistent CTA, one host thread
 // per CUDA thread): k_ntt_fwd_s<0, true> and k_ntt_inv_s<true> with their bulk-copy (TMA) input prefetch -- a
 // staging buffer that is re-armed and overwritten while other threads may still read it, an mbarrier with a
-// transaction count -- and k_polymul_s<2> / <3>.  tests/emul/trace_rt.h reports every pair of unordered
+// transaction count --, k_polymul_s<2> / <3> and the stand-alone CMUX k_cmux_s<4> (two of the four item slots used).  tests/emul/trace_rt.h reports every pair of unordered
 // conflicting shared-memory accesses; the results are checked as well: INTT(NTT(x)) == x and the products
 // against the oracle's schoolbook product.
 // usage: emul_nttk [polys] [drop] [deadlock seconds]   drop = 11 / 12 removes the barrier that protects the staging buffer of the
@@ -11,7 +11,7 @@
 // deadlock that follows when the mbarrier's phase runs ahead of a waiting thread).
 #define B2_HOST_TRACE 1
 #include <random>
-#include "../../cufhe_b200/csrc/k_ntt_s.cuh"
+#include "../../cufhe_b200/csrc/k_cmux.cuh"
 #include "../../oracle/cufhe_oracle.h"
 #define TRACE_THREADS 512
 #define TRACE_CTA_THREADS 512
@@ -84,7 +84,52 @@ int main(int argc, char** argv)
             bad_prod += memcmp(ref, &prod[(size_t)p * kN], sizeof ref) != 0;
         }
     }
-    printf("polynomials %d: %ld shared-memory accesses traced, races %ld, round-trip words wrong %d, residues out of range %d, products wrong %d\n",
+    // stand-alone CMUX: out = c0 + (c1 - c0) [.] TRGSW, two items in a four-item CTA, one TRGSW per item
+    int bad_cmux = 0;
+    {
+        const int items = 2;
+        std::vector<uint32_t> tr_raw((size_t)items * 8 * kN), tr_dev((size_t)items * 16 * kN), c1((size_t)items * 2 * kN), c0((size_t)items * 2 * kN), co((size_t)items * 2 * kN);
+        for (auto& v : tr_raw) v = (uint32_t)rng();
+        for (auto& v : c1) v = (uint32_t)rng();
+        for (auto& v : c0) v = (uint32_t)rng();
+        auto ntt_host = [&](uint32_t* dst, const uint32_t* src, int q) {
+            const uint32_t p = kP[q], psi = h_psi(p);
+            std::vector<uint32_t> w(kN);
+            for (int i = 0; i < kN; i++) w[i] = src[i] % p;
+            for (int s = 0, len = kN / 2; s < kNbit; s++, len >>= 1)
+                for (int g = 0; g < (1 << s); g++) {
+                    const uint32_t tw = h_powmod(psi, brv10((1u << s) + g), p);
+                    for (int j = 0; j < len; j++) {
+                        const int u = g * 2 * len + j, v = u + len;
+                        const uint32_t t = h_mulmod(w[v], tw, p);
+                        w[v] = (w[u] + p - t) % p;
+                        w[u] = (w[u] + t) % p;
+                    }
+                }
+            const uint32_t r32 = (uint32_t)((1ull << 32) % p);
+            for (int T = 0; T < 64; T++)
+                for (int k = 0; k < 16; k++) dst[bk16_slot(T, k)] = h_mulmod(w[eC(T, k)], r32, p);
+        };
+        for (int it = 0; it < items; it++)
+            for (int row = 0; row < 4; row++)
+                for (int q = 0; q < 2; q++)
+                    for (int o = 0; o < 2; o++)
+                        ntt_host(&tr_dev[(((size_t)it * 4 + row) * 2 + q) * 2 * kN + (size_t)o * kN], &tr_raw[((size_t)it * 4 + row) * 2 * kN + (size_t)o * kN], q);
+        CmuxParams CP{};
+        CP.cs = tr_dev.data(); CP.c1 = c1.data(); CP.c0 = c0.data(); CP.out = co.data(); CP.count = items; CP.cs_per_item = 1;
+        trace::races = trace::events = 0;
+        reset((size_t)cmux_smem_bytes(4));
+        trace::launch(1, [&](int, int) { k_cmux_s<4>(CP, L.pr); });
+        printf("k_cmux_s<4>:          %ld accesses, races %ld\n", trace::events, trace::races);
+        races += trace::races; events += trace::events;
+        static uint32_t ref[2 * kN];
+        for (int it = 0; it < items; it++) {
+            orc_cmux(ref, &tr_raw[(size_t)it * 8 * kN], &c1[(size_t)it * 2 * kN], &c0[(size_t)it * 2 * kN], 0);
+            bad_cmux += memcmp(ref, &co[(size_t)it * 2 * kN], sizeof ref) != 0;
+        }
+    }
+    bad_prod += bad_cmux;
+    printf("polynomials %d: %ld shared-memory accesses traced, races %ld, round-trip words wrong %d, residues out of range %d, products / CMUX results wrong %d\n",
            n, events, races, bad_rt, bad_range, bad_prod);
     trace::print_races();
     return 0;

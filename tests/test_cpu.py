@@ -171,7 +171,7 @@ def test_cluster_kernel_race_detector_on_the_real_kernel_source(tmp_path):
 def test_transform_kernels_race_detector_on_the_real_kernel_source(tmp_path):
     """tests/emul/emul_nttk.cpp runs the REAL k_ntt_fwd_s<0, true> / k_ntt_inv_s<true> (bulk-copy input prefetch:
     a staging buffer that is re-armed while it may still be read, an mbarrier with a transaction count) and
-    k_polymul_s<2> / <3> as one persistent CTA on host threads under the vector-clock tracer: no race in 2.1 M
+    k_polymul_s<2> / <3> / k_cmux_s<4> as one CTA on host threads under the vector-clock tracer: no race in 2.3 M
     traced accesses, INTT(NTT(x)) == x, canonical residues, products equal to the schoolbook truth.  Without the
     barrier that keeps the producer from refilling a staging buffer (sites 11 / 12) the detector reports races
     and the deadlock that follows."""
@@ -180,7 +180,7 @@ def test_transform_kernels_race_detector_on_the_real_kernel_source(tmp_path):
     subprocess.check_call(["g++", "-O2", "-std=c++17", "-pthread", "-o", exe, os.path.join(ROOT, "tests", "emul", "emul_nttk.cpp"),
                            "-L" + os.path.join(ROOT, "oracle"), "-lorc", "-Wl,-rpath," + os.path.join(ROOT, "oracle")])
     out = subprocess.run([exe, "13", "0"], capture_output=True, text=True, timeout=900).stdout
-    assert "races 0, round-trip words wrong 0, residues out of range 0, products wrong 0" in out, out
+    assert "races 0, round-trip words wrong 0, residues out of range 0, products / CMUX results wrong 0" in out, out
     for site in (11, 12):
         out = subprocess.run([exe, "13", str(site), "5"], capture_output=True, text=True, timeout=900).stdout
         # the producer runs ahead: the phase completes twice before a consumer has waited once -> races on the buffer
