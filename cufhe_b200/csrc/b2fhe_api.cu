@@ -37,7 +37,7 @@ int g_ks_lat_max_per_sm = 32;    // k_keyswitch_lat up to this many gates per SM
 int g_br_cluster_max = 70;       // k_blind_rotate_cl4s up to this many gates: 33 four-CTA clusters run one CTA per SM (1.43 ms), up to 70 two per SM (1.91 ms); beyond that k_blind_rotate_s with one gate per CTA (3.3 ms up to 148 gates) wins
 int g_latency_mode = 1;          // small calls: 1 = latency kernels (one gate over several SMs), 0 = always the throughput kernel (b2fhe_set_latency_mode)
 bool g_br_tail_split = true;     // last partial wave of k_blind_rotate_s as its own launch (b2fhe_set_br_variant(-1) / (-2) = off / on)
-bool g_ntt_prefetch = true;     // stand-alone NTT / INTT: inputs prefetched by bulk copies (b2fhe_set_br_variant(-3) / (-4) = off / on)
+bool g_ntt_prefetch = true;     // stand-alone NTT / INTT: inputs prefetched by bulk copies; products: 5 / 3 per CTA (b2fhe_set_br_variant(-3) / (-4) = off / on)
 int g_br_variant = 0;            // 0 = by batch size, 5 = k_blind_rotate_cl4s, 40 = k_blind_rotate_s, 6 / 41 = their schedule-fuzzing builds, 48 = the key-row-0 timing experiment
 std::atomic<uint64_t> g_launches{0};
 thread_local std::string t_err;
@@ -114,6 +114,8 @@ int setup_device(int device)
     CK(cudaFuncSetAttribute(k_ntt_inv_s<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_inv_pf_smem_bytes<kNttTeams>()));
     CK(cudaFuncSetAttribute(k_polymul_s<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, 4>()));
     CK(cudaFuncSetAttribute(k_polymul_s<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<3, 6>()));
+    CK(cudaFuncSetAttribute(k_polymul_s<2, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, 10>()));
+    CK(cudaFuncSetAttribute(k_polymul_s<3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<3, 9>()));
     return noalloc_setup(device);
 }
 

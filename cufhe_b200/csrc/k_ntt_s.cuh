@@ -273,9 +273,10 @@ __global__ void __launch_bounds__(kNttThreadsS) k_ntt_inv_s(const uint32_t* __re
 // out = a (*) b negacyclic, mod 2^32.  a: any u32, b: int32.  NPR = 2: exact for |sum a_i b_j| < 2^52;
 // NPR = 3: exact for ALL inputs (|sum| < 2^73 < P/2 ~ 2^80), which covers the reference test's domain
 // a < 2^32, b < 2^18 (test/test_polynomial_mult_1024.cu:38-39) that a 2^53 modulus cannot.
-// A product is NPR teams (one per prime), two products per CTA; the last team finishes the CRT.
-template <int NPR>
-__global__ void __launch_bounds__(64 * NPR * 2) k_polymul_s(const uint32_t* __restrict__ a_in, const uint32_t* __restrict__ b_in,
+// A product is NPR teams (one per prime), PP products per CTA (named barriers: NPR PP for the teams + PP for the
+// products <= 15); the last team finishes the CRT.
+template <int NPR, int PP = 2>
+__global__ void __launch_bounds__(64 * NPR * PP) k_polymul_s(const uint32_t* __restrict__ a_in, const uint32_t* __restrict__ b_in,
                                                             uint32_t* __restrict__ out, int npoly, const PrimeSTables* __restrict__ g_tab)
 {
     B2_DYN_SMEM(smem);
@@ -286,12 +287,13 @@ __global__ void __launch_bounds__(64 * NPR * 2) k_polymul_s(const uint32_t* __re
     const SAddr a = team_addr(smem, NPR, team, q, T);
     const int32_t p = prime_of(q);
     const uint32_t pinv = pinv_of(q);
-    const int tbar = 1 + team, pbar = 1 + 2 * NPR + slot;
+    static_assert(NPR * PP + PP <= 15, "named barriers");
+    const int tbar = 1 + team, pbar = 1 + PP * NPR + slot;
     uint32_t own_of[NPR];                               // chunk T of array 0 of every team of my product
 #pragma unroll
     for (int r = 0; r < NPR; r++) own_of[r] = team_addr(smem, NPR, slot * NPR + r, r, T).own;
     bool lead = false;
-    for (int pl = blockIdx.x * 2 + slot; pl < npoly; pl += gridDim.x * 2) {                 // slot-uniform
+    for (int pl = blockIdx.x * PP + slot; pl < npoly; pl += gridDim.x * PP) {               // slot-uniform
         int32_t x[16], y[16];
         const uint32_t* pa = a_in + (size_t)pl * kN + T;
         const uint32_t* pb = b_in + (size_t)pl * kN + T;

@@ -218,7 +218,8 @@ int b2fhe_set_gates_per_cta(int gates);          /* 0 = default */
  * results, tools only), 6 / 41 = schedule-fuzzing builds of 5 / 40 (every warp sleeps a random 0..1 us around
  * every barrier, __syncwarp, mbarrier wait and hand-over; tests only).  0 / 5 / 6 / 40 / 41 produce identical bits.  -1 / -2 switch off / on the separate launch
  * of a last partial wave (on by default; does not change the variant).  -3 / -4 switch off / on the
- * bulk-copy input prefetch of b2fhe_ntt1024_batch / b2fhe_intt1024_batch (on by default; A/B only). */
+ * bulk-copy input prefetch of b2fhe_ntt1024_batch / b2fhe_intt1024_batch and the larger CTAs of the polynomial
+ * products (five / three products per CTA instead of two) -- on by default; A/B only, same bits. */
 int b2fhe_set_br_variant(int variant);
 /* 1 (default): small batches use the latency kernels; 0: every batch uses the throughput kernel (right for
  * many small calls in flight on many streams).  The choice depends on this setting and the batch size only. */

@@ -3,7 +3,7 @@
 // Runs the REAL kernels of cufhe_b200/csrc/k_ntt_s.cuh (B2_HOST_TRACE build, one persistent CTA, one host thread
 // per CUDA thread): k_ntt_fwd_s<0, true> and k_ntt_inv_s<true> with their bulk-copy (TMA) input prefetch -- a
 // staging buffer that is re-armed and overwritten while other threads may still read it, an mbarrier with a
-// transaction count --, k_polymul_s<2> / <3> and the stand-alone CMUX k_cmux_s<4> (two of the four item slots used).  tests/emul/trace_rt.h reports every pair of unordered
+// transaction count --, k_polymul_s<2, 5> / <3, 3> and the stand-alone CMUX k_cmux_s<4> (two of the four item slots used).  tests/emul/trace_rt.h reports every pair of unordered
 // conflicting shared-memory accesses; the results are checked as well: INTT(NTT(x)) == x and the products
 // against the oracle's schoolbook product.
 // usage: emul_nttk [polys] [drop] [deadlock seconds]   drop = 11 / 12 removes the barrier that protects the staging buffer of the
@@ -13,8 +13,8 @@
 #include <random>
 #include "../../cufhe_b200/csrc/k_cmux.cuh"
 #include "../../oracle/cufhe_oracle.h"
-#define TRACE_THREADS 512
-#define TRACE_CTA_THREADS 512
+#define TRACE_THREADS 640
+#define TRACE_CTA_THREADS 640
 #include "trace_rt.h"
 
 using namespace b2;
@@ -46,12 +46,12 @@ int main(int argc, char** argv)
     long races = 0, events = 0;
     // forward, inputs prefetched by bulk copies
     reset((size_t)ntt_fwd_pf_smem_bytes<kNttTeams>());
-    trace::launch(1, [&](int, int) { k_ntt_fwd_s<0, true>(a.data(), res.data(), n, L.pr); });
+    trace::launch(1, [&](int, int) { k_ntt_fwd_s<0, true>(a.data(), res.data(), n, L.pr); }, 512);
     printf("k_ntt_fwd_s<0, true>: %ld accesses, races %ld\n", trace::events, trace::races);
     races += trace::races; events += trace::events; trace::races = trace::events = 0;
     // inverse, inputs prefetched by bulk copies
     reset((size_t)ntt_inv_pf_smem_bytes<kNttTeams>());
-    trace::launch(1, [&](int, int) { k_ntt_inv_s<true>(res.data(), back.data(), n, L.pr); });
+    trace::launch(1, [&](int, int) { k_ntt_inv_s<true>(res.data(), back.data(), n, L.pr); }, 512);
     printf("k_ntt_inv_s<true>:    %ld accesses, races %ld\n", trace::events, trace::races);
     races += trace::races; events += trace::events; trace::races = trace::events = 0;
     int bad_rt = 0;
@@ -66,18 +66,18 @@ int main(int argc, char** argv)
     {
         std::vector<uint32_t> b8((size_t)n * kN);
         for (auto& v : b8) v = (uint32_t)(int32_t)((int)(rng() % 256) - 128);
-        reset((size_t)ntt_s_smem_bytes<2, 4>());
-        trace::launch(1, [&](int, int) { k_polymul_s<2>(a.data(), b8.data(), prod.data(), n, L.pr); }, 256);
-        printf("k_polymul_s<2>:       %ld accesses, races %ld\n", trace::events, trace::races);
+        reset((size_t)ntt_s_smem_bytes<2, 10>());
+        trace::launch(1, [&](int, int) { k_polymul_s<2, 5>(a.data(), b8.data(), prod.data(), n, L.pr); }, 640);
+        printf("k_polymul_s<2, 5>:    %ld accesses, races %ld\n", trace::events, trace::races);
         races += trace::races; events += trace::events; trace::races = trace::events = 0;
         static uint32_t ref[kN];
         for (int p = 0; p < n; p++) {
             orc_polymul_schoolbook(ref, &a[(size_t)p * kN], &b8[(size_t)p * kN]);
             bad_prod += memcmp(ref, &prod[(size_t)p * kN], sizeof ref) != 0;
         }
-        reset((size_t)ntt_s_smem_bytes<3, 6>());
-        trace::launch(1, [&](int, int) { k_polymul_s<3>(a.data(), b.data(), prod.data(), n, L.pr); }, 384);
-        printf("k_polymul_s<3>:       %ld accesses, races %ld\n", trace::events, trace::races);
+        reset((size_t)ntt_s_smem_bytes<3, 9>());
+        trace::launch(1, [&](int, int) { k_polymul_s<3, 3>(a.data(), b.data(), prod.data(), n, L.pr); }, 576);
+        printf("k_polymul_s<3, 3>:    %ld accesses, races %ld\n", trace::events, trace::races);
         races += trace::races; events += trace::events;
         for (int p = 0; p < n; p++) {
             orc_polymul_schoolbook(ref, &a[(size_t)p * kN], &b[(size_t)p * kN]);
@@ -119,7 +119,7 @@ int main(int argc, char** argv)
         CP.cs = tr_dev.data(); CP.c1 = c1.data(); CP.c0 = c0.data(); CP.out = co.data(); CP.count = items; CP.cs_per_item = 1;
         trace::races = trace::events = 0;
         reset((size_t)cmux_smem_bytes(4));
-        trace::launch(1, [&](int, int) { k_cmux_s<4>(CP, L.pr); });
+        trace::launch(1, [&](int, int) { k_cmux_s<4>(CP, L.pr); }, 512);
         printf("k_cmux_s<4>:          %ld accesses, races %ld\n", trace::events, trace::races);
         races += trace::races; events += trace::events;
         static uint32_t ref[2 * kN];

@@ -171,7 +171,7 @@ def test_cluster_kernel_race_detector_on_the_real_kernel_source(tmp_path):
 def test_transform_kernels_race_detector_on_the_real_kernel_source(tmp_path):
     """tests/emul/emul_nttk.cpp runs the REAL k_ntt_fwd_s<0, true> / k_ntt_inv_s<true> (bulk-copy input prefetch:
     a staging buffer that is re-armed while it may still be read, an mbarrier with a transaction count) and
-    k_polymul_s<2> / <3> / k_cmux_s<4> as one CTA on host threads under the vector-clock tracer: no race in 2.3 M
+    k_polymul_s<2, 5> / <3, 3> / k_cmux_s<4> as one CTA on host threads under the vector-clock tracer: no race in 2.3 M
     traced accesses, INTT(NTT(x)) == x, canonical residues, products equal to the schoolbook truth.  Without the
     barrier that keeps the producer from refilling a staging buffer (sites 11 / 12) the detector reports races
     and the deadlock that follows."""
