@@ -81,6 +81,7 @@ def test_ntt_input_prefetch_equals_plain_loads(engine):
     cnt = 5003
     a = rng.integers(0, 2**32, size=(cnt + 1, N), dtype=np.uint64).astype(np.uint32)
     da = dev_u32(a.reshape(-1))
+    dsmall = dev_u32(rng.integers(-128, 128, size=(cnt, N)).astype(np.int32).view(np.uint32))
     outs = {}
     try:
         for pf in (-3, -4):
@@ -93,14 +94,21 @@ def test_ntt_input_prefetch_equals_plain_loads(engine):
             cf._lib.check(L.b2fhe_intt1024_batch(0, None, db.data_ptr(), dn.data_ptr(), cnt))
             cf._lib.check(L.b2fhe_ntt1024_batch(0, None, d1.data_ptr(), da.data_ptr() + 4096 * 17, 1))
             cf._lib.check(L.b2fhe_ntt1024_batch(0, None, dm.data_ptr(), da.data_ptr() + 4, 7))      # 4-byte aligned source
+            # the same switch selects the CTA shape of the products (five / three products per CTA, or two)
+            p2 = torch.zeros((cnt, N), dtype=torch.int32, device="cuda")
+            p3 = torch.zeros((cnt, N), dtype=torch.int32, device="cuda")
+            cf._lib.check(L.b2fhe_polymul1024_batch(0, None, p2.data_ptr(), da.data_ptr(), dsmall.data_ptr(), cnt))
+            cf._lib.check(L.b2fhe_polymul1024_exact_batch(0, None, p3.data_ptr(), da.data_ptr(), da.data_ptr() + 4096 * 3, cnt - 3))
             torch.cuda.synchronize()
-            outs[pf] = (to_np(dn, np.uint32), to_np(db, np.uint32), to_np(d1, np.uint32), to_np(dm, np.uint32))
+            outs[pf] = (to_np(dn, np.uint32), to_np(db, np.uint32), to_np(d1, np.uint32), to_np(dm, np.uint32), to_np(p2, np.uint32), to_np(p3, np.uint32))
     finally:
         cf._lib.check(L.b2fhe_set_br_variant(-4))
     for x, y in zip(outs[-3], outs[-4]):
         assert np.array_equal(x, y)
     assert np.array_equal(outs[-4][1], a[:cnt])                       # round trip
     assert np.array_equal(outs[-4][2][0], outs[-4][0][17])
+    assert np.array_equal(outs[-4][4][5], orc.polymul(a[5], to_np(dsmall, np.uint32)[5], schoolbook=True))
+    assert np.array_equal(outs[-4][5][cnt - 4], orc.polymul(a[cnt - 4], a[cnt - 1], schoolbook=True))
 
 
 def test_polymul_edge_cases(engine):
