@@ -116,6 +116,8 @@ int setup_device(int device)
     CK(cudaFuncSetAttribute(k_polymul_s<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<3, 6>()));
     CK(cudaFuncSetAttribute(k_polymul_s<2, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<2, 10>()));
     CK(cudaFuncSetAttribute(k_polymul_s<3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ntt_s_smem_bytes<3, 9>()));
+    CK(cudaFuncSetAttribute(k_polymul_s<2, 5, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, polymul_pf_smem_bytes<2, 5>()));
+    CK(cudaFuncSetAttribute(k_polymul_s<3, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, polymul_pf_smem_bytes<3, 3>()));
     return noalloc_setup(device);
 }
 

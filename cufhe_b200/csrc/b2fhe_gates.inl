@@ -542,7 +542,10 @@ int b2fhe_polymul1024_batch(int device, b2fhe_stream_t stream, uint32_t* out, co
     if (int r = get_ctx(device, c)) return r;
     if (count == 0) return 0;
     REQUIRE(out && a && b && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    if (g_ntt_prefetch)      // A/B switch shared with the transforms: five products per CTA (20 warps per SM) / two (2 x 8 warps)
+    const bool aligned = ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0;
+    if (g_ntt_prefetch && aligned)      // five products per CTA (20 warps per SM), operands prefetched by bulk copies
+        k_polymul_s<2, 5, true><<<ntt_grid(*c, count, 5, 1), 640, polymul_pf_smem_bytes<2, 5>(), (cudaStream_t)stream>>>(a, b, out, (int)count, c->tabs->pr);
+    else if (g_ntt_prefetch)            // 4-byte aligned operands: plain loads
         k_polymul_s<2, 5><<<ntt_grid(*c, count, 5, 1), 640, ntt_s_smem_bytes<2, 10>(), (cudaStream_t)stream>>>(a, b, out, (int)count, c->tabs->pr);
     else
         k_polymul_s<2><<<ntt_grid(*c, count, 2, 2), 256, ntt_s_smem_bytes<2, 4>(), (cudaStream_t)stream>>>(a, b, out, (int)count, c->tabs->pr);
@@ -555,7 +558,10 @@ int b2fhe_polymul1024_exact_batch(int device, b2fhe_stream_t stream, uint32_t* o
     if (int r = get_ctx(device, c)) return r;
     if (count == 0) return 0;
     REQUIRE(out && a && b && count < (1u << 30), B2FHE_E_BAD_ARGUMENT);
-    if (g_ntt_prefetch)      // three products per CTA (18 warps per SM) / two (12 warps)
+    const bool aligned = ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0;
+    if (g_ntt_prefetch && aligned)      // three products per CTA (18 warps per SM), operands prefetched by bulk copies
+        k_polymul_s<3, 3, true><<<ntt_grid(*c, count, 3, 1), 576, polymul_pf_smem_bytes<3, 3>(), (cudaStream_t)stream>>>(a, b, out, (int)count, c->tabs->pr);
+    else if (g_ntt_prefetch)
         k_polymul_s<3, 3><<<ntt_grid(*c, count, 3, 1), 576, ntt_s_smem_bytes<3, 9>(), (cudaStream_t)stream>>>(a, b, out, (int)count, c->tabs->pr);
     else
         k_polymul_s<3><<<ntt_grid(*c, count, 2, 1), 384, ntt_s_smem_bytes<3, 6>(), (cudaStream_t)stream>>>(a, b, out, (int)count, c->tabs->pr);

@@ -150,6 +150,14 @@ template <int K = 0> __device__ __forceinline__ void ld_stage_a(int32_t (&x)[16]
     }
 }
 
+template <int K = 0> __device__ __forceinline__ void ld_stage_b(int32_t (&y)[16], const uint32_t base, const int32_t p)
+{
+    if constexpr (K < 16) {
+        y[K] = lazy_s32(lds32<256 * K>(base), p);
+        ld_stage_b<K + 1>(y, base, p);
+    }
+}
+
 // MODE 0: polynomials -> canonical residues, out[poly][2][1024]
 // MODE 1: bootstrapping key / TRGSW rows -> Montgomery-form residues in [0, p), out index
 //         ((pl>>1)*2 + q)*2 + (pl&1), i.e. [i][row][prime][out poly][1024]
@@ -275,7 +283,10 @@ __global__ void __launch_bounds__(kNttThreadsS) k_ntt_inv_s(const uint32_t* __re
 // a < 2^32, b < 2^18 (test/test_polynomial_mult_1024.cu:38-39) that a 2^53 modulus cannot.
 // A product is NPR teams (one per prime), PP products per CTA (named barriers: NPR PP for the teams + PP for the
 // products <= 15); the last team finishes the CRT.
-template <int NPR, int PP = 2>
+// PF: the next product's two operands (8 KB) are fetched by bulk copies into a per-product staging buffer while the
+// current product is computed (both operand arrays 16-byte aligned).
+template <int NPR, int PP> __host__ __device__ constexpr int polymul_pf_smem_bytes() { return ntt_s_smem_bytes<NPR, NPR * PP>() + PP * (2 * kN * 4 + 8); }
+template <int NPR, int PP = 2, bool PF = false>
 __global__ void __launch_bounds__(64 * NPR * PP) k_polymul_s(const uint32_t* __restrict__ a_in, const uint32_t* __restrict__ b_in,
                                                             uint32_t* __restrict__ out, int npoly, const PrimeSTables* __restrict__ g_tab)
 {
@@ -293,13 +304,41 @@ __global__ void __launch_bounds__(64 * NPR * PP) k_polymul_s(const uint32_t* __r
 #pragma unroll
     for (int r = 0; r < NPR; r++) own_of[r] = team_addr(smem, NPR, slot * NPR + r, r, T).own;
     bool lead = false;
-    for (int pl = blockIdx.x * PP + slot; pl < npoly; pl += gridDim.x * PP) {               // slot-uniform
+    const uint32_t stg = smem_u32(smem) + ntt_s_smem_bytes<NPR, NPR * PP>() + slot * (2 * kN * 4);
+    const uint32_t mb = smem_u32(smem) + ntt_s_smem_bytes<NPR, NPR * PP>() + PP * (2 * kN * 4) + slot * 8;
+    const bool producer = PF && q == 0 && T == 0;
+    const int first = blockIdx.x * PP + slot, stride = gridDim.x * PP;
+    if (PF) {
+        if (producer) { mbar_init(mb, 1); mbar_fence_init(); }
+        named_bar_sync(pbar, 64 * NPR);                 // the product's teams see the initialised mbarrier
+        if (producer && first < npoly) {
+            mbar_arrive_expect_tx(mb, 2 * kN * 4);
+            bulk_g2s(stg, a_in + (size_t)first * kN, kN * 4, mb);
+            bulk_g2s(stg + kN * 4, b_in + (size_t)first * kN, kN * 4, mb);
+        }
+    }
+    uint32_t phase = 0;
+    for (int pl = first; pl < npoly; pl += stride) {                                         // slot-uniform
         int32_t x[16], y[16];
-        const uint32_t* pa = a_in + (size_t)pl * kN + T;
-        const uint32_t* pb = b_in + (size_t)pl * kN + T;
+        if (PF) {
+            mbar_wait(mb, phase);
+            phase ^= 1u;
+            ld_stage_a(x, stg + 4 * T, p);
+            ld_stage_b(y, stg + kN * 4 + 4 * T, p);
+            // every team of the product has read the staging buffer -- and the finishing team the chunks of the previous product
+            if (sync_kept<0, 13>()) named_bar_sync(pbar, 64 * NPR);
+            if (producer && pl + stride < npoly) {
+                mbar_arrive_expect_tx(mb, 2 * kN * 4);
+                bulk_g2s(stg, a_in + (size_t)(pl + stride) * kN, kN * 4, mb);
+                bulk_g2s(stg + kN * 4, b_in + (size_t)(pl + stride) * kN, kN * 4, mb);
+            }
+        } else {
+            const uint32_t* pa = a_in + (size_t)pl * kN + T;
+            const uint32_t* pb = b_in + (size_t)pl * kN + T;
 #pragma unroll
-        for (int k = 0; k < 16; k++) { x[k] = lazy_u32(__ldg(pa + 64 * k), p); y[k] = lazy_s32((int32_t)__ldg(pb + 64 * k), p); }
-        if (lead) named_bar_sync(pbar, 64 * NPR);       // the finishing team has read the chunks of the previous product
+            for (int k = 0; k < 16; k++) { x[k] = lazy_u32(__ldg(pa + 64 * k), p); y[k] = lazy_s32((int32_t)__ldg(pb + 64 * k), p); }
+            if (lead) named_bar_sync(pbar, 64 * NPR);   // the finishing team has read the chunks of the previous product
+        }
         sfwd_general_dev<2>(x, y, a, q, p, tbar, lead, T);
         lead = true;
         const uint32_t r2 = canon_s(c_s.r2[q], p);

@@ -6,8 +6,8 @@
 // transaction count --, k_polymul_s<2, 5> / <3, 3> and the stand-alone CMUX k_cmux_s<4> (two of the four item slots used).  tests/emul/trace_rt.h reports every pair of unordered
 // conflicting shared-memory accesses; the results are checked as well: INTT(NTT(x)) == x and the products
 // against the oracle's schoolbook product.
-// usage: emul_nttk [polys] [drop] [deadlock seconds]   drop = 11 / 12 removes the barrier that protects the staging buffer of the
-// forward / inverse kernel from being refilled while it is read; the detector must then report (races, and the
+// usage: emul_nttk [polys] [drop] [deadlock seconds]   drop = 11 / 12 / 13 removes the barrier that protects the staging buffer of the
+// forward / inverse / product kernel from being refilled while it is read; the detector must then report (races, and the
 // deadlock that follows when the mbarrier's phase runs ahead of a waiting thread).
 #define B2_HOST_TRACE 1
 #include <random>
@@ -66,18 +66,18 @@ int main(int argc, char** argv)
     {
         std::vector<uint32_t> b8((size_t)n * kN);
         for (auto& v : b8) v = (uint32_t)(int32_t)((int)(rng() % 256) - 128);
-        reset((size_t)ntt_s_smem_bytes<2, 10>());
-        trace::launch(1, [&](int, int) { k_polymul_s<2, 5>(a.data(), b8.data(), prod.data(), n, L.pr); }, 640);
-        printf("k_polymul_s<2, 5>:    %ld accesses, races %ld\n", trace::events, trace::races);
+        reset((size_t)polymul_pf_smem_bytes<2, 5>());
+        trace::launch(1, [&](int, int) { k_polymul_s<2, 5, true>(a.data(), b8.data(), prod.data(), n, L.pr); }, 640);
+        printf("k_polymul_s<2, 5, 1>: %ld accesses, races %ld\n", trace::events, trace::races);
         races += trace::races; events += trace::events; trace::races = trace::events = 0;
         static uint32_t ref[kN];
         for (int p = 0; p < n; p++) {
             orc_polymul_schoolbook(ref, &a[(size_t)p * kN], &b8[(size_t)p * kN]);
             bad_prod += memcmp(ref, &prod[(size_t)p * kN], sizeof ref) != 0;
         }
-        reset((size_t)ntt_s_smem_bytes<3, 9>());
-        trace::launch(1, [&](int, int) { k_polymul_s<3, 3>(a.data(), b.data(), prod.data(), n, L.pr); }, 576);
-        printf("k_polymul_s<3, 3>:    %ld accesses, races %ld\n", trace::events, trace::races);
+        reset((size_t)polymul_pf_smem_bytes<3, 3>());
+        trace::launch(1, [&](int, int) { k_polymul_s<3, 3, true>(a.data(), b.data(), prod.data(), n, L.pr); }, 576);
+        printf("k_polymul_s<3, 3, 1>: %ld accesses, races %ld\n", trace::events, trace::races);
         races += trace::races; events += trace::events;
         for (int p = 0; p < n; p++) {
             orc_polymul_schoolbook(ref, &a[(size_t)p * kN], &b[(size_t)p * kN]);

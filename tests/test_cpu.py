@@ -171,9 +171,10 @@ def test_cluster_kernel_race_detector_on_the_real_kernel_source(tmp_path):
 def test_transform_kernels_race_detector_on_the_real_kernel_source(tmp_path):
     """tests/emul/emul_nttk.cpp runs the REAL k_ntt_fwd_s<0, true> / k_ntt_inv_s<true> (bulk-copy input prefetch:
     a staging buffer that is re-armed while it may still be read, an mbarrier with a transaction count) and
-    k_polymul_s<2, 5> / <3, 3> / k_cmux_s<4> as one CTA on host threads under the vector-clock tracer: no race in 2.3 M
+    k_polymul_s<2, 5, true> / <3, 3, true> (operands prefetched the same way) / k_cmux_s<4> as one CTA on host threads under
+    the vector-clock tracer: no race in 2.5 M
     traced accesses, INTT(NTT(x)) == x, canonical residues, products equal to the schoolbook truth.  Without the
-    barrier that keeps the producer from refilling a staging buffer (sites 11 / 12) the detector reports races
+    barrier that keeps the producer from refilling a staging buffer (sites 11 / 12 / 13) the detector reports races
     and the deadlock that follows."""
     orc.build()
     exe = str(tmp_path / "emul_nttk")
@@ -181,7 +182,7 @@ def test_transform_kernels_race_detector_on_the_real_kernel_source(tmp_path):
                            "-L" + os.path.join(ROOT, "oracle"), "-lorc", "-Wl,-rpath," + os.path.join(ROOT, "oracle")])
     out = subprocess.run([exe, "13", "0"], capture_output=True, text=True, timeout=900).stdout
     assert "races 0, round-trip words wrong 0, residues out of range 0, products / CMUX results wrong 0" in out, out
-    for site in (11, 12):
+    for site in (11, 12, 13):
         out = subprocess.run([exe, "13", str(site), "5"], capture_output=True, text=True, timeout=900).stdout
         # the producer runs ahead: the phase completes twice before a consumer has waited once -> races on the buffer
         # and / or a consumer that waits for a parity that never comes again

@@ -99,8 +99,11 @@ def test_ntt_input_prefetch_equals_plain_loads(engine):
             p3 = torch.zeros((cnt, N), dtype=torch.int32, device="cuda")
             cf._lib.check(L.b2fhe_polymul1024_batch(0, None, p2.data_ptr(), da.data_ptr(), dsmall.data_ptr(), cnt))
             cf._lib.check(L.b2fhe_polymul1024_exact_batch(0, None, p3.data_ptr(), da.data_ptr(), da.data_ptr() + 4096 * 3, cnt - 3))
+            pm = torch.zeros((9, N), dtype=torch.int32, device="cuda")
+            cf._lib.check(L.b2fhe_polymul1024_batch(0, None, pm.data_ptr(), da.data_ptr() + 4, dsmall.data_ptr(), 9))      # 4-byte aligned operand
             torch.cuda.synchronize()
-            outs[pf] = (to_np(dn, np.uint32), to_np(db, np.uint32), to_np(d1, np.uint32), to_np(dm, np.uint32), to_np(p2, np.uint32), to_np(p3, np.uint32))
+            outs[pf] = (to_np(dn, np.uint32), to_np(db, np.uint32), to_np(d1, np.uint32), to_np(dm, np.uint32), to_np(p2, np.uint32), to_np(p3, np.uint32),
+                        to_np(pm, np.uint32))
     finally:
         cf._lib.check(L.b2fhe_set_br_variant(-4))
     for x, y in zip(outs[-3], outs[-4]):
