@@ -36,10 +36,10 @@ static float run(const char* name, BrParams P, const TeamSTables* tabs, int reps
 int main(int argc, char** argv)
 {
     const int count = argc > 1 ? atoi(argv[1]) : 16384;
-    static TeamSTables LS; static TeamSConst CS;
+    static TeamSTables3 LS; static TeamSConst CS;
     make_tables16s(LS, CS);
     CK(cudaMemcpyToSymbol(c_s, &CS, sizeof CS));
-    TeamSTables* tabs; CK(cudaMalloc(&tabs, sizeof LS)); CK(cudaMemcpy(tabs, &LS, sizeof LS, cudaMemcpyHostToDevice));
+    TeamSTables* tabs; CK(cudaMalloc(&tabs, sizeof LS)); CK(cudaMemcpy(tabs, &LS, sizeof LS, cudaMemcpyHostToDevice));   // the first two primes are a TeamSTables
     std::mt19937_64 rng(1);
     const size_t bkw = (size_t)kLwe * kRows * 2 * 2 * kN;
     std::vector<uint32_t> bk(bkw);
